@@ -1,0 +1,225 @@
+"""Mesh container, `.inp` reader/writer and rank-local renumbering.
+
+Host-side mirror of the reference's input layer -- same grammar, same index
+conventions -- so a deck the reference reads gives the arrays the C ABI takes:
+
+* grammar: `ReadParameters` src/m_io.F90:12-20, `ReadElementsCoords` :71-105,
+  `ReadDistMaterials` :282-328, forces :330-371, BCs :373-412;
+* local numbering: src/main.F90:49-96 (`work`/`nl2g`/`indxmap`);
+* element distribution: `epart` -> ascending global element order per rank,
+  src/m_io.F90:200-237.
+
+Element type codes are `getElTypeNo` (src/m_elems.F90:25): 1 tri, 2 qua, 3 tet,
+4 hex, 5 coh.  hex has 8 nodes here (the reference's table says 6: defect D1).
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Optional
+
+import numpy as np
+
+TRI, QUA, TET, HEX, COH = 1, 2, 3, 4, 5
+TYPE_NAMES = {"tri": TRI, "qua": QUA, "tet": TET, "hex": HEX, "coh": COH}
+TYPE_TAGS = {v: k for k, v in TYPE_NAMES.items()}
+NEN = {TRI: 3, QUA: 4, TET: 4, HEX: 8, COH: 4}
+NIP = {TRI: 1, QUA: 4, TET: 1, HEX: 8, COH: 2}
+DIM = {TRI: 2, QUA: 2, TET: 3, HEX: 3, COH: 2}
+
+
+@dataclasses.dataclass
+class Mesh:
+    pdim: int
+    etype: np.ndarray          # [nels] int32 type codes
+    eptr: np.ndarray           # [nels+1] int32
+    eind: np.ndarray           # 1-based LOCAL node ids
+    emat: np.ndarray           # [nels] 1-based material row, 0 for coh
+    enlmat: np.ndarray         # [nels] 0 linear / k -> cohprops row k
+    coords: np.ndarray         # [nlnds, pdim]
+    nl2g: np.ndarray           # [nlnds] 1-based global node id
+    nnds: int                  # global node count
+    mat: np.ndarray            # [nmts, 5] E nu visc expn density
+    cohprops: np.ndarray       # [ncoh, 6]
+    bcnode: np.ndarray         # [nbcs, 1+pdim] global node, flags (0 = constrained)
+    bcval: np.ndarray          # [nbcs, pdim]
+    fnode: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros(0, np.int32))
+    fval: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros((0, 0)))
+    t: float = 1.0
+    dt: float = 1.0
+    nodal_bw: int = 10
+    stype: str = "implicit"
+    eglobal: Optional[np.ndarray] = None   # [nels] 0-based global element id (rank-local meshes)
+
+    @property
+    def nels(self) -> int:
+        return len(self.etype)
+
+    @property
+    def nlnds(self) -> int:
+        return self.coords.shape[0]
+
+    @property
+    def cpdim(self) -> int:
+        return 3 if self.pdim == 2 else 6
+
+    @property
+    def ndof(self) -> int:
+        return self.pdim * self.nnds
+
+    def elem_nodes(self, e: int) -> np.ndarray:
+        return self.eind[self.eptr[e]:self.eptr[e + 1]]
+
+    def normalized(self) -> "Mesh":
+        """dtype / contiguity normalisation (what the C ABI expects)."""
+        i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        return dataclasses.replace(
+            self, etype=i32(self.etype), eptr=i32(self.eptr), eind=i32(self.eind), emat=i32(self.emat),
+            enlmat=i32(self.enlmat), coords=f64(self.coords).reshape(-1, self.pdim), nl2g=i32(self.nl2g),
+            mat=f64(self.mat).reshape(-1, 5), cohprops=f64(self.cohprops).reshape(-1, 6),
+            bcnode=i32(self.bcnode).reshape(-1, 1 + self.pdim), bcval=f64(self.bcval).reshape(-1, self.pdim))
+
+
+def from_uniform(pdim, etype_code, conn, coords, E=3.0e10, nu=0.25, **kw) -> Mesh:
+    """Single-type mesh from a [nels, nen] 1-based connectivity table."""
+    conn = np.asarray(conn, dtype=np.int32)
+    nels, nen = conn.shape
+    coords = np.asarray(coords, dtype=np.float64).reshape(-1, pdim)
+    return Mesh(pdim=pdim, etype=np.full(nels, etype_code, np.int32),
+                eptr=np.arange(0, (nels + 1) * nen, nen, dtype=np.int32), eind=conn.reshape(-1).copy(),
+                emat=np.ones(nels, np.int32), enlmat=np.zeros(nels, np.int32), coords=coords,
+                nl2g=np.arange(1, coords.shape[0] + 1, dtype=np.int32), nnds=coords.shape[0],
+                mat=np.array([[E, nu, 1.0e18, 1.0, 3000.0]]), cohprops=np.zeros((0, 6)),
+                bcnode=np.zeros((0, 1 + pdim), np.int32), bcval=np.zeros((0, pdim)), **kw).normalized()
+
+
+# --------------------------------------------------------------------------- .inp grammar
+class _Records:
+    """Fortran list-directed reads: each read starts on a fresh record and pulls records
+    until it has the items it needs; anything left on the last record is dropped (that is
+    why trailing `! comments` work in the decks)."""
+
+    def __init__(self, text: str):
+        self.lines = text.splitlines()
+        self.pos = 0
+
+    def read(self, n: int):
+        out = []
+        while len(out) < n:
+            if self.pos >= len(self.lines):
+                raise ValueError("unexpected end of input deck")
+            line = self.lines[self.pos].split("!")[0].replace(",", " ")
+            self.pos += 1
+            out.extend(line.split())
+        return out[:n]
+
+    def peek_first(self):
+        p = self.pos
+        while True:
+            toks = self.lines[p].split("!")[0].replace(",", " ").split()
+            if toks:
+                return toks[0]
+            p += 1
+
+
+def _f(tok: str) -> float:
+    return float(tok.replace("d", "e").replace("D", "E"))
+
+
+def read_inp(path_or_text: str) -> Mesh:
+    """Parse a deck in the CURRENT grammar (8 header counts; elements carry `mat nlMat`)."""
+    text = path_or_text
+    if "\n" not in path_or_text:
+        with open(path_or_text) as fh:
+            text = fh.read()
+    r = _Records(text)
+    stype, pdim, nodal_bw = r.read(3)
+    pdim, nodal_bw = int(pdim), int(nodal_bw)
+    nels, nnds, nmts, ncoh, nceqs, nfrcs, ntrcs, nbcs = (int(x) for x in r.read(8))
+    t, dt = (_f(x) for x in r.read(2))
+    etype, eptr, eind, emat, enl = [], [0], [], [], []
+    for _ in range(nels):
+        tag = r.peek_first().strip("'\"")
+        code = TYPE_NAMES[tag]
+        toks = r.read(1 + NEN[code] + 2)
+        etype.append(code)
+        eind.extend(int(x) for x in toks[1:1 + NEN[code]])
+        eptr.append(len(eind))
+        emat.append(int(toks[-2]))
+        enl.append(int(toks[-1]))
+    coords = np.array([[_f(x) for x in r.read(pdim)] for _ in range(nnds)]).reshape(nnds, pdim)
+    mat = np.array([[_f(x) for x in r.read(5)] for _ in range(nmts)]).reshape(nmts, 5)
+    coh = np.zeros((ncoh, 6))
+    for i in range(ncoh):
+        toks = r.read(7)  # seplaw id then PROP_COUNTS(1) = 6 props (src/m_seplaw.F90:8)
+        coh[i] = [_f(x) for x in toks[1:]]
+    # order in the file follows the reads in main: BCs, forces, tractions (src/main.F90:100-102)
+    bcnode = np.zeros((nbcs, 1 + pdim), np.int32)
+    bcval = np.zeros((nbcs, pdim))
+    for i in range(nbcs):
+        toks = r.read(1 + 2 * pdim)
+        bcnode[i] = [int(x) for x in toks[:1 + pdim]]
+        bcval[i] = [_f(x) for x in toks[1 + pdim:]]
+    fnode = np.zeros(nfrcs, np.int32)
+    fval = np.zeros((nfrcs, pdim + 2))
+    for i in range(nfrcs):
+        toks = r.read(1 + pdim + 2)
+        fnode[i] = int(toks[0])
+        fval[i] = [_f(x) for x in toks[1:]]
+    return Mesh(pdim=pdim, etype=np.array(etype), eptr=np.array(eptr), eind=np.array(eind),
+                emat=np.array(emat), enlmat=np.array(enl), coords=coords,
+                nl2g=np.arange(1, nnds + 1), nnds=nnds, mat=mat, cohprops=coh, bcnode=bcnode,
+                bcval=bcval, fnode=fnode, fval=fval, t=t, dt=dt, nodal_bw=nodal_bw,
+                stype=stype.strip("'\"")).normalized()
+
+
+def write_inp(m: Mesh, path: str) -> None:
+    """Emit the current grammar (global mesh: nl2g must be the identity)."""
+    assert np.array_equal(m.nl2g, np.arange(1, m.nnds + 1)), "write_inp wants a global mesh"
+    with open(path, "w") as fh:
+        fh.write(f"{m.stype} {m.pdim} {m.nodal_bw}\n")
+        fh.write(f"{m.nels} {m.nnds} {len(m.mat)} {len(m.cohprops)} 0 {len(m.fnode)} 0 {len(m.bcnode)}\n")
+        fh.write(f"{m.t!r} {m.dt!r}\n")
+        for e in range(m.nels):
+            nodes = " ".join(str(int(x)) for x in m.elem_nodes(e))
+            fh.write(f"{TYPE_TAGS[int(m.etype[e])]} {nodes} {int(m.emat[e])} {int(m.enlmat[e])}\n")
+        for x in m.coords:
+            fh.write(" ".join(repr(float(v)) for v in x) + "\n")
+        for row in m.mat:
+            fh.write(" ".join(repr(float(v)) for v in row) + "\n")
+        for row in m.cohprops:
+            fh.write("1 " + " ".join(repr(float(v)) for v in row) + "\n")
+        for i in range(len(m.bcnode)):
+            fh.write(" ".join(str(int(v)) for v in m.bcnode[i]) + " " +
+                     " ".join(repr(float(v)) for v in m.bcval[i]) + "\n")
+        for i in range(len(m.fnode)):
+            fh.write(f"{int(m.fnode[i])} " + " ".join(repr(float(v)) for v in m.fval[i]) + "\n")
+
+
+# --------------------------------------------------------------------------- distribution
+def localize(g: Mesh, epart: np.ndarray, rank: int) -> Mesh:
+    """Rank-local mesh exactly as src/m_io.F90:200-237 + src/main.F90:49-96 build it:
+    elements with epart == rank in ascending global order; local node ids assigned in
+    ascending global node order; nl2g the inverse map."""
+    epart = np.asarray(epart)
+    sel = np.nonzero(epart == rank)[0]
+    counts = (g.eptr[1:] - g.eptr[:-1])[sel]
+    eptr = np.zeros(len(sel) + 1, np.int64)
+    np.cumsum(counts, out=eptr[1:])
+    idx = np.repeat(g.eptr[sel].astype(np.int64) - eptr[:-1], counts) + np.arange(eptr[-1])
+    gnodes = g.eind[idx]
+    nl2g = np.unique(gnodes)                      # ascending global ids -> local 1..nlnds
+    work = np.zeros(g.nnds + 1, np.int32)
+    work[nl2g] = np.arange(1, len(nl2g) + 1)
+    return dataclasses.replace(
+        g, etype=g.etype[sel], eptr=eptr.astype(np.int32), eind=work[gnodes], emat=g.emat[sel],
+        enlmat=g.enlmat[sel], coords=g.coords[nl2g - 1], nl2g=nl2g.astype(np.int32),
+        eglobal=sel.astype(np.int64)).normalized()
+
+
+def petsc_ownership(n: int, nranks: int, rank: int):
+    """PETSC_DECIDE row split used by MatCreateAIJ/VecCreateMPI (src/main.F90:137-138,154):
+    rank r owns n/P + (r < n mod P) consecutive rows.  Returns [start, end)."""
+    base, rem = divmod(n, nranks)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
