@@ -1,0 +1,117 @@
+// femx_internal.h -- ctx layout, host plan, launcher prototypes (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/femx.h"
+
+namespace femx {
+
+constexpr int kMaxNen = 8;
+__host__ __device__ inline int type_nen(int t) { return t == FEMX_TRI ? 3 : (t == FEMX_HEX ? 8 : 4); }
+__host__ __device__ inline int type_nip(int t) {
+  return t == FEMX_QUA ? 4 : (t == FEMX_HEX ? 8 : (t == FEMX_COH ? 2 : 1));
+}
+__host__ __device__ inline int type_dim(int t) { return (t == FEMX_TET || t == FEMX_HEX) ? 3 : 2; }
+
+// PENALTY_PARAM = 1.0e30 is a default-real literal in the reference (src/m_global.F90:15)
+constexpr double kPenalty = 1.0000000150474662e30;
+
+// ------------------------------------------------------------------ host plan (plan.cpp)
+// One-time integer pass: block (node x node) CSR of the assembled matrix, the
+// node -> (element, local node) incidence in ascending element order, and the
+// element -> block-position map.  Scalar CSR slots follow in closed form:
+//   slot(r,i,k,j) = pd*pd*bptr[r] + i*pd*(bptr[r+1]-bptr[r]) + pd*k + j
+struct Plan {
+  int pdim = 0, nels = 0, nlnds = 0, nnds = 0;
+  std::vector<int32_t> conn0;      // 0-based local nodes, eptr offsets
+  std::vector<int64_t> bptr;       // [nlnds+1]
+  std::vector<int32_t> bcol;       // [nblk] local node, ascending
+  std::vector<int32_t> bdiag;      // [nlnds] position of r in its own block row
+  std::vector<int64_t> n2e_ptr;    // [nlnds+1]
+  std::vector<int32_t> n2e_elem;   // ascending element per node
+  std::vector<uint8_t> n2e_a;      // local node index within that element
+  std::vector<int64_t> eb_ptr;     // [nels+1] sum nen^2
+  std::vector<uint16_t> bpos;      // block position of (e, a, b) in row conn[e][a]
+  std::vector<int64_t> ke_off;     // [nels+1] offsets (doubles) of packed Ke scratch: nen^2*pd^2
+  std::vector<int64_t> fe_off;     // [nels+1] offsets of per-element vectors: nen*pd
+  int64_t nblk = 0;
+  // cohesive overlay: blocks / nodes touched by nonlinear elements, contributions ascending
+  std::vector<int32_t> coh_elems;        // local element ids with enlmat != 0
+  std::vector<int64_t> cblk_id;          // touched block ids (r-major order)
+  std::vector<int32_t> cblk_row;         // row node of each touched block
+  std::vector<int32_t> cblk_ptr;         // [ncblk+1]
+  std::vector<int32_t> cblk_src;         // (coh index << 8) | (a << 4) | b
+  std::vector<int32_t> cnode_id;         // nodes touched by cohesive elements
+  std::vector<int32_t> cnode_ptr;        // [ncnode+1]
+  std::vector<int32_t> cnode_src;        // (coh index << 4) | a
+  double build_seconds = 0.0;
+};
+
+int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int *eind,
+               const int *enlmat, int nlnds, int nnds, Plan *out, std::string *err);
+
+// ------------------------------------------------------------------ device views
+struct Bucket {            // homogeneous element-type bucket, ascending local element id
+  int type = 0, n = 0;
+  int32_t *d_elem = nullptr;   // [n] local element id
+  std::vector<int32_t> h_elem;
+};
+
+struct DevMesh {
+  int pdim = 0, nels = 0, nlnds = 0, nnds = 0, cp = 0;
+  int32_t *etype = nullptr, *eptr = nullptr, *conn0 = nullptr, *emat = nullptr, *enlmat = nullptr;
+  int32_t *nl2g = nullptr;     // 1-based global node
+  double *coords = nullptr;    // [nlnds][pdim]
+  double *lam_mu = nullptr;    // [nmts][2]
+  double *cohprops = nullptr;  // [ncoh][6]
+  // plan
+  int64_t *bptr = nullptr, *n2e_ptr = nullptr, *eb_ptr = nullptr, *ke_off = nullptr, *fe_off = nullptr;
+  int32_t *bcol = nullptr, *bdiag = nullptr, *n2e_elem = nullptr;
+  uint8_t *n2e_a = nullptr;
+  uint16_t *bpos = nullptr;
+  int32_t *node_count = nullptr;  // stress-average multiplicity per local node
+};
+
+}  // namespace femx
+
+struct femx_ctx {
+  int device = 0;
+  femx_opts opts{};
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  double last_ms = 0.0;
+  // host copies
+  int pdim = 0, nels = 0, nlnds = 0, nnds = 0, nmts = 0, ncoh = 0, nbcs = 0;
+  std::vector<int32_t> etype, eptr, eind, emat, enlmat, nl2g;
+  std::vector<double> coords, E_nu, cohprops, bcval;
+  std::vector<int32_t> bcnode;
+  bool has_mesh = false, has_plan = false;
+  femx::Plan plan;
+  femx::DevMesh dm;
+  std::vector<femx::Bucket> buckets;
+  // scratch
+  double *d_ke = nullptr;     // packed block-major element matrices
+  double *d_fe = nullptr;     // per-element vectors (f_e)
+  double *d_sn = nullptr;     // per-element nodal stress [nen][cp]
+  double *d_u = nullptr;      // staged u_local
+  double *d_vals = nullptr;   // internal values buffer for host-output calls
+  double *d_vec[4] = {nullptr, nullptr, nullptr, nullptr};  // global-length staging vectors
+  int64_t nnz = 0;
+  // BC / cohesive device lists
+  int32_t *d_bc_slot_row = nullptr;  // unused placeholder
+  int64_t *d_bc_diag = nullptr;      // diag slot per constrained dof
+  int64_t *d_bc_dof = nullptr;       // global dof per constrained entry
+  double *d_bc_val = nullptr;
+  int nbc_dofs = 0;
+  int32_t *d_coh_elems = nullptr, *d_cblk_row = nullptr, *d_cblk_ptr = nullptr, *d_cblk_src = nullptr;
+  int64_t *d_cblk_id = nullptr;
+  int32_t *d_cnode_id = nullptr, *d_cnode_ptr = nullptr, *d_cnode_src = nullptr;
+  double *d_coh_ke = nullptr, *d_coh_fe = nullptr;
+  std::vector<void *> allocs;  // everything cudaMalloc'ed by the ctx
+};

@@ -1,0 +1,509 @@
+// kernels.cu -- two-pass assembly (variant 1), stress, cohesive overlay, SpMV, pattern export.
+//
+// Pass 1: one thread per (element, local node a) computes row-block a of Ke in registers and
+//         stores it block-major [a][b][i][j] into the packed scratch, plus f_e = Ke u_e.
+// Pass 2: one warp per node row sums, for every node block of that row, the incident
+//         elements' blocks in ascending element order (deterministic, atomic-free; each CSR
+//         value is written exactly once) -- the gather-ordered equivalent of
+//         MatSetValues(ADD_VALUES) + MatAssembly (src/main.F90:157-171).
+#include "elem_math.cuh"
+#include "launch.h"
+
+namespace femx {
+
+__constant__ double c_n2inv_qua[16];
+__constant__ double c_n2inv_hex[64];
+
+template <int T>
+__device__ __forceinline__ void load_elem(const DevMesh &dm, int e, double (&X)[ET<T>::NEN][ET<T>::DIM],
+                                          int (&nd)[ET<T>::NEN]) {
+  const int32_t *c = dm.conn0 + dm.eptr[e];
+#pragma unroll
+  for (int a = 0; a < ET<T>::NEN; ++a) {
+    nd[a] = c[a];
+#pragma unroll
+    for (int d = 0; d < ET<T>::DIM; ++d) X[a][d] = dm.coords[(int64_t)nd[a] * ET<T>::DIM + d];
+  }
+}
+
+// ---------------------------------------------------------------- pass 1
+template <int T>
+__global__ void __launch_bounds__(128) elem_rows_kernel(DevMesh dm, const int32_t *__restrict__ elems, int n,
+                                                        const double *__restrict__ u, double *__restrict__ ke,
+                                                        double *__restrict__ fe) {
+  constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, D2 = DIM * DIM;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)n * NEN) return;
+  const int e = elems[tid / NEN], a = (int)(tid % NEN);
+  double *kout = ke + dm.ke_off[e] + (int64_t)a * NEN * D2;
+  if constexpr (T == FEMX_COH) {
+    // E = nu = 0 -> D = 0 (src/m_global.F90:250-252): an explicit zero block that still
+    // enters the sparsity pattern (src/main.F90:162)
+    for (int q = 0; q < NEN * D2; ++q) kout[q] = 0.0;
+    if (fe)
+      for (int i = 0; i < DIM; ++i) fe[dm.fe_off[e] + a * DIM + i] = 0.0;
+  } else {
+    double X[NEN][DIM];
+    int nd[NEN];
+    load_elem<T>(dm, e, X, nd);
+    const int m = dm.emat[e] - 1;
+    const double lam = dm.lam_mu[2 * m], mu = dm.lam_mu[2 * m + 1];
+    double acc[NEN][D2];
+    ke_row_blocks<T>(X, a, lam, mu, acc);
+#pragma unroll
+    for (int b = 0; b < NEN; ++b)
+#pragma unroll
+      for (int q = 0; q < D2; ++q) kout[b * D2 + q] = acc[b][q];
+    if (fe) {
+      double f[DIM];
+#pragma unroll
+      for (int i = 0; i < DIM; ++i) f[i] = 0.0;
+#pragma unroll
+      for (int b = 0; b < NEN; ++b)
+#pragma unroll
+        for (int j = 0; j < DIM; ++j) {
+          const double ub = u[(int64_t)nd[b] * DIM + j];
+#pragma unroll
+          for (int i = 0; i < DIM; ++i) f[i] += acc[b][i * DIM + j] * ub;
+        }
+#pragma unroll
+      for (int i = 0; i < DIM; ++i) fe[dm.fe_off[e] + a * DIM + i] = f[i];
+    }
+  }
+}
+
+// ---------------------------------------------------------------- pass 2
+template <int PD>
+__global__ void __launch_bounds__(256) gather_rows_kernel(DevMesh dm, const double *__restrict__ ke,
+                                                          const double *__restrict__ fe, double *__restrict__ vals,
+                                                          double *__restrict__ fint) {
+  constexpr int D2 = PD * PD;
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= dm.nlnds) return;
+  const int64_t b0 = dm.bptr[r];
+  const int nb = (int)(dm.bptr[r + 1] - b0);
+  const int64_t p0 = dm.n2e_ptr[r], p1 = dm.n2e_ptr[r + 1];
+  double *vrow = vals + D2 * b0;
+  for (int chunk = 0; chunk < nb; chunk += 32) {
+    const int k = chunk + lane;
+    double acc[D2];
+#pragma unroll
+    for (int q = 0; q < D2; ++q) acc[q] = 0.0;
+    for (int64_t p = p0; p < p1; ++p) {
+      const int e = dm.n2e_elem[p], a = dm.n2e_a[p];
+      const int nen = type_nen(dm.etype[e]);
+      const int my = lane < nen ? (int)dm.bpos[dm.eb_ptr[e] + a * nen + lane] : -1;
+      const double *kb = ke + dm.ke_off[e] + (int64_t)a * nen * D2;
+      for (int b = 0; b < nen; ++b) {
+        const int kk = __shfl_sync(0xffffffffu, my, b);
+        if (kk == k) {
+#pragma unroll
+          for (int q = 0; q < D2; ++q) acc[q] += kb[b * D2 + q];
+        }
+      }
+    }
+    if (k < nb) {
+#pragma unroll
+      for (int i = 0; i < PD; ++i)
+#pragma unroll
+        for (int j = 0; j < PD; ++j) vrow[(int64_t)i * PD * nb + PD * k + j] = acc[i * PD + j];
+    }
+  }
+  if (fint && lane < PD) {
+    double s = 0.0;
+    for (int64_t p = p0; p < p1; ++p) s += fe[dm.fe_off[dm.n2e_elem[p]] + dm.n2e_a[p] * PD + lane];
+    fint[(int64_t)PD * (dm.nl2g[r] - 1) + lane] = s;
+  }
+}
+
+// ---------------------------------------------------------------- unit-level element API
+template <int T>
+__global__ void element_ke_kernel(int n, const double *__restrict__ ecoords, const double *__restrict__ E_nu,
+                                  double *__restrict__ out) {
+  constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, ND = NEN * DIM;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)n * NEN) return;
+  const int64_t e = tid / NEN;
+  const int a = (int)(tid % NEN);
+  double X[NEN][DIM];
+  for (int b = 0; b < NEN; ++b)
+    for (int d = 0; d < DIM; ++d) X[b][d] = ecoords[(e * NEN + b) * DIM + d];
+  double lam, mu;
+  lame(E_nu[2 * e], E_nu[2 * e + 1], &lam, &mu);
+  double acc[NEN][DIM * DIM];
+  ke_row_blocks<T>(X, a, lam, mu, acc);
+  double *k = out + e * ND * ND;  // column-major k(row, col), src/m_local.F90:43
+#pragma unroll
+  for (int b = 0; b < NEN; ++b)
+#pragma unroll
+    for (int i = 0; i < DIM; ++i)
+#pragma unroll
+      for (int j = 0; j < DIM; ++j) k[(b * DIM + j) * ND + a * DIM + i] = acc[b][i * DIM + j];
+}
+
+// nodal extrapolation: RecoverNodalStress src/m_global.F90:488-515 with the memoised inverse of
+// N2(j,:) = N(xi_j) (NodalStressInv src/m_elems.F90:725-745) held in __constant__
+template <int T>
+__device__ __forceinline__ void nodal_from_ip(const double (&sig)[ET<T>::NIP][ET<T>::CP],
+                                              double (&sn)[ET<T>::NEN][ET<T>::CP]) {
+  constexpr int NEN = ET<T>::NEN, NIP = ET<T>::NIP, CP = ET<T>::CP;
+  if constexpr (NIP == 1) {
+#pragma unroll
+    for (int a = 0; a < NEN; ++a)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) sn[a][c] = sig[0][c];
+  } else {
+    const double *inv = T == FEMX_QUA ? c_n2inv_qua : c_n2inv_hex;
+#pragma unroll
+    for (int a = 0; a < NEN; ++a)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < NIP; ++j) s += inv[a * NIP + j] * sig[j][c];
+        sn[a][c] = s;
+      }
+  }
+}
+
+template <int T>
+__global__ void element_stress_kernel(int n, const double *__restrict__ ecoords, const double *__restrict__ edisp,
+                                      const double *__restrict__ E_nu, double *__restrict__ estress,
+                                      double *__restrict__ enodal) {
+  constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, NIP = ET<T>::NIP, CP = ET<T>::CP;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  double X[NEN][DIM], U[NEN][DIM];
+  for (int b = 0; b < NEN; ++b)
+    for (int d = 0; d < DIM; ++d) {
+      X[b][d] = ecoords[(e * NEN + b) * DIM + d];
+      U[b][d] = edisp[(e * NEN + b) * DIM + d];
+    }
+  double lam, mu;
+  lame(E_nu[2 * e], E_nu[2 * e + 1], &lam, &mu);
+  double sig[NIP][CP], sn[NEN][CP];
+  ip_stress<T>(X, U, lam, mu, sig);
+  nodal_from_ip<T>(sig, sn);
+  for (int q = 0; q < NIP; ++q)
+    for (int c = 0; c < CP; ++c) estress[(e * NIP + q) * CP + c] = sig[q][c];
+  if (enodal)
+    for (int a = 0; a < NEN; ++a)
+      for (int c = 0; c < CP; ++c) enodal[(e * NEN + a) * CP + c] = sn[a][c];
+}
+
+// ---------------------------------------------------------------- stress, mesh level
+template <int T>
+__global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int32_t *__restrict__ elems, int n,
+                                                          const double *__restrict__ uu, double *__restrict__ sn_out) {
+  constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, NIP = ET<T>::NIP, CP = ET<T>::CP;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const int e = elems[idx];
+  double *out = sn_out + (int64_t)dm.eptr[e] * CP;
+  if constexpr (T == FEMX_COH) {
+    for (int q = 0; q < NEN * CP; ++q) out[q] = 0.0;  // D5: contribution defined as zero
+  } else {
+    double X[NEN][DIM], U[NEN][DIM];
+    int nd[NEN];
+    load_elem<T>(dm, e, X, nd);
+#pragma unroll
+    for (int a = 0; a < NEN; ++a)
+#pragma unroll
+      for (int d = 0; d < DIM; ++d) U[a][d] = uu[(int64_t)nd[a] * DIM + d];
+    const int m = dm.emat[e] - 1;
+    double sig[NIP][CP], sn[NEN][CP];
+    ip_stress<T>(X, U, dm.lam_mu[2 * m], dm.lam_mu[2 * m + 1], sig);
+    nodal_from_ip<T>(sig, sn);
+#pragma unroll
+    for (int a = 0; a < NEN; ++a)
+#pragma unroll
+      for (int c = 0; c < CP; ++c) out[a * CP + c] = sn[a][c];
+  }
+}
+
+// nodal sum in ascending element order, then the average (src/main.F90:258-279)
+__global__ void node_stress_gather_kernel(DevMesh dm, const double *__restrict__ sn, double *__restrict__ out,
+                                          int col_major) {
+  const int cp = dm.cp;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)dm.nlnds * cp) return;
+  const int64_t r = tid / cp;
+  const int c = (int)(tid % cp);
+  double s = 0.0;
+  for (int64_t p = dm.n2e_ptr[r]; p < dm.n2e_ptr[r + 1]; ++p)
+    s += sn[((int64_t)dm.eptr[dm.n2e_elem[p]] + dm.n2e_a[p]) * cp + c];
+  s = s / (double)dm.node_count[r];
+  out[col_major ? (int64_t)c * dm.nlnds + r : tid] = s;
+}
+
+// ---------------------------------------------------------------- pattern / BC / SpMV
+template <int PD>
+__global__ void colidx_kernel(DevMesh dm, int32_t *__restrict__ colidx) {
+  const int64_t blk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nblk = dm.bptr[dm.nlnds];
+  if (blk >= nblk) return;
+  // find the row by bisection over bptr
+  int lo = 0, hi = dm.nlnds;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (dm.bptr[mid] <= blk) lo = mid; else hi = mid;
+  }
+  const int64_t b0 = dm.bptr[lo];
+  const int nb = (int)(dm.bptr[lo + 1] - b0), k = (int)(blk - b0);
+  const int gcol = PD * (dm.nl2g[dm.bcol[blk]] - 1);
+  for (int i = 0; i < PD; ++i)
+    for (int j = 0; j < PD; ++j) colidx[PD * PD * b0 + (int64_t)i * PD * nb + PD * k + j] = gcol + j;
+}
+
+__global__ void apply_kbc_kernel(int n, const int64_t *__restrict__ diag, double *__restrict__ vals) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) vals[diag[i]] = kPenalty;  // MatSetValue(j, j, 1e30, INSERT), src/m_global.F90:296
+}
+
+__global__ void bc_force_kernel(int n, const int64_t *__restrict__ dof, const double *__restrict__ val,
+                                double scale, double *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // vvec = PENALTY_PARAM * bcval * dt / t, INSERT (src/m_global.F90:451)
+  if (i < n) out[dof[i]] = kPenalty * val[i] * scale;
+}
+
+// y[g] = sum_k J[row, k] * x[col] - sub[g] over the local node rows (one warp per node)
+template <int PD>
+__global__ void __launch_bounds__(256) spmv_sub_kernel(DevMesh dm, const double *__restrict__ vals,
+                                                       const double *__restrict__ x, const double *__restrict__ sub,
+                                                       double *__restrict__ y) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= dm.nlnds) return;
+  const int64_t b0 = dm.bptr[r];
+  const int nb = (int)(dm.bptr[r + 1] - b0);
+  double acc[PD];
+#pragma unroll
+  for (int i = 0; i < PD; ++i) acc[i] = 0.0;
+  for (int k = lane; k < nb; k += 32) {
+    const int64_t gc = (int64_t)PD * (dm.nl2g[dm.bcol[b0 + k]] - 1);
+#pragma unroll
+    for (int j = 0; j < PD; ++j) {
+      const double xv = x[gc + j];
+#pragma unroll
+      for (int i = 0; i < PD; ++i) acc[i] += vals[PD * PD * b0 + (int64_t)i * PD * nb + PD * k + j] * xv;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < PD; ++i)
+    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+  if (lane == 0) {
+    const int64_t g = (int64_t)PD * (dm.nl2g[r] - 1);
+#pragma unroll
+    for (int i = 0; i < PD; ++i) y[g + i] = acc[i] - sub[g + i];
+  }
+}
+
+// ---------------------------------------------------------------- cohesive
+__global__ void cohesive_mesh_kernel(DevMesh dm, const int32_t *__restrict__ coh_elems, int n,
+                                     const double *__restrict__ u, double dt, int quirks,
+                                     double *__restrict__ force, double *__restrict__ stiff) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= n) return;
+  const int e = coh_elems[ci];
+  const int32_t *c = dm.conn0 + dm.eptr[e];
+  double X[4][2], U[4][2];
+  for (int a = 0; a < 4; ++a) {
+    // D3: the reference reads the rank's local nodes 1..4 (src/m_elems.F90:700-702)
+    const int un = (quirks & FEMX_Q_GATHER_LOCAL14) ? a : c[a];
+    for (int d = 0; d < 2; ++d) {
+      X[a][d] = dm.coords[(int64_t)c[a] * 2 + d];
+      U[a][d] = u[(int64_t)un * 2 + d];
+    }
+  }
+  cohesive_element(X, U, dm.cohprops + 6 * (dm.enlmat[e] - 1), dt, quirks, force ? force + 8 * ci : nullptr,
+                   stiff ? stiff + 64 * ci : nullptr);
+}
+
+__global__ void cohesive_unit_kernel(int n, const double *__restrict__ ecoords, const int32_t *__restrict__ nodes,
+                                     const double *__restrict__ u, const double *__restrict__ props, double dt,
+                                     int quirks, double *__restrict__ force, double *__restrict__ stiff) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ci >= n) return;
+  double X[4][2], U[4][2];
+  for (int a = 0; a < 4; ++a) {
+    const int un = (quirks & FEMX_Q_GATHER_LOCAL14) ? a : nodes[4 * ci + a] - 1;
+    for (int d = 0; d < 2; ++d) {
+      X[a][d] = ecoords[(ci * 4 + a) * 2 + d];
+      U[a][d] = u[(int64_t)un * 2 + d];
+    }
+  }
+  cohesive_element(X, U, props + 6 * ci, dt, quirks, force + 8 * ci, stiff + 64 * ci);
+}
+
+// J[slot] = K[slot] + sum of cohesive tangents in ascending element order, per touched block
+__global__ void jacobian_overlay_kernel(DevMesh dm, int n, const int64_t *__restrict__ blk_id,
+                                        const int32_t *__restrict__ blk_row, const int32_t *__restrict__ ptr,
+                                        const int32_t *__restrict__ src, const double *__restrict__ coh_ke,
+                                        const double *__restrict__ kvals, double *__restrict__ jvals) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int r = blk_row[t];
+  const int64_t b0 = dm.bptr[r];
+  const int nb = (int)(dm.bptr[r + 1] - b0), k = (int)(blk_id[t] - b0);
+  for (int i = 0; i < 2; ++i)
+    for (int j = 0; j < 2; ++j) {
+      const int64_t slot = 4 * b0 + (int64_t)i * 2 * nb + 2 * k + j;
+      double s = kvals[slot];
+      for (int q = ptr[t]; q < ptr[t + 1]; ++q) {
+        const int ci = src[q] >> 8, a = (src[q] >> 4) & 15, b = src[q] & 15;
+        s += coh_ke[64 * ci + (a * 2 + i) * 8 + b * 2 + j];
+      }
+      jvals[slot] = s;
+    }
+}
+
+// out[g] += sum of cohesive nodal forces in ascending element order (src/m_global.F90:203-205)
+__global__ void cohesive_force_gather_kernel(DevMesh dm, int n, const int32_t *__restrict__ node_id,
+                                             const int32_t *__restrict__ ptr, const int32_t *__restrict__ src,
+                                             const double *__restrict__ coh_fe, double *__restrict__ out) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int64_t g = 2 * (int64_t)(dm.nl2g[node_id[t]] - 1);
+  for (int d = 0; d < 2; ++d) {
+    double s = out[g + d];
+    for (int q = ptr[t]; q < ptr[t + 1]; ++q) s += coh_fe[8 * (src[q] >> 4) + (src[q] & 15) * 2 + d];
+    out[g + d] = s;
+  }
+}
+
+// ================================================================= launchers
+static inline int nblocks(int64_t n, int bs) { return (int)((n + bs - 1) / bs); }
+
+void set_n2inv(const double *qua16, const double *hex64) {
+  cudaMemcpyToSymbol(c_n2inv_qua, qua16, sizeof(double) * 16);
+  cudaMemcpyToSymbol(c_n2inv_hex, hex64, sizeof(double) * 64);
+}
+
+int launch_elem_rows(femx_ctx *c, const double *d_u, double *d_ke, double *d_fe) {
+  int launches = 0;
+  for (auto &b : c->buckets) {
+    if (!b.n) continue;
+    const int64_t nt = (int64_t)b.n * type_nen(b.type);
+    const int bs = 128, g = nblocks(nt, bs);
+    switch (b.type) {
+      case FEMX_TRI: elem_rows_kernel<FEMX_TRI><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_u, d_ke, d_fe); break;
+      case FEMX_QUA: elem_rows_kernel<FEMX_QUA><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_u, d_ke, d_fe); break;
+      case FEMX_TET: elem_rows_kernel<FEMX_TET><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_u, d_ke, d_fe); break;
+      case FEMX_HEX: elem_rows_kernel<FEMX_HEX><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_u, d_ke, d_fe); break;
+      case FEMX_COH: elem_rows_kernel<FEMX_COH><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_u, d_ke, d_fe); break;
+    }
+    ++launches;
+  }
+  return launches;
+}
+
+int launch_gather_rows(femx_ctx *c, const double *d_ke, const double *d_fe, double *d_vals, double *d_fint) {
+  const int bs = 256, g = nblocks((int64_t)c->nlnds * 32, bs);
+  if (c->pdim == 2) gather_rows_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_ke, d_fe, d_vals, d_fint);
+  else gather_rows_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_ke, d_fe, d_vals, d_fint);
+  return 1;
+}
+
+int launch_element_ke(femx_ctx *c, int type, int n, const double *d_x, const double *d_enu, double *d_out) {
+  const int bs = 128, g = nblocks((int64_t)n * type_nen(type), bs);
+  switch (type) {
+    case FEMX_TRI: element_ke_kernel<FEMX_TRI><<<g, bs, 0, c->stream>>>(n, d_x, d_enu, d_out); break;
+    case FEMX_QUA: element_ke_kernel<FEMX_QUA><<<g, bs, 0, c->stream>>>(n, d_x, d_enu, d_out); break;
+    case FEMX_TET: element_ke_kernel<FEMX_TET><<<g, bs, 0, c->stream>>>(n, d_x, d_enu, d_out); break;
+    case FEMX_HEX: element_ke_kernel<FEMX_HEX><<<g, bs, 0, c->stream>>>(n, d_x, d_enu, d_out); break;
+    default: return 0;
+  }
+  return 1;
+}
+
+int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const double *d_u, const double *d_enu,
+                          double *d_sig, double *d_sn) {
+  const int bs = 128, g = nblocks(n, bs);
+  switch (type) {
+    case FEMX_TRI: element_stress_kernel<FEMX_TRI><<<g, bs, 0, c->stream>>>(n, d_x, d_u, d_enu, d_sig, d_sn); break;
+    case FEMX_QUA: element_stress_kernel<FEMX_QUA><<<g, bs, 0, c->stream>>>(n, d_x, d_u, d_enu, d_sig, d_sn); break;
+    case FEMX_TET: element_stress_kernel<FEMX_TET><<<g, bs, 0, c->stream>>>(n, d_x, d_u, d_enu, d_sig, d_sn); break;
+    case FEMX_HEX: element_stress_kernel<FEMX_HEX><<<g, bs, 0, c->stream>>>(n, d_x, d_u, d_enu, d_sig, d_sn); break;
+    default: return 0;
+  }
+  return 1;
+}
+
+int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major) {
+  int launches = 0;
+  for (auto &b : c->buckets) {
+    if (!b.n) continue;
+    const int bs = 128, g = nblocks(b.n, bs);
+    switch (b.type) {
+      case FEMX_TRI: mesh_stress_kernel<FEMX_TRI><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_QUA: mesh_stress_kernel<FEMX_QUA><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_TET: mesh_stress_kernel<FEMX_TET><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_HEX: mesh_stress_kernel<FEMX_HEX><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_COH: mesh_stress_kernel<FEMX_COH><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+    }
+    ++launches;
+  }
+  const int bs = 256;
+  node_stress_gather_kernel<<<nblocks((int64_t)c->nlnds * c->dm.cp, bs), bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major);
+  return launches + 1;
+}
+
+int launch_colidx(femx_ctx *c, int32_t *d_colidx) {
+  const int bs = 256, g = nblocks(c->plan.nblk, bs);
+  if (!g) return 0;
+  if (c->pdim == 2) colidx_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
+  else colidx_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
+  return 1;
+}
+
+int launch_apply_kbc(femx_ctx *c, double *d_vals) {
+  if (!c->nbc_dofs) return 0;
+  apply_kbc_kernel<<<nblocks(c->nbc_dofs, 128), 128, 0, c->stream>>>(c->nbc_dofs, c->d_bc_diag, d_vals);
+  return 1;
+}
+
+int launch_bc_force(femx_ctx *c, double scale, double *d_out) {
+  if (!c->nbc_dofs) return 0;
+  bc_force_kernel<<<nblocks(c->nbc_dofs, 128), 128, 0, c->stream>>>(c->nbc_dofs, c->d_bc_dof, c->d_bc_val, scale, d_out);
+  return 1;
+}
+
+int launch_spmv_sub(femx_ctx *c, const double *d_vals, const double *d_x, const double *d_sub, double *d_y) {
+  const int bs = 256, g = nblocks((int64_t)c->nlnds * 32, bs);
+  if (c->pdim == 2) spmv_sub_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y);
+  else spmv_sub_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y);
+  return 1;
+}
+
+int launch_cohesive_mesh(femx_ctx *c, const double *d_u, double dt, double *d_force, double *d_stiff) {
+  const int n = (int)c->plan.coh_elems.size();
+  if (!n) return 0;
+  cohesive_mesh_kernel<<<nblocks(n, 64), 64, 0, c->stream>>>(c->dm, c->d_coh_elems, n, d_u, dt, c->opts.quirks, d_force, d_stiff);
+  return 1;
+}
+
+int launch_cohesive_unit(femx_ctx *c, int n, const double *d_x, const int32_t *d_nodes, const double *d_u,
+                         const double *d_props, double dt, double *d_force, double *d_stiff) {
+  cohesive_unit_kernel<<<nblocks(n, 64), 64, 0, c->stream>>>(n, d_x, d_nodes, d_u, d_props, dt, c->opts.quirks, d_force, d_stiff);
+  return 1;
+}
+
+int launch_jacobian_overlay(femx_ctx *c, const double *d_kvals, double *d_jvals) {
+  const int n = (int)c->plan.cblk_id.size();
+  if (!n) return 0;
+  jacobian_overlay_kernel<<<nblocks(n, 128), 128, 0, c->stream>>>(c->dm, n, c->d_cblk_id, c->d_cblk_row, c->d_cblk_ptr,
+                                                                 c->d_cblk_src, c->d_coh_ke, d_kvals, d_jvals);
+  return 1;
+}
+
+int launch_cohesive_force_gather(femx_ctx *c, double *d_out) {
+  const int n = (int)c->plan.cnode_id.size();
+  if (!n) return 0;
+  cohesive_force_gather_kernel<<<nblocks(n, 128), 128, 0, c->stream>>>(c->dm, n, c->d_cnode_id, c->d_cnode_ptr,
+                                                                      c->d_cnode_src, c->d_coh_fe, d_out);
+  return 1;
+}
+
+}  // namespace femx

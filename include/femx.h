@@ -1,0 +1,166 @@
+/*
+ * femx.h -- C ABI of the B200-native defmod assembly hot path.
+ *
+ * The reference (srinath-chakravarthy/FEM, Fortran 90 + PETSc) has no FFI; the boundary
+ * this library sits under is the module-procedure surface that `program main` and
+ * PETSc SNES call.  Every entry point below names the reference
+ * procedure / loop it replaces (paths relative to the reference tree).  A Fortran
+ * host binds these with ISO_C_BINDING (fortran/femx_mod.F90).
+ *
+ * Conventions kept from the reference, never re-based silently:
+ *   - element type codes = getElTypeNo, src/m_elems.F90:25: 1 tri 2 qua 3 tet 4 hex 5 coh
+ *     (hex has 8 nodes; the reference's table says 6 -- defect D1, src/m_elems.F90:27)
+ *   - element node ids are 1-based LOCAL ids (src/main.F90:68-73), local ids ascend with
+ *     the global id (src/main.F90:57-63), nl2g is 1-based global (src/main.F90:76-81)
+ *   - global dofs / CSR columns are 0-based: pdim*(g-1)+d (src/main.F90:93-94)
+ *   - BC flag 0 = constrained (BC_PRESENT, src/m_global.F90:14)
+ *   - element matrices are column-major k(:,:) (src/m_local.F90:43)
+ *   - all reals are fp64, all indices 32-bit int except nnz / rowptr (int64)
+ *
+ * Every function returns 0 on success or a FEMX_ERR_* code; femx_last_error() gives the
+ * text.  No exceptions, no exit(), no CPU fallback: without a CUDA device femx_create
+ * fails with FEMX_ERR_CUDA.  One ctx per rank / per GPU; a ctx is not re-entrant.
+ */
+#ifndef FEMX_H
+#define FEMX_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct femx_ctx femx_ctx;
+
+enum {
+  FEMX_OK = 0,
+  FEMX_ERR_ARG = 1,      /* bad argument / call order                     */
+  FEMX_ERR_CUDA = 2,     /* CUDA runtime failure (latched in the ctx)      */
+  FEMX_ERR_NCCL = 3,     /* NCCL failure                                   */
+  FEMX_ERR_ALLOC = 4,
+  FEMX_ERR_UNSUPPORTED = 5
+};
+
+enum { FEMX_TRI = 1, FEMX_QUA = 2, FEMX_TET = 3, FEMX_HEX = 4, FEMX_COH = 5 };
+
+/* where a caller buffer lives */
+enum { FEMX_HOST = 0, FEMX_DEVICE = 1 };
+
+/* coords layout: (node, dim) row-major, or Fortran coords(nlnds, pdim) column-major
+ * (src/m_global.F90:22) */
+enum { FEMX_ROW_MAJOR = 0, FEMX_COL_MAJOR = 1 };
+
+/* quirk switches: a set bit reproduces the reference as written, a clear
+ * bit the corrected Abaqus-UEL form the element was transplanted from. */
+enum {
+  FEMX_Q_GATHER_LOCAL14 = 1,     /* D3 getCohRels reads local nodes 1..4, src/m_elems.F90:700-702 */
+  FEMX_Q_TANGENT_PRECEDENCE = 2, /* D4 lost parentheses, src/m_global.F90:829-831                 */
+  FEMX_Q_FORCE_LAST_IP = 4,      /* D8 force assigned per ip, src/m_global.F90:669                */
+  FEMX_Q_COH_COUNTS_NODE = 8,    /* D5 coh bumps count_node, src/main.F90:263                     */
+  FEMX_Q_REFERENCE = 15,
+  FEMX_Q_UEL = 0
+};
+
+/* assembly variants: 0 = best available for the mesh, 1 = two-pass
+ * (element kernel -> packed Ke scratch -> ordered gather), 2 = fused tile kernel */
+typedef struct {
+  int quirks;            /* FEMX_Q_* bits                                   */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 2 fused                     */
+  int reserved[6];
+} femx_opts;
+
+/* ---- lifetime ------------------------------------------------------------------- */
+int femx_create(femx_ctx **ctx, int device, const femx_opts *opts /* NULL = defaults */);
+int femx_destroy(femx_ctx *ctx);
+const char *femx_last_error(const femx_ctx *ctx /* NULL = last create failure */);
+/* pinned host memory for buffers that cross the ABI every step */
+int femx_host_alloc(void **ptr, int64_t bytes);
+int femx_host_free(void *ptr);
+/* raw device memory for callers without a CUDA runtime of their own (tests, Fortran) */
+int femx_device_alloc(femx_ctx *ctx, void **ptr, int64_t bytes);
+int femx_device_free(femx_ctx *ctx, void *ptr);
+int femx_memcpy(femx_ctx *ctx, void *dst, const void *src, int64_t bytes, int dst_where, int src_where);
+int femx_synchronize(femx_ctx *ctx);
+
+/* ---- state the path reads (module globals of src/m_global.F90:17-87) ------------- */
+/* local_elements(:) as eptr/eind (exactly what PartitionBroadcast builds at
+ * src/m_io.F90:128-135, but 1-based local ids), coords, nl2g, nnds */
+int femx_set_mesh(femx_ctx *ctx, int pdim, int nels, const int *etype, const int *eptr,
+                  const int *eind, const int *emat, const int *enlmat, int nlnds,
+                  const double *coords, int coords_layout, const int *nl2g, int nnds);
+/* mat(:,1:2) = (E, nu) row-major [nmts*2] (src/m_global.F90:254-255);
+ * cohmats(:)%props [ncoh*6] (src/m_seplaw.F90:19-24) */
+int femx_set_materials(femx_ctx *ctx, int nmts, const double *E_nu, int ncoh, const double *cohprops);
+/* bcnode(nbcs, 1+pdim) row-major: global node, flags; bcval(nbcs, pdim) (src/m_global.F90:33-34) */
+int femx_set_bcs(femx_ctx *ctx, int nbcs, const int *bcnode, const double *bcval);
+
+/* ---- one-time integer pass (replaces MatCreateAIJ preallocation guess + the sorted
+ *      insert of MatSetValues, src/main.F90:153-171) ------------------------------ */
+int femx_build_plan(femx_ctx *ctx);
+/* nrows = pdim*nnds (global rows; rows of nodes this rank does not touch are empty) */
+int femx_pattern_size(femx_ctx *ctx, int64_t *nrows, int64_t *nnz);
+/* CSR of the assembled AIJ: columns ascending, explicit zeros kept (what MatView shows,
+ * examples/tmp.txt:15-33).  Either pointer may be NULL. */
+int femx_get_pattern(femx_ctx *ctx, int64_t *rowptr, int32_t *colidx, int where);
+/* element -> nonzero-slot map at node-block granularity: for element e, local nodes a, b
+ * slot(e,a,i,b,j) = rowstart(row(a,i)) + pdim*blockpos[e][a*nen+b] + j.
+ * blockpos is [sum nen^2] uint16, offsets [nels+1] (int64). */
+int femx_get_slot_map(femx_ctx *ctx, int64_t *offsets, uint16_t *blockpos);
+
+/* ---- element-level entry points (unit parity; FormElKE src/m_local.F90:21,
+ *      CalcElStress :93, applyTract_1 src/m_global.F90:622, applyStiff_1 :762) ------ */
+/* n elements of one type; ecoords [n][nen][dim]; ke [n][ndof*ndof] column-major */
+int femx_element_ke(femx_ctx *ctx, int type, int n, const double *ecoords, const double *E_nu /*[n*2]*/,
+                    double *ke);
+/* estress [n][nip][cp]; enodal [n][nen][cp] (RecoverNodalStress src/m_global.F90:488) */
+int femx_element_stress(femx_ctx *ctx, int type, int n, const double *ecoords, const double *edisp,
+                        const double *E_nu, double *estress, double *enodal);
+/* cohesive: nodes [n][4] 1-based local ids into u_local; force [n][8]; stiff [n][8*8] row-major
+ * (row = (node1,dof1), col = (node2,dof2), exactly result(:,:) of applyStiff_1) */
+int femx_element_cohesive(femx_ctx *ctx, int n, const double *ecoords, const int *nodes,
+                          const double *u_local, int nu_local, const double *props /*[n*6]*/,
+                          double dt, double *force, double *stiff);
+
+/* ---- global entry points --------------------------------------------------------- */
+/* `do i=1,nels: FormLocalK; MatSetValues(ADD)` + MatAssembly, src/main.F90:157-168.
+ * vals[nnz] in femx_get_pattern order.  No BC applied (see femx_apply_kbc). */
+int femx_assemble_K(femx_ctx *ctx, double *vals, int where);
+/* headline path: K values and the elastic internal force f = sum_e Ke u_e in one pass.
+ * u_local [pdim*nlnds] (what GetVec_U yields, src/m_global.F90:549); fint [pdim*nnds] global */
+int femx_assemble_K_fint(femx_ctx *ctx, const double *u_local, double *vals, double *fint, int where);
+/* ApplyKBC / UpdateKMatBcs, src/m_global.F90:264-299: diag <- 1e30 (INSERT) */
+int femx_apply_kbc(femx_ctx *ctx, double *vals, int where);
+/* CalcJacobian, src/m_global.F90:98-158: J = K + sum coh tangents, BC diagonal inserted.
+ * kvals = values from femx_assemble_K (+apply_kbc), same memory space as jvals */
+int femx_jacobian(femx_ctx *ctx, const double *kvals, const double *u_total_local, double dt,
+                  double *jvals, int where);
+/* CalcResidual, src/m_global.F90:161-235 (single rank: vectors are global [pdim*nnds]):
+ * r = J*du - (f_ext + sum f_coh(u_total), BC rows <- 1e30*bcval*dt/t_total) */
+int femx_residual(femx_ctx *ctx, const double *jvals, const double *u_total_local, const double *du,
+                  const double *f_ext, double dt, double t_total, double *r, int where);
+/* the bracket alone, for multi-rank hosts that keep MatMultAdd in PETSc */
+int femx_residual_forces(femx_ctx *ctx, const double *u_total_local, const double *f_ext, double dt,
+                         double t_total, double *out, int where);
+/* RecoverStress + RecoverNodalStress + nodal average, src/main.F90:253-279.
+ * stress_node [nlnds][cp] row-major (or column-major stress_node(nlnds,cpdim) by layout) */
+int femx_stress(femx_ctx *ctx, const double *uu_local, double *stress_node, int layout, int where);
+
+/* ---- multi-GPU (one ctx per rank) ----------------------------------- */
+/* rows [row_start,row_end) of the global matrix are owned by this rank: the PETSC_DECIDE
+ * split of MatCreateAIJ, src/main.F90:154.  Must precede femx_build_plan. */
+int femx_set_ownership(femx_ctx *ctx, int nranks, int rank, int64_t row_start, int64_t row_end);
+int femx_nccl_unique_id(char id[128]);
+int femx_comm_init(femx_ctx *ctx, const char id[128]);
+
+/* ---- instrumentation -------------------------------------------------------------- */
+/* kernels launched by this ctx since creation (bench.py "gpu_launches") */
+int64_t femx_launch_count(const femx_ctx *ctx);
+/* device time of the last assemble / stress / jacobian call's kernels, CUDA events on the ctx
+ * stream, ms (0 if none) */
+double femx_last_kernel_ms(const femx_ctx *ctx);
+int femx_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
