@@ -1,0 +1,281 @@
+// femx_api.cu -- the C ABI of include/femx.h.  Plain pointers and sizes in, status codes out.
+#include "api_util.h"
+
+static std::string g_create_err;
+
+
+extern "C" {
+
+int femx_version(void) { return 100; }
+
+const char *femx_last_error(const femx_ctx *c) { return c ? c->err.c_str() : g_create_err.c_str(); }
+
+int femx_create(femx_ctx **out, int device, const femx_opts *opts) {
+  if (!out) return FEMX_ERR_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_err = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                   " (femx has no CPU fallback)";
+    return FEMX_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) { g_create_err = "device index out of range"; return FEMX_ERR_ARG; }
+  if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return FEMX_ERR_CUDA; }
+  femx_ctx *c = new femx_ctx;
+  c->device = device;
+  if (opts) c->opts = *opts;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+    g_create_err = "stream/event creation failed";
+    delete c;
+    return FEMX_ERR_CUDA;
+  }
+  double q[16], h[64];
+  nodal_stress_tables(q, h);
+  set_n2inv(q, h);
+  *out = c;
+  return FEMX_OK;
+}
+
+int femx_destroy(femx_ctx *c) {
+  if (!c) return FEMX_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (void *p : c->allocs) cudaFree(p);
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return FEMX_OK;
+}
+
+int femx_host_alloc(void **ptr, int64_t bytes) {
+  return cudaMallocHost(ptr, (size_t)(bytes > 0 ? bytes : 1)) == cudaSuccess ? FEMX_OK : FEMX_ERR_ALLOC;
+}
+int femx_host_free(void *ptr) { return cudaFreeHost(ptr) == cudaSuccess ? FEMX_OK : FEMX_ERR_CUDA; }
+
+int femx_device_alloc(femx_ctx *c, void **ptr, int64_t bytes) {
+  if (!c || !ptr) return FEMX_ERR_ARG;
+  char *p = nullptr;
+  int rc = dev_alloc(c, &p, bytes);
+  *ptr = p;
+  return rc;
+}
+int femx_device_free(femx_ctx *c, void *ptr) {
+  if (!c) return FEMX_ERR_ARG;
+  dev_release(c, ptr);
+  return FEMX_OK;
+}
+int femx_memcpy(femx_ctx *c, void *dst, const void *src, int64_t bytes, int dw, int sw) {
+  if (!c) return FEMX_ERR_ARG;
+  cudaMemcpyKind k = dw == FEMX_DEVICE ? (sw == FEMX_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice)
+                                       : (sw == FEMX_DEVICE ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost);
+  CK(cudaMemcpyAsync(dst, src, (size_t)bytes, k, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+int femx_synchronize(femx_ctx *c) {
+  if (!c) return FEMX_ERR_ARG;
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+int64_t femx_launch_count(const femx_ctx *c) { return c ? c->launches : 0; }
+double femx_last_kernel_ms(const femx_ctx *c) { return c ? c->last_ms : 0.0; }
+
+// --------------------------------------------------------------------------- state
+int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *eptr, const int *eind,
+                  const int *emat, const int *enlmat, int nlnds, const double *coords, int layout,
+                  const int *nl2g, int nnds) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(pdim == 2 || pdim == 3, "pdim must be 2 or 3");
+  ARG(nels >= 0 && nlnds >= 0 && nnds >= nlnds, "bad sizes");
+  ARG(etype && eptr && eind && emat && enlmat && coords && nl2g, "null mesh array");
+  c->pdim = pdim; c->nels = nels; c->nlnds = nlnds; c->nnds = nnds;
+  c->etype.assign(etype, etype + nels);
+  c->eptr.assign(eptr, eptr + nels + 1);
+  c->eind.assign(eind, eind + eptr[nels]);
+  c->emat.assign(emat, emat + nels);
+  c->enlmat.assign(enlmat, enlmat + nels);
+  c->nl2g.assign(nl2g, nl2g + nlnds);
+  for (int i = 0; i < nlnds; ++i) {
+    ARG(nl2g[i] >= 1 && nl2g[i] <= nnds, "nl2g out of range (1-based global ids)");
+    ARG(i == 0 || nl2g[i] > nl2g[i - 1], "nl2g must ascend (src/main.F90:57-63 numbering)");
+  }
+  c->coords.resize((size_t)nlnds * pdim);
+  for (int i = 0; i < nlnds; ++i)
+    for (int d = 0; d < pdim; ++d)
+      c->coords[(size_t)i * pdim + d] = layout == FEMX_COL_MAJOR ? coords[(size_t)d * nlnds + i] : coords[(size_t)i * pdim + d];
+  c->has_mesh = true;
+  c->has_plan = false;
+  return FEMX_OK;
+}
+
+int femx_set_materials(femx_ctx *c, int nmts, const double *E_nu, int ncoh, const double *cohprops) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(nmts >= 0 && ncoh >= 0, "bad counts");
+  c->nmts = nmts; c->ncoh = ncoh;
+  c->E_nu.assign(E_nu, E_nu + 2 * (size_t)nmts);
+  c->cohprops.assign(cohprops, cohprops + 6 * (size_t)ncoh);
+  if (c->has_plan) {  // refresh device copies
+    std::vector<double> lm(2 * (size_t)nmts);
+    for (int m = 0; m < nmts; ++m) lame(E_nu[2 * m], E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
+    dev_release(c, c->dm.lam_mu); dev_release(c, c->dm.cohprops);
+    int rc;
+    if ((rc = upload(c, &c->dm.lam_mu, lm))) return rc;
+    if ((rc = upload(c, &c->dm.cohprops, c->cohprops))) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  return FEMX_OK;
+}
+
+static int prepare_bcs(femx_ctx *c) {
+  dev_release(c, c->d_bc_diag); dev_release(c, c->d_bc_dof); dev_release(c, c->d_bc_val);
+  c->d_bc_diag = nullptr; c->d_bc_dof = nullptr; c->d_bc_val = nullptr;
+  std::vector<int64_t> diag, dof;
+  std::vector<double> val;
+  const int pd = c->pdim;
+  for (int i = 0; i < c->nbcs; ++i) {
+    const int node = c->bcnode[(size_t)i * (1 + pd)];
+    auto it = std::lower_bound(c->nl2g.begin(), c->nl2g.end(), node);
+    if (it == c->nl2g.end() || *it != node) continue;  // node not on this rank
+    const int r = (int)(it - c->nl2g.begin());
+    const int64_t b0 = c->plan.bptr[r];
+    const int nb = (int)(c->plan.bptr[r + 1] - b0);
+    for (int d = 0; d < pd; ++d)
+      if (c->bcnode[(size_t)i * (1 + pd) + 1 + d] == 0) {  // BC_PRESENT
+        diag.push_back((int64_t)pd * pd * b0 + (int64_t)d * pd * nb + pd * c->plan.bdiag[r] + d);
+        dof.push_back((int64_t)pd * node - pd + d);
+        val.push_back(c->bcval[(size_t)i * pd + d]);
+      }
+  }
+  c->nbc_dofs = (int)diag.size();
+  int rc;
+  if ((rc = upload(c, &c->d_bc_diag, diag))) return rc;
+  if ((rc = upload(c, &c->d_bc_dof, dof))) return rc;
+  if ((rc = upload(c, &c->d_bc_val, val))) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+
+int femx_set_bcs(femx_ctx *c, int nbcs, const int *bcnode, const double *bcval) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_mesh, "femx_set_mesh first");
+  ARG(nbcs >= 0, "bad nbcs");
+  c->nbcs = nbcs;
+  c->bcnode.assign(bcnode, bcnode + (size_t)nbcs * (1 + c->pdim));
+  c->bcval.assign(bcval, bcval + (size_t)nbcs * c->pdim);
+  return c->has_plan ? prepare_bcs(c) : FEMX_OK;
+}
+
+int femx_set_ownership(femx_ctx *c, int nranks, int rank, int64_t row_start, int64_t row_end) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(nranks == 1 && rank == 0, "multi-rank ownership is not wired up in this build");
+  (void)row_start; (void)row_end;
+  return FEMX_OK;
+}
+int femx_nccl_unique_id(char id[128]) { memset(id, 0, 128); return FEMX_ERR_UNSUPPORTED; }
+int femx_comm_init(femx_ctx *c, const char id[128]) {
+  (void)id;
+  if (c) c->err = "NCCL exchange is not wired up in this build";
+  return FEMX_ERR_UNSUPPORTED;
+}
+
+// --------------------------------------------------------------------------- plan
+int femx_build_plan(femx_ctx *c) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_mesh, "femx_set_mesh first");
+  CK(cudaSetDevice(c->device));
+  int rc = build_plan(c->pdim, c->nels, c->etype.data(), c->eptr.data(), c->eind.data(), c->enlmat.data(),
+                      c->nlnds, c->nnds, &c->plan, &c->err);
+  if (rc) return rc;
+  for (int e = 0; e < c->nels; ++e) {
+    if (c->etype[e] != FEMX_COH) ARG(c->emat[e] >= 1 && c->emat[e] <= c->nmts, "element material id out of range (femx_set_materials first)");
+    if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
+  }
+  femx::Plan &P = c->plan;
+  femx::DevMesh &dm = c->dm;
+  dm.pdim = c->pdim; dm.nels = c->nels; dm.nlnds = c->nlnds; dm.nnds = c->nnds; dm.cp = c->pdim == 2 ? 3 : 6;
+  c->nnz = (int64_t)c->pdim * c->pdim * P.nblk;
+#define UP(dst, src) if ((rc = upload(c, &dst, src))) return rc
+  UP(dm.etype, c->etype); UP(dm.eptr, c->eptr); UP(dm.conn0, P.conn0); UP(dm.emat, c->emat); UP(dm.enlmat, c->enlmat);
+  UP(dm.nl2g, c->nl2g); UP(dm.coords, c->coords); UP(dm.cohprops, c->cohprops);
+  std::vector<double> lm(2 * (size_t)c->nmts);
+  for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
+  UP(dm.lam_mu, lm);
+  UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
+  UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
+  // stress multiplicity (count_node, src/main.F90:263); mesh constant, computed once
+  std::vector<int32_t> cnt(c->nlnds, 0);
+  for (int r = 0; r < c->nlnds; ++r)
+    for (int64_t p = P.n2e_ptr[r]; p < P.n2e_ptr[r + 1]; ++p)
+      if (c->etype[P.n2e_elem[p]] != FEMX_COH || (c->opts.quirks & FEMX_Q_COH_COUNTS_NODE)) cnt[r]++;
+  UP(dm.node_count, cnt);
+  // type buckets
+  c->buckets.clear();
+  for (int t = FEMX_TRI; t <= FEMX_COH; ++t) {
+    femx::Bucket b;
+    b.type = t;
+    for (int e = 0; e < c->nels; ++e)
+      if (c->etype[e] == t) b.h_elem.push_back(e);
+    b.n = (int)b.h_elem.size();
+    if (b.n) { UP(b.d_elem, b.h_elem); c->buckets.push_back(b); }
+  }
+  UP(c->d_coh_elems, P.coh_elems); UP(c->d_cblk_id, P.cblk_id); UP(c->d_cblk_row, P.cblk_row);
+  UP(c->d_cblk_ptr, P.cblk_ptr); UP(c->d_cblk_src, P.cblk_src); UP(c->d_cnode_id, P.cnode_id);
+  UP(c->d_cnode_ptr, P.cnode_ptr); UP(c->d_cnode_src, P.cnode_src);
+  if ((rc = dev_alloc(c, &c->d_coh_ke, 64 * (int64_t)P.coh_elems.size()))) return rc;
+  if ((rc = dev_alloc(c, &c->d_coh_fe, 8 * (int64_t)P.coh_elems.size()))) return rc;
+#undef UP
+  CK(cudaStreamSynchronize(c->stream));
+  c->has_plan = true;
+  c->d_ke = c->d_fe = c->d_sn = c->d_u = c->d_vals = c->d_kstage = nullptr;
+  for (auto &v : c->d_vec) v = nullptr;
+  c->buf_n.clear();
+  return prepare_bcs(c);
+}
+
+int femx_pattern_size(femx_ctx *c, int64_t *nrows, int64_t *nnz) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan, "femx_build_plan first");
+  if (nrows) *nrows = (int64_t)c->pdim * c->nnds;
+  if (nnz) *nnz = c->nnz;
+  return FEMX_OK;
+}
+
+int femx_get_pattern(femx_ctx *c, int64_t *rowptr, int32_t *colidx, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan, "femx_build_plan first");
+  const int pd = c->pdim;
+  const int64_t n = (int64_t)pd * c->nnds;
+  if (rowptr) {
+    std::vector<int64_t> rp(n + 1, 0);
+    for (int r = 0; r < c->nlnds; ++r) {
+      const int64_t nb = c->plan.bptr[r + 1] - c->plan.bptr[r];
+      for (int i = 0; i < pd; ++i) rp[(int64_t)pd * (c->nl2g[r] - 1) + i + 1] = pd * nb;
+    }
+    for (int64_t i = 0; i < n; ++i) rp[i + 1] += rp[i];
+    if (where == FEMX_DEVICE) CK(cudaMemcpy(rowptr, rp.data(), sizeof(int64_t) * (n + 1), cudaMemcpyHostToDevice));
+    else memcpy(rowptr, rp.data(), sizeof(int64_t) * (n + 1));
+  }
+  if (colidx) {
+    View v(c, colidx, sizeof(int32_t) * (size_t)c->nnz, where, false, true);
+    if (v.rc) return v.rc;
+    c->launches += launch_colidx(c, v.as<int32_t>());
+    int rc = v.finish();
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+  }
+  return FEMX_OK;
+}
+
+int femx_get_slot_map(femx_ctx *c, int64_t *offsets, uint16_t *blockpos) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan, "femx_build_plan first");
+  if (offsets) memcpy(offsets, c->plan.eb_ptr.data(), sizeof(int64_t) * (c->nels + 1));
+  if (blockpos) memcpy(blockpos, c->plan.bpos.data(), sizeof(uint16_t) * c->plan.bpos.size());
+  return FEMX_OK;
+}
+
+}  // extern "C"

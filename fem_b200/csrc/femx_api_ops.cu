@@ -1,0 +1,246 @@
+// femx_api_ops.cu -- element-level and mesh-level entry points of include/femx.h.
+#include "api_util.h"
+
+namespace {
+
+// persistent device buffer, grown on demand
+int ensure(femx_ctx *c, double **p, int64_t n) {
+  auto it = c->buf_n.find(p);
+  if (*p && it != c->buf_n.end() && it->second >= n) return FEMX_OK;
+  if (*p) { dev_release(c, *p); *p = nullptr; }
+  c->buf_n[p] = n;
+  return dev_alloc(c, p, n);
+}
+
+// device pointer for an input vector: the caller's (DEVICE) or a persistent staging copy
+int stage_in(femx_ctx *c, const double *src, int64_t n, int where, double **slot, const double **out) {
+  if (where == FEMX_DEVICE) { *out = src; return FEMX_OK; }
+  int rc = ensure(c, slot, n);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(*slot, src, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  *out = *slot;
+  return FEMX_OK;
+}
+
+int stage_out(femx_ctx *c, double *dst, int64_t n, int where, double **slot, double **out) {
+  if (where == FEMX_DEVICE) { *out = dst; return FEMX_OK; }
+  int rc = ensure(c, slot, n);
+  if (rc) return rc;
+  *out = *slot;
+  return FEMX_OK;
+}
+
+int copy_back(femx_ctx *c, double *dst, const double *dev, int64_t n, int where) {
+  if (where == FEMX_DEVICE || dst == dev) return FEMX_OK;
+  CK(cudaMemcpyAsync(dst, dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  return FEMX_OK;
+}
+
+int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int where) {
+  ARG(c->has_plan, "femx_build_plan first");
+  ARG(vals, "vals is NULL");
+  ARG((u_local == nullptr) == (fint == nullptr), "u_local and fint go together");
+  CK(cudaSetDevice(c->device));
+  const int64_t nloc = (int64_t)c->pdim * c->nlnds, nglob = (int64_t)c->pdim * c->nnds;
+  int rc;
+  const double *d_u = nullptr;
+  double *d_vals = nullptr, *d_fint = nullptr;
+  if (u_local && (rc = stage_in(c, u_local, nloc, where, &c->d_u, &d_u))) return rc;
+  if ((rc = stage_out(c, vals, c->nnz, where, &c->d_vals, &d_vals))) return rc;
+  if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
+  if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
+  if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
+  if ((rc = begin_timing(c))) return rc;
+  if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
+  c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
+  c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);
+  if ((rc = end_timing(c))) return rc;
+  if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
+  if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;
+  return finish_call(c, true);
+}
+
+}  // namespace
+
+extern "C" {
+
+// --------------------------------------------------------------------------- element level
+int femx_element_ke(femx_ctx *c, int type, int n, const double *ecoords, const double *E_nu, double *ke) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(type >= FEMX_TRI && type <= FEMX_HEX, "femx_element_ke: type must be tri/qua/tet/hex");
+  ARG(n >= 0 && ecoords && E_nu && ke, "bad arguments");
+  if (n == 0) return FEMX_OK;
+  CK(cudaSetDevice(c->device));
+  const int nen = type_nen(type), dim = type_dim(type), nd = nen * dim;
+  View x(c, ecoords, sizeof(double) * (size_t)n * nen * dim, FEMX_HOST, true, false);
+  View m(c, E_nu, sizeof(double) * (size_t)n * 2, FEMX_HOST, true, false);
+  View k(c, ke, sizeof(double) * (size_t)n * nd * nd, FEMX_HOST, false, true);
+  if (x.rc || m.rc || k.rc) return x.rc | m.rc | k.rc;
+  c->launches += launch_element_ke(c, type, n, x.as<double>(), m.as<double>(), k.as<double>());
+  int rc = k.finish();
+  if (rc) return rc;
+  return finish_call(c, false);
+}
+
+int femx_element_stress(femx_ctx *c, int type, int n, const double *ecoords, const double *edisp,
+                        const double *E_nu, double *estress, double *enodal) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(type >= FEMX_TRI && type <= FEMX_HEX, "femx_element_stress: type must be tri/qua/tet/hex");
+  ARG(n >= 0 && ecoords && edisp && E_nu && estress, "bad arguments");
+  if (n == 0) return FEMX_OK;
+  CK(cudaSetDevice(c->device));
+  const int nen = type_nen(type), dim = type_dim(type), nip = type_nip(type), cp = dim == 2 ? 3 : 6;
+  View x(c, ecoords, sizeof(double) * (size_t)n * nen * dim, FEMX_HOST, true, false);
+  View u(c, edisp, sizeof(double) * (size_t)n * nen * dim, FEMX_HOST, true, false);
+  View m(c, E_nu, sizeof(double) * (size_t)n * 2, FEMX_HOST, true, false);
+  View s(c, estress, sizeof(double) * (size_t)n * nip * cp, FEMX_HOST, false, true);
+  View sn(c, enodal, sizeof(double) * (size_t)n * nen * cp, FEMX_HOST, false, true);
+  if (x.rc || u.rc || m.rc || s.rc || sn.rc) return FEMX_ERR_ALLOC;
+  c->launches += launch_element_stress(c, type, n, x.as<double>(), u.as<double>(), m.as<double>(), s.as<double>(),
+                                       sn.as<double>());
+  int rc = s.finish();
+  if (rc) return rc;
+  if ((rc = sn.finish())) return rc;
+  return finish_call(c, false);
+}
+
+int femx_element_cohesive(femx_ctx *c, int n, const double *ecoords, const int *nodes, const double *u_local,
+                          int nu_local, const double *props, double dt, double *force, double *stiff) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(n >= 0 && ecoords && nodes && u_local && props && force && stiff, "bad arguments");
+  ARG(nu_local >= 8, "u_local must hold at least 4 nodes");
+  if (n == 0) return FEMX_OK;
+  CK(cudaSetDevice(c->device));
+  View x(c, ecoords, sizeof(double) * (size_t)n * 8, FEMX_HOST, true, false);
+  View nd(c, nodes, sizeof(int) * (size_t)n * 4, FEMX_HOST, true, false);
+  View u(c, u_local, sizeof(double) * (size_t)nu_local, FEMX_HOST, true, false);
+  View p(c, props, sizeof(double) * (size_t)n * 6, FEMX_HOST, true, false);
+  View f(c, force, sizeof(double) * (size_t)n * 8, FEMX_HOST, false, true);
+  View s(c, stiff, sizeof(double) * (size_t)n * 64, FEMX_HOST, false, true);
+  if (x.rc || nd.rc || u.rc || p.rc || f.rc || s.rc) return FEMX_ERR_ALLOC;
+  c->launches += launch_cohesive_unit(c, n, x.as<double>(), nd.as<int32_t>(), u.as<double>(), p.as<double>(), dt,
+                                      f.as<double>(), s.as<double>());
+  int rc = f.finish();
+  if (rc) return rc;
+  if ((rc = s.finish())) return rc;
+  return finish_call(c, false);
+}
+
+// --------------------------------------------------------------------------- mesh level
+int femx_assemble_K(femx_ctx *c, double *vals, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  return assemble(c, nullptr, vals, nullptr, where);
+}
+
+int femx_assemble_K_fint(femx_ctx *c, const double *u_local, double *vals, double *fint, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(u_local && fint, "u_local / fint is NULL");
+  return assemble(c, u_local, vals, fint, where);
+}
+
+int femx_apply_kbc(femx_ctx *c, double *vals, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && vals, "femx_build_plan first / vals NULL");
+  CK(cudaSetDevice(c->device));
+  if (where == FEMX_DEVICE) {
+    c->launches += launch_apply_kbc(c, vals);
+    return finish_call(c, false);
+  }
+  // host values: the BC list is O(#BC); patch through a staged copy of the touched slots
+  View v(c, vals, sizeof(double) * (size_t)c->nnz, FEMX_HOST, true, true);
+  if (v.rc) return v.rc;
+  c->launches += launch_apply_kbc(c, v.as<double>());
+  int rc = v.finish();
+  if (rc) return rc;
+  return finish_call(c, false);
+}
+
+int femx_jacobian(femx_ctx *c, const double *kvals, const double *u_total_local, double dt, double *jvals, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && kvals && u_total_local && jvals, "femx_build_plan first / NULL argument");
+  CK(cudaSetDevice(c->device));
+  int rc;
+  const double *d_u = nullptr, *d_k = nullptr;
+  double *d_j = nullptr;
+  if ((rc = stage_in(c, u_total_local, (int64_t)c->pdim * c->nlnds, where, &c->d_u, &d_u))) return rc;
+  if ((rc = stage_in(c, kvals, c->nnz, where, &c->d_kstage, &d_k))) return rc;
+  if ((rc = stage_out(c, jvals, c->nnz, where, &c->d_vals, &d_j))) return rc;
+  if ((rc = begin_timing(c))) return rc;
+  // MatCopy(Mat_K, Jacobian) src/m_global.F90:123
+  if (d_j != d_k) CK(cudaMemcpyAsync(d_j, d_k, sizeof(double) * (size_t)c->nnz, cudaMemcpyDeviceToDevice, c->stream));
+  c->launches += launch_cohesive_mesh(c, d_u, dt, nullptr, c->d_coh_ke);
+  c->launches += launch_jacobian_overlay(c, d_k, d_j);
+  c->launches += launch_apply_kbc(c, d_j);  // ApplyKBC(Jacobian) :154
+  if ((rc = end_timing(c))) return rc;
+  if ((rc = copy_back(c, jvals, d_j, c->nnz, where))) return rc;
+  return finish_call(c, true);
+}
+
+static int residual_impl(femx_ctx *c, const double *jvals, const double *u_total_local, const double *du,
+                         const double *f_ext, double dt, double t_total, double *r, int where) {
+  ARG(c->has_plan && u_total_local && f_ext && r, "femx_build_plan first / NULL argument");
+  ARG(t_total != 0.0, "t_total is zero");
+  CK(cudaSetDevice(c->device));
+  const int64_t nglob = (int64_t)c->pdim * c->nnds;
+  int rc;
+  const double *d_u = nullptr, *d_f = nullptr, *d_du = nullptr, *d_j = nullptr;
+  double *d_r = nullptr, *d_br = nullptr;
+  if ((rc = stage_in(c, u_total_local, (int64_t)c->pdim * c->nlnds, where, &c->d_u, &d_u))) return rc;
+  if ((rc = stage_in(c, f_ext, nglob, where, &c->d_vec[1], &d_f))) return rc;
+  if ((rc = stage_out(c, r, nglob, where, &c->d_vec[0], &d_r))) return rc;
+  if (jvals) {
+    if ((rc = stage_in(c, du, nglob, where, &c->d_vec[2], &d_du))) return rc;
+    if ((rc = stage_in(c, jvals, c->nnz, where, &c->d_vals, &d_j))) return rc;
+    // bracket goes to a scratch vector, r gets J*du - bracket
+    if ((rc = ensure(c, &c->d_vec[3], nglob))) return rc;
+    d_br = c->d_vec[3];
+  } else {
+    d_br = d_r;
+  }
+  if ((rc = begin_timing(c))) return rc;
+  CK(cudaMemcpyAsync(d_br, d_f, sizeof(double) * (size_t)nglob, cudaMemcpyDeviceToDevice, c->stream));  // VecCopy(Vec_F, R)
+  c->launches += launch_cohesive_mesh(c, d_u, dt, c->d_coh_fe, nullptr);
+  c->launches += launch_cohesive_force_gather(c, d_br);
+  c->launches += launch_bc_force(c, dt / t_total, d_br);  // EnforceBCForce :439-455
+  if (jvals) {
+    if (c->nlnds != c->nnds) CK(cudaMemsetAsync(d_r, 0, sizeof(double) * (size_t)nglob, c->stream));
+    c->launches += launch_spmv_sub(c, d_j, d_du, d_br, d_r);  // VecScale(-1); MatMultAdd :225-226
+  }
+  if ((rc = end_timing(c))) return rc;
+  if ((rc = copy_back(c, r, d_r, nglob, where))) return rc;
+  return finish_call(c, true);
+}
+
+int femx_residual(femx_ctx *c, const double *jvals, const double *u_total_local, const double *du,
+                  const double *f_ext, double dt, double t_total, double *r, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(jvals && du, "jvals / du is NULL");
+  return residual_impl(c, jvals, u_total_local, du, f_ext, dt, t_total, r, where);
+}
+
+int femx_residual_forces(femx_ctx *c, const double *u_total_local, const double *f_ext, double dt, double t_total,
+                         double *out, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  return residual_impl(c, nullptr, u_total_local, nullptr, f_ext, dt, t_total, out, where);
+}
+
+int femx_stress(femx_ctx *c, const double *uu_local, double *stress_node, int layout, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && uu_local && stress_node, "femx_build_plan first / NULL argument");
+  CK(cudaSetDevice(c->device));
+  const int cp = c->pdim == 2 ? 3 : 6;
+  const int64_t nout = (int64_t)c->nlnds * cp;
+  int rc;
+  const double *d_u = nullptr;
+  double *d_out = nullptr;
+  if ((rc = stage_in(c, uu_local, (int64_t)c->pdim * c->nlnds, where, &c->d_u, &d_u))) return rc;
+  if ((rc = stage_out(c, stress_node, nout, where, &c->d_vec[2], &d_out))) return rc;
+  if ((rc = ensure(c, &c->d_sn, (int64_t)c->eptr[c->nels] * cp))) return rc;
+  if ((rc = begin_timing(c))) return rc;
+  c->launches += launch_mesh_stress(c, d_u, c->d_sn, d_out, layout == FEMX_COL_MAJOR);
+  if ((rc = end_timing(c))) return rc;
+  if ((rc = copy_back(c, stress_node, d_out, nout, where))) return rc;
+  return finish_call(c, true);
+}
+
+}  // extern "C"

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <map>
 #include <string>
 #include <vector>
 
@@ -101,6 +102,8 @@ struct femx_ctx {
   double *d_sn = nullptr;     // per-element nodal stress [nen][cp]
   double *d_u = nullptr;      // staged u_local
   double *d_vals = nullptr;   // internal values buffer for host-output calls
+  double *d_kstage = nullptr; // staged K values (host-input femx_jacobian)
+  std::map<double **, int64_t> buf_n;  // capacity of the grow-on-demand buffers above
   double *d_vec[4] = {nullptr, nullptr, nullptr, nullptr};  // global-length staging vectors
   int64_t nnz = 0;
   // BC / cohesive device lists

@@ -1,0 +1,25 @@
+// launch.h -- host-callable launchers implemented in the .cu files (each returns the
+// number of kernels it launched on ctx->stream).
+#pragma once
+#include "femx_internal.h"
+
+namespace femx {
+
+void set_n2inv(const double *qua16, const double *hex64);
+int launch_elem_rows(femx_ctx *c, const double *d_u, double *d_ke, double *d_fe);
+int launch_gather_rows(femx_ctx *c, const double *d_ke, const double *d_fe, double *d_vals, double *d_fint);
+int launch_element_ke(femx_ctx *c, int type, int n, const double *d_x, const double *d_enu, double *d_out);
+int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const double *d_u, const double *d_enu,
+                          double *d_sig, double *d_sn);
+int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major);
+int launch_colidx(femx_ctx *c, int32_t *d_colidx);
+int launch_apply_kbc(femx_ctx *c, double *d_vals);
+int launch_bc_force(femx_ctx *c, double scale, double *d_out);
+int launch_spmv_sub(femx_ctx *c, const double *d_vals, const double *d_x, const double *d_sub, double *d_y);
+int launch_cohesive_mesh(femx_ctx *c, const double *d_u, double dt, double *d_force, double *d_stiff);
+int launch_cohesive_unit(femx_ctx *c, int n, const double *d_x, const int32_t *d_nodes, const double *d_u,
+                         const double *d_props, double dt, double *d_force, double *d_stiff);
+int launch_jacobian_overlay(femx_ctx *c, const double *d_kvals, double *d_jvals);
+int launch_cohesive_force_gather(femx_ctx *c, double *d_out);
+
+}  // namespace femx

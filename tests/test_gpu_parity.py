@@ -1,0 +1,232 @@
+"""Parity proper: the CUDA path through the C ABI vs the CPU oracle on the same inputs.
+
+Bar (BASELINE.json north_star): sparsity pattern and index maps bit-exact; element,
+global-matrix and residual entries <= 1e-12 relative; stress fields <= 1e-10 relative.
+"Relative" is |a-b| <= tol * max(|b|, scale) with scale the largest entry of the object
+compared, so structurally cancelling entries do not produce false failures.
+"""
+import dataclasses
+
+import numpy as np
+import pytest
+
+from fem_b200 import api, mesh as fm, meshgen as mg
+
+pytestmark = pytest.mark.gpu
+
+TOL_MAT = 1e-12
+TOL_FIELD = 1e-10
+
+
+def close(a, b, tol, scale=None):
+    a, b = np.asarray(a), np.asarray(b)
+    scale = np.abs(b).max() if scale is None else scale
+    return bool(np.all(np.abs(a - b) <= tol * np.maximum(np.abs(b), scale)))
+
+
+@pytest.fixture(scope="module")
+def fx():
+    f = api.Femx(quirks=api.Q_REFERENCE)
+    yield f
+    f.close()
+
+
+def _distorted(t, n, seed):
+    from tests.test_oracle_elements import REF_SHAPES
+    rng = np.random.default_rng(seed)
+    x = np.repeat(REF_SHAPES[t][None], n, 0)
+    d = x.shape[2]
+    A = np.eye(d) + 0.2 * rng.standard_normal((n, d, d))
+    return np.einsum("nad,ned->nae", x, A) + 0.15 * rng.uniform(-1, 1, x.shape) + rng.uniform(-3, 3, (n, 1, d))
+
+
+@pytest.mark.parametrize("t", [fm.TRI, fm.QUA, fm.TET, fm.HEX])
+def test_element_ke_and_stress(fx, orc, t):
+    n = 257
+    x = _distorted(t, n, 5)
+    rng = np.random.default_rng(9)
+    E = rng.uniform(1e3, 5e10, n)
+    nu = rng.uniform(0.05, 0.45, n)
+    u = 1e-3 * rng.standard_normal(x.shape)
+    K = fx.FormElKE(t, x, E, nu)
+    s, sn = fx.CalcElStress(t, x, u, E, nu)
+    for e in range(n):
+        Ko = orc.form_el_ke(t, x[e], E[e], nu[e])
+        assert close(K[e], Ko, TOL_MAT), e
+        so = orc.calc_el_stress(t, x[e], u[e].reshape(-1), E[e], nu[e])
+        assert close(s[e], so, TOL_FIELD), e
+        assert close(sn[e], orc.recover_nodal_stress(t, so), TOL_FIELD), e
+
+
+@pytest.mark.parametrize("quirks", [api.Q_REFERENCE, api.Q_UEL, api.Q_TANGENT_PRECEDENCE, api.Q_FORCE_LAST_IP])
+def test_cohesive_element(orc, quirks):
+    rng = np.random.default_rng(1)
+    n = 64
+    x0 = rng.uniform(-2, 2, (n, 1, 2))
+    ang = rng.uniform(0, 2 * np.pi, n)
+    L = rng.uniform(0.5, 2.0, n)
+    tvec = np.stack([np.cos(ang), np.sin(ang)], 1) * L[:, None]
+    x = np.concatenate([x0, x0 + tvec[:, None], x0 + tvec[:, None], x0], axis=1) + 1e-3 * rng.standard_normal((n, 4, 2))
+    nodes = np.stack([rng.permutation(12)[:4] + 1 for _ in range(n)]).astype(np.int32)
+    u = 4e-3 * rng.standard_normal(24)
+    props = np.stack([rng.uniform(50, 200, n), rng.uniform(.005, .02, n), rng.uniform(.005, .02, n),
+                      rng.uniform(.3, 1., n), rng.uniform(0., .5, n), rng.uniform(0, 1e-3, n)], 1)
+    with api.Femx(quirks=quirks) as f:
+        F, S = f.cohesive(x, nodes, u, props, 0.01)
+    for e in range(n):
+        Fo = orc.apply_tract_1(x[e], nodes[e], u, 0.01, props[e], quirks)
+        So = orc.apply_stiff_1(x[e], nodes[e], u, 0.01, props[e], quirks)
+        assert close(F[e], Fo, TOL_MAT), e
+        assert close(S[e], So, TOL_MAT), e
+
+
+def _meshes(golden):
+    yield "lin_two_quads_qs", fm.read_inp(golden["decks"]["lin_two_quads_qs"])     # BASELINE config 1
+    yield "two_quads_qs", fm.read_inp(golden["decks"]["two_quads_qs"])
+    yield "cohesive_test_2", fm.read_inp(golden["decks"]["cohesive_test_2"])
+    yield "hex6_jitter", mg.jitter(mg.hex_cube(6))
+    yield "hex_rect", mg.hex_cube(5)
+    yield "tet4_jitter", mg.jitter(mg.tet_cube(4))
+    yield "quad_jitter", mg.jitter(mg.quad_rect(9, 7))
+    yield "coh_strip", mg.jitter(mg.cohesive_strip(12, 3))
+    # a rank-local mesh: ragged node set, nl2g not the identity
+    g = mg.jitter(mg.hex_cube(5))
+    yield "hex_rank1of3", fm.localize(g, mg.slab_partition(g, 3), 1)
+
+
+def test_pattern_values_fint_vs_oracle(fx, orc, golden):
+    for name, m in _meshes(golden):
+        fx.set_mesh(m).build_plan()
+        om = orc.Mesh(m)
+        rp_o, ci_o, va_o = orc.assemble_K(om, prealloc=m.pdim * (m.nodal_bw + 1)).export(om.ndof)
+        rp, ci = fx.pattern()
+        assert np.array_equal(rp, rp_o), name          # bit-exact pattern
+        assert np.array_equal(ci, ci_o), name
+        u = mg.displacement_field(m)
+        vals, fint = fx.assemble_K_fint(u)
+        assert close(vals, va_o, TOL_MAT), name
+        assert np.array_equal(fx.assemble_K(), vals), name   # deterministic, same order
+        assert close(fint, orc.fint(om, u.reshape(-1)), TOL_MAT), name
+        # index map: slot(e,a,i,b,j) must address (row, col) of that entry
+        off, bpos = fx.slot_map()
+        for e in range(0, m.nels, max(1, m.nels // 40)):
+            nd = m.elem_nodes(e)
+            nen = len(nd)
+            for a in range(nen):
+                for b in range(nen):
+                    row = m.pdim * (m.nl2g[nd[a] - 1] - 1)
+                    col = m.pdim * (m.nl2g[nd[b] - 1] - 1)
+                    slot = rp[row] + m.pdim * bpos[off[e] + a * nen + b]
+                    assert ci[slot] == col, (name, e, a, b)
+        # BC penalty: exact INSERT
+        kb = fx.apply_kbc(vals.copy())
+        _, _, vb_o = orc.assemble_K(om, apply_bc=True).export(om.ndof)
+        pen = vb_o == float(np.float32(1e30))
+        assert np.array_equal(kb[pen], vb_o[pen]) and close(kb[~pen], vb_o[~pen], TOL_MAT, np.abs(va_o).max()), name
+
+
+def test_golden_matview_through_cuda(golden):
+    """examples/tmp.txt: the Jacobian of cohesive_test_2.inp, now from the CUDA path."""
+    g = golden["jacobian_matview_cohesive_test_2"]
+    m = fm.read_inp(golden["decks"]["cohesive_test_2"])
+    m = dataclasses.replace(m, mat=np.vstack([m.mat, np.zeros((1, 5))]), emat=np.array([1, 2, 0], np.int32))
+    with api.Femx(quirks=api.Q_REFERENCE) as f:
+        f.set_mesh(m).build_plan()
+        rp, ci = f.pattern()
+        K = f.apply_kbc(f.assemble_K())
+        J = f.CalcJacobian(K, np.zeros(16), m.dt)
+    for i in range(16):
+        assert ci[rp[i]:rp[i + 1]].tolist() == [c for c, _ in g[i]]
+    for i in range(8):
+        for (c, gv), v in zip(g[i], J[rp[i]:rp[i + 1]]):
+            assert abs(v - gv) <= 6e-6 * abs(gv) or (abs(gv) < 1e-300 and abs(v) < 1e-9), (i, c, v, gv)
+
+
+@pytest.mark.parametrize("quirks", [api.Q_REFERENCE, api.Q_UEL])
+def test_jacobian_residual_vs_oracle(orc, golden, quirks):
+    for name, m in (("cohesive_test_2", fm.read_inp(golden["decks"]["cohesive_test_2"])),
+                    ("two_quads_qs", fm.read_inp(golden["decks"]["two_quads_qs"])),
+                    ("coh_strip", mg.jitter(mg.cohesive_strip(16, 3)))):
+        om = orc.Mesh(m)
+        rng = np.random.default_rng(4)
+        u_tot = 2e-3 * rng.standard_normal(m.nlnds * 2)
+        du = 1e-3 * rng.standard_normal(om.ndof)
+        fext = 10.0 * rng.standard_normal(om.ndof)
+        Ko = orc.assemble_K(om, apply_bc=True)
+        Jo = orc.jacobian(om, Ko, u_tot, m.dt, quirks)
+        _, _, jv_o = Jo.export(om.ndof)
+        r_o = orc.residual(om, Jo, u_tot, du, fext, m.dt, m.t, quirks)
+        with api.Femx(quirks=quirks) as f:
+            f.set_mesh(m).build_plan()
+            K = f.apply_kbc(f.assemble_K())
+            J = f.CalcJacobian(K, u_tot, m.dt)
+            r = f.CalcResidual(J, u_tot, du, fext, m.dt, m.t)
+            br = f.residual_forces(u_tot, fext, m.dt, m.t)
+        pen = jv_o == float(np.float32(1e30))
+        scale = np.abs(jv_o[~pen]).max()
+        assert np.array_equal(J[pen], jv_o[pen]), name
+        assert close(J[~pen], jv_o[~pen], TOL_MAT, scale), name
+        # rows with a 1e30 penalty: compare relative to the row's own magnitude
+        assert close(r, r_o, TOL_MAT, None if np.abs(r_o).max() < 1e20 else np.abs(r_o[np.abs(r_o) < 1e20]).max()), name
+        assert close(br, -(r_o - np.asarray(_spmv(Jo, du, om.ndof, orc))), 1e-9), name
+
+
+def _spmv(Jo, x, n, orc):
+    rp, ci, va = Jo.export(n)
+    y = np.zeros(n)
+    for i in range(n):
+        y[i] = va[rp[i]:rp[i + 1]] @ x[ci[rp[i]:rp[i + 1]]]
+    return y
+
+
+def test_stress_vs_oracle(fx, orc, golden):
+    for name, m in _meshes(golden):
+        fx.set_mesh(m).build_plan()
+        u = mg.displacement_field(m)
+        s_o, cnt = orc.stress(orc.Mesh(m), u.reshape(-1), orc.Q_REFERENCE)
+        s = fx.stress(u)
+        assert close(s, s_o, TOL_FIELD), name
+        assert np.array_equal(fx.stress(u, layout=api.COL_MAJOR), s), name
+
+
+def test_elastic_golden_vtk_through_cuda(fx, golden):
+    coords = np.array([[0, 2], [0, 1], [0, 0], [1, 2], [1, 1], [1, 0]], float)
+    m = fm.from_uniform(2, fm.QUA, [[1, 2, 5, 4], [2, 3, 6, 5]], coords, E=3640.0, nu=0.3)
+    u = np.zeros((6, 2))
+    u[:, 1] = 0.05 * coords[:, 1]
+    s = fx.set_mesh(m).build_plan().stress(u)
+    assert np.allclose(s, [105.0, 245.0, 0.0], rtol=1e-12, atol=1e-10)
+
+
+def test_edge_cases(fx):
+    # ragged / mixed element types with unused global nodes, single element, empty BC list
+    m = fm.from_uniform(2, fm.TRI, [[2, 5, 9]], np.array([[0, 0], [1, 0], [0, 1.]]))
+    m = dataclasses.replace(m, nl2g=np.array([2, 5, 9], np.int32), nnds=11, eind=np.array([1, 2, 3], np.int32))
+    fx.set_mesh(m).build_plan()
+    rp, ci = fx.pattern()
+    assert fx.nrows == 22 and fx.nnz == 36
+    assert rp[2] == 0 and rp[4] == 12 and rp[-1] == 36
+    assert ci[:6].tolist() == [2, 3, 8, 9, 16, 17]
+    vals, fint = fx.assemble_K_fint(np.zeros(6))
+    assert np.all(fint == 0) and abs(vals.reshape(6, 6).sum()) < 1e-3
+
+
+def test_large_mesh_properties(fx):
+    """Size-independent properties at a size the oracle cannot finish quickly: rigid-body
+    modes give zero internal force, K is symmetric, row sums vanish, stress of a linear
+    field is constant."""
+    m = mg.jitter(mg.hex_cube(24))
+    fx.set_mesh(m).build_plan()
+    rp, ci = fx.pattern()
+    x = m.coords
+    rot = np.c_[-x[:, 1], x[:, 0], np.zeros(len(x))]
+    vals, f_rot = fx.assemble_K_fint(rot)
+    _, f_tr = fx.assemble_K_fint(np.tile([1.0, -2.0, 0.5], (len(x), 1)))
+    scale = np.abs(vals).max()
+    assert np.abs(f_tr).max() <= 1e-10 * scale and np.abs(f_rot).max() <= 1e-9 * scale * np.abs(x).max()
+    import scipy.sparse as sp
+    A = sp.csr_matrix((vals, ci, rp), shape=(fx.nrows, fx.nrows))
+    assert abs(A - A.T).max() <= 1e-12 * scale
+    G = 1e-3 * np.array([[1, 2, 0], [0, -1, 3], [2, 0, 1.0]])
+    s = fx.stress(x @ G.T)
+    assert np.abs(s - s[0]).max() <= 1e-9 * np.abs(s[0]).max()
