@@ -91,7 +91,9 @@ def _meshes(golden):
     yield "coh_strip", mg.jitter(mg.cohesive_strip(12, 3))
     # a rank-local mesh: ragged node set, nl2g not the identity
     g = mg.jitter(mg.hex_cube(5))
-    yield "hex_rank1of3", fm.localize(g, mg.slab_partition(g, 3), 1)
+    loc = fm.localize(g, mg.slab_partition(g, 3), 1)
+    keep = np.isin(loc.bcnode[:, 0], loc.nl2g)       # BCs of nodes this rank holds
+    yield "hex_rank1of3", dataclasses.replace(loc, bcnode=loc.bcnode[keep], bcval=loc.bcval[keep])
 
 
 def test_pattern_values_fint_vs_oracle(fx, orc, golden):
