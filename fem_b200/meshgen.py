@@ -37,9 +37,12 @@ def hash_uniform(ids: np.ndarray, seed: int, ncomp: int) -> np.ndarray:
     return out
 
 
-def jitter(m: Mesh, amount=0.15, seed=12345) -> Mesh:
-    """Move interior nodes by amount*h*U(-1,1) so elements are not congruent."""
-    lo, hi = m.coords.min(0), m.coords.max(0)
+def jitter(m: Mesh, amount=0.15, seed=12345, lo=None, hi=None) -> Mesh:
+    """Move interior nodes by amount*h*U(-1,1) so elements are not congruent.  The offset of a
+    node depends only on its GLOBAL id, so rank-local pieces of one mesh agree (pass the global
+    bounding box as lo/hi for those)."""
+    lo = m.coords.min(0) if lo is None else np.asarray(lo, float)
+    hi = m.coords.max(0) if hi is None else np.asarray(hi, float)
     interior = np.all((m.coords > lo + 1e-9) & (m.coords < hi - 1e-9), axis=1)
     d = amount * hash_uniform(m.nl2g.astype(np.uint64), seed, m.pdim)
     c = m.coords.copy()
@@ -151,6 +154,30 @@ def cohesive_strip(nx: int, ny: int, E=3640.0, nu=0.3, props=(100.0, 0.01, 0.01,
     return Mesh(pdim=2, etype=etype, eptr=eptr, eind=eind, emat=emat, enlmat=enl, coords=coords,
                 nl2g=np.arange(1, len(coords) + 1), nnds=len(coords), mat=np.array([[E, nu, 1e18, 1.0, 3000.0]]),
                 cohprops=np.array([props]), bcnode=bcnode, bcval=bcval, t=t, dt=dt, nodal_bw=10).normalized()
+
+
+def hex_block(nx: int, ny: int, nz: int, z0: int = 0, nz_total: int | None = None, E=3.0e10, nu=0.25,
+              jittered=True) -> Mesh:
+    """Rank-local z-slab [z0, z0+nz] of an nx x ny x nz_total hex8 column, built directly in
+    local form (what `localize` would give for a slab partition): global node ids of the
+    column, local ids ascending with them, elements in ascending global order."""
+    nz_total = nz if nz_total is None else nz_total
+    npl = (nx + 1) * (ny + 1)
+    i, j, k = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    order = np.argsort((i + nx * (j + ny * k)).reshape(-1), kind="stable")
+    i, j, k = (a.reshape(-1)[order] for a in (i, j, k))
+    nid = lambda a, b, c: 1 + a + (nx + 1) * (b + (ny + 1) * c)       # local == global - z0*npl
+    conn = np.stack([nid(i, j, k), nid(i + 1, j, k), nid(i + 1, j + 1, k), nid(i, j + 1, k),
+                     nid(i, j, k + 1), nid(i + 1, j, k + 1), nid(i + 1, j + 1, k + 1), nid(i, j + 1, k + 1)], axis=1)
+    zz, yy, xx = np.meshgrid(np.arange(z0, z0 + nz + 1.0), np.arange(ny + 1.0), np.arange(nx + 1.0), indexing="ij")
+    coords = np.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], axis=1)
+    m = from_uniform(3, HEX, conn, coords, E=E, nu=nu, nodal_bw=26)
+    m.nl2g = (np.arange(1, len(coords) + 1) + z0 * npl).astype(np.int32)
+    m.nnds = npl * (nz_total + 1)
+    m.eglobal = np.arange(m.nels, dtype=np.int64) + z0 * nx * ny
+    if jittered:
+        m = jitter(m, lo=(0, 0, 0), hi=(nx, ny, nz_total))
+    return m
 
 
 def slab_partition(m: Mesh, nparts: int) -> np.ndarray:
