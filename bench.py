@@ -123,6 +123,8 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=24, help="edge of the bounded CPU sample cube")
     ap.add_argument("--impl", default="femx")
     ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--tile", type=int, default=0)
+    ap.add_argument("--lz", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -142,7 +144,7 @@ def main():
 
     from fem_b200 import api
     m, u = build_workload(args.n, world, rank)
-    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant)
+    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz)
     t0 = time.time()
     fx.set_mesh(m).build_plan()
     plan_s = time.time() - t0
@@ -222,7 +224,7 @@ def main():
                            "elements_per_gpu": m.nels, "dof_per_gpu": int(m.pdim * m.nlnds), "nnz_per_gpu": int(nnz),
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
                            "parallelism": f"element partition x{world}, no exchange" if world > 1 else "1 GPU",
-                           "variant": args.variant, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
+                           "variant": args.variant, "tile": args.tile, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
                 "gpu_launches": int(launches),
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -227,6 +227,25 @@ int femx_build_plan(femx_ctx *c) {
   if ((rc = dev_alloc(c, &c->d_coh_ke, 64 * (int64_t)P.coh_elems.size()))) return rc;
   if ((rc = dev_alloc(c, &c->d_coh_fe, 8 * (int64_t)P.coh_elems.size()))) return rc;
 #undef UP
+  // fused hex8 path (variant 2): only if the mesh provably is a logical grid of hex8
+  c->hex = femx::HexPlan();
+  if (c->opts.assembly_variant != 1) {
+    build_hex_plan(P, c->etype.data(), c->eptr.data(), c->emat.data(), c->E_nu.data(), c->nmts, &c->hex, &c->hex.why);
+    if (c->hex.ok) {
+      femx::DevHex &hx = c->dhex;
+      hx.NI = c->hex.NI; hx.NJ = c->hex.NJ; hx.NK = c->hex.NK; hx.rho = c->hex.rho;
+      UP(hx.node_at, c->hex.node_at); UP(hx.elem_at, c->hex.elem_at); UP(hx.kmap, c->hex.kmap);
+      std::vector<double> c4((size_t)c->nlnds * 4, 0.0), smu(c->nmts);
+      for (int i = 0; i < c->nlnds; ++i)
+        for (int d = 0; d < 3; ++d) c4[(size_t)i * 4 + d] = c->coords[(size_t)i * 3 + d];
+      for (int m = 0; m < c->nmts; ++m) smu[m] = std::sqrt(lm[2 * m + 1]);
+      UP(hx.coords4, c4); UP(hx.sqrt_mu, smu);
+    } else if (c->opts.assembly_variant == 2) {
+      c->err = "assembly_variant 2 requested but the mesh does not qualify: " + c->hex.why;
+      return FEMX_ERR_UNSUPPORTED;
+    }
+  }
+#undef UP
   CK(cudaStreamSynchronize(c->stream));
   c->has_plan = true;
   c->d_ke = c->d_fe = c->d_sn = c->d_u = c->d_vals = c->d_kstage = nullptr;

@@ -48,12 +48,19 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (u_local && (rc = stage_in(c, u_local, nloc, where, &c->d_u, &d_u))) return rc;
   if ((rc = stage_out(c, vals, c->nnz, where, &c->d_vals, &d_vals))) return rc;
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
-  if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
-  if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
+  const bool fused = c->hex.ok && c->opts.assembly_variant != 1;
+  if (!fused) {
+    if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
+    if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
+  }
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
-  c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
-  c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);
+  if (fused) {
+    c->launches += launch_hex_fused(c, d_u, d_vals, d_fint);
+  } else {
+    c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
+    c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);
+  }
   if ((rc = end_timing(c))) return rc;
   if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
   if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;

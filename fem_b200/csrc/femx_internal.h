@@ -52,6 +52,27 @@ struct Plan {
   double build_seconds = 0.0;
 };
 
+// plan_hex.cpp: logical-grid proof + canonical 27-stencil positions for the fused hex8 kernel
+struct HexPlan {
+  bool ok = false;
+  double rho = 0.0;                 // lambda / mu (one Poisson ratio per mesh)
+  int NI = 0, NJ = 0, NK = 0;       // logical node-grid extents
+  std::vector<int32_t> node_at;     // [NK][NJ][NI] local node id or -1
+  std::vector<int32_t> elem_at;     // [NK][NJ][NI] local element id or -1 (cell spans i..i+1)
+  std::vector<uint8_t> kmap;        // [nlnds][32]: block position of neighbour (dz,dy,dx), 255 = none
+  std::string why;                  // reason the mesh does not qualify
+};
+struct DevHex {
+  int NI = 0, NJ = 0, NK = 0;
+  double rho = 0.0;
+  int32_t *node_at = nullptr, *elem_at = nullptr;
+  uint8_t *kmap = nullptr;
+  double *coords4 = nullptr;        // [nlnds][4] padded coordinates (128-bit loads)
+  double *sqrt_mu = nullptr;        // [nmts]
+};
+int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,
+                   HexPlan *H, std::string *why);
+
 int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int *eind,
                const int *enlmat, int nlnds, int nnds, Plan *out, std::string *err);
 
@@ -94,6 +115,8 @@ struct femx_ctx {
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
   femx::Plan plan;
+  femx::HexPlan hex;
+  femx::DevHex dhex;
   femx::DevMesh dm;
   std::vector<femx::Bucket> buckets;
   // scratch

@@ -1,0 +1,338 @@
+// hex_fused.cu -- assembly variant 2: fused, gather-ordered hex8 K (+ f_int) kernel.
+//
+// One CTA owns a TX x TY column of logical node positions and marches through node layers.
+// Per step one ELEMENT layer is resident in shared memory as scaled physical gradients
+//   gt_b(ip) = adj(J)^T dN_b * sqrt(mu w / detJ)            [8 ip][3][8 nodes] fp64 per element
+// so that  sum_ip gt_a gt_b^T = mu * sum_ip w detJ (grad N_a)(grad N_b)^T = G'_ab  and
+//   K_ab = rho G'_ab + G'_ab^T + tr(G'_ab) I,   rho = lambda/mu      (== B_a^T D B_b, FormElKE
+// src/m_local.F90:61-65 with D of src/m_local.F90:214-228).
+// Four threads serve each node position; every thread sums 16 (corner element, node b)
+// contributions into 9 register-resident 3x3 blocks (no atomics, fixed order):
+//   role 0  upper node (layer m+1), nodes b of the bottom face  -> its dz=-1 blocks, stored now
+//   role 3  lower node (layer m),   nodes b of the top face     -> its dz=+1 blocks, stored now
+//   roles 1/2 alternate: "start" the dz=0 blocks of the upper node with this layer's elements,
+//            and next step "finish" them with the layer above, then store.
+// Every CSR value is written exactly once; rows leave through a per-warp shared-memory
+// transpose so that global stores are contiguous 216-byte runs.
+#include "elem_math.cuh"
+#include "launch.h"
+
+namespace femx {
+
+namespace {
+
+constexpr int kGeoStride = 194;   // doubles per element: 8*24 + 2 pad -> 16B-unit stride 97 (odd)
+
+struct RunMeta {       // destination of one thread's 9 blocks for the current step
+  long long base;      // slot of (row i = 0, block position 0)
+  int nb;              // blocks in the node's row, 0 = nothing to store
+  unsigned char k[12]; // block position per canonical slot (255 = absent)
+};
+
+__device__ __forceinline__ int hs_index(int sx, int sy) { return sy ? (sx ? 2 : 3) : (sx ? 1 : 0); }
+
+template <int TX, int TY, bool WITH_F>
+__global__ void __launch_bounds__(4 * TX * TY, (TX * TY <= 32) ? 2 : 1)
+hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__restrict__ vals,
+                 double *__restrict__ fint, int LZ) {
+  constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32;
+  constexpr int EX = TX + 1, EY = TY + 1, EL = EX * EY;
+  constexpr int UX = TX + 2, UY = TY + 2, UL = UX * UY;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]
+  double *stage = geo + EL * kGeoStride;                                 // [NW][32][27]
+  double *ulay = stage + NW * 32 * 27;                                   // [2][UL][3]   (WITH_F)
+  double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]      (WITH_F)
+  RunMeta *meta = reinterpret_cast<RunMeta *>(fcarry + (WITH_F ? NP * 3 : 0));  // [NT]
+  int *eid = reinterpret_cast<int *>(meta + NT);                         // [EL]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = tid >> 2, role = tid & 3;
+  const int px = p % TX, py = p / TX;
+  const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+  const int l0 = blockIdx.z * LZ, l1 = min(l0 + LZ, hx.NK) - 1;
+  const int gi = i0 + px, gj = j0 + py;
+  const bool in_xy = gi < hx.NI && gj < hx.NJ;
+  const double rho = hx.rho;
+
+  double acc[9][9];
+#pragma unroll
+  for (int s = 0; s < 9; ++s)
+#pragma unroll
+    for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
+
+  // displacement of one node layer (halo included) into buffer lay&1
+  auto load_u_layer = [&](int lay) {
+    double *ub = ulay + ((lay & 1) ? UL * 3 : 0);
+    for (int t = tid; t < UL; t += NT) {
+      const int ni = i0 - 1 + t % UX, nj = j0 - 1 + t / UX;
+      int r = -1;
+      if (lay >= 0 && lay < hx.NK && ni >= 0 && nj >= 0 && ni < hx.NI && nj < hx.NJ)
+        r = hx.node_at[((long long)lay * hx.NJ + nj) * hx.NI + ni];
+      ub[t * 3 + 0] = r >= 0 ? u[(long long)r * 3 + 0] : 0.0;
+      ub[t * 3 + 1] = r >= 0 ? u[(long long)r * 3 + 1] : 0.0;
+      ub[t * 3 + 2] = r >= 0 ? u[(long long)r * 3 + 2] : 0.0;
+    }
+  };
+  if (WITH_F) {
+    if (tid < NP * 3) fcarry[tid] = 0.0;
+    load_u_layer(l0 - 1);
+  }
+  __syncthreads();
+
+  for (int m = l0 - 1; m <= l1; ++m) {
+    // ------------------------------------------------------------ phase A: geometry of element layer m
+    const bool layer_ok = m >= 0 && m < hx.NK - 1;
+    for (int t = tid; t < EL; t += NT) {
+      const int ei = i0 - 1 + t % EX, ej = j0 - 1 + t / EX;
+      int e = -1;
+      if (layer_ok && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
+        e = hx.elem_at[((long long)m * hx.NJ + ej) * hx.NI + ei];
+      eid[t] = e;
+    }
+    if (WITH_F) load_u_layer(m + 1);   // layer m is already resident in the other buffer
+    __syncthreads();
+    for (int item = tid; item < EL * 8; item += NT) {
+      const int es = item % EL, ip = item / EL;
+      const int e = eid[es];
+      if (e < 0) continue;
+      double X[8][3];
+      const int4 c0 = *reinterpret_cast<const int4 *>(dm.conn0 + (long long)e * 8);
+      const int4 c1 = *reinterpret_cast<const int4 *>(dm.conn0 + (long long)e * 8 + 4);
+      const int nd[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        const double2 xy = *reinterpret_cast<const double2 *>(hx.coords4 + (long long)nd[b] * 4);
+        X[b][0] = xy.x; X[b][1] = xy.y; X[b][2] = hx.coords4[(long long)nd[b] * 4 + 2];
+      }
+      double dN[3][8];
+      parent_grad<FEMX_HEX>(ip, dN);
+      double J[3][3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          double s = 0.0;
+#pragma unroll
+          for (int a = 0; a < 8; ++a) s += dN[i][a] * X[a][j];
+          J[i][j] = s;
+        }
+      // adjugate (inverse * det): inv[i][j] = adj[i][j] / det
+      double adj[3][3];
+      adj[0][0] = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+      adj[0][1] = J[0][2] * J[2][1] - J[0][1] * J[2][2];
+      adj[0][2] = J[0][1] * J[1][2] - J[0][2] * J[1][1];
+      adj[1][0] = J[1][2] * J[2][0] - J[1][0] * J[2][2];
+      adj[1][1] = J[0][0] * J[2][2] - J[0][2] * J[2][0];
+      adj[1][2] = J[0][2] * J[1][0] - J[0][0] * J[1][2];
+      adj[2][0] = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+      adj[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
+      adj[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+      const double det = J[0][0] * adj[0][0] + J[0][1] * adj[1][0] + J[0][2] * adj[2][0];
+      const double sc = hx.sqrt_mu[dm.emat[e] - 1] * sqrt(1.0 / det);   // hex weights are 1 (src/m_elems.F90:508)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) adj[i][j] *= sc;
+      double *g = geo + es * kGeoStride + ip * 24;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        double row[8];
+#pragma unroll
+        for (int b = 0; b < 8; ++b) row[b] = adj[i][0] * dN[0][b] + adj[i][1] * dN[1][b] + adj[i][2] * dN[2][b];
+#pragma unroll
+        for (int b = 0; b < 8; b += 2) *reinterpret_cast<double2 *>(g + i * 8 + b) = make_double2(row[b], row[b + 1]);
+      }
+    }
+    __syncthreads();
+
+    // ------------------------------------------------------------ phase B: 16 contributions per thread
+    const int par = (m + 2) & 1;
+    const bool isA = (role == 1 + par), isB = (role == 2 - par);
+    const bool upper = role == 0 || isB;                 // works on node layer m+1
+    const int lay = upper ? m + 1 : m;
+    const bool lay_ok = lay >= l0 && lay <= l1;
+    int r = -1;
+    if (in_xy && lay_ok) r = hx.node_at[((long long)lay * hx.NJ + gj) * hx.NI + gi];
+    const int atop = upper ? 4 : 0;                      // our node sits on the top face of layer-m elements
+    const int btop = (role == 3 || isB) ? 4 : 0;
+    if (!isA) {
+#pragma unroll
+      for (int s = 0; s < 9; ++s)
+#pragma unroll
+        for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
+    }
+    if (r >= 0) {
+#pragma unroll
+      for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+        for (int ox = 0; ox < 2; ++ox) {
+          const int es = (py + oy) * EX + (px + ox);
+          if (eid[es] < 0) continue;
+          const double *g = geo + es * kGeoStride;
+          const int a = hs_index(1 - ox, 1 - oy) + atop;
+#pragma unroll 2
+          for (int ip = 0; ip < 8; ++ip) {
+            const double *gp = g + ip * 24;
+            double ga[3], gb[3][4];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+              ga[i] = gp[i * 8 + a];
+              const double2 v0 = *reinterpret_cast<const double2 *>(gp + i * 8 + btop);
+              const double2 v1 = *reinterpret_cast<const double2 *>(gp + i * 8 + btop + 2);
+              gb[i][0] = v0.x; gb[i][1] = v0.y; gb[i][2] = v1.x; gb[i][3] = v1.y;
+            }
+#pragma unroll
+            for (int bb = 0; bb < 4; ++bb) {
+              const int bx = (bb == 1 || bb == 2) ? 1 : 0, by = bb >= 2 ? 1 : 0;
+              const int s = (by + oy) * 3 + (bx + ox);
+#pragma unroll
+              for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) acc[s][i * 3 + j] = fma(ga[i], gb[j][bb], acc[s][i * 3 + j]);
+            }
+          }
+        }
+    }
+    // ------------------------------------------------------------ store the groups completed by this step
+    const bool writer = r >= 0 && !isB;
+    const int grp = role == 0 ? 0 : (role == 3 ? 2 : 1);       // dz = -1, 0, +1
+    {
+      RunMeta mt;
+      mt.nb = 0;
+      mt.base = 0;
+      if (writer) {
+        const long long b0 = dm.bptr[r];
+        mt.nb = (int)(dm.bptr[r + 1] - b0);
+        mt.base = 9 * b0;
+        const uint4 kw0 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32);
+        const uint4 kw1 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32 + 16);
+        const unsigned int w[8] = {kw0.x, kw0.y, kw0.z, kw0.w, kw1.x, kw1.y, kw1.z, kw1.w};
+#pragma unroll
+        for (int s = 0; s < 9; ++s) {
+          unsigned int byte = 255;
+#pragma unroll
+          for (int g3 = 0; g3 < 3; ++g3) {
+            const int idx = g3 * 9 + s;
+            if (g3 == grp) byte = (w[idx >> 2] >> ((idx & 3) * 8)) & 255u;
+          }
+          mt.k[s] = (unsigned char)byte;
+        }
+      }
+      meta[tid] = mt;
+    }
+    double fpart[3] = {0.0, 0.0, 0.0};
+    if (writer) {
+      // G' -> K per block: K = rho G' + G'^T + tr(G') I
+#pragma unroll
+      for (int s = 0; s < 9; ++s) {
+        const double tr = acc[s][0] + acc[s][4] + acc[s][8];
+        double k9[9];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+          for (int j = 0; j < 3; ++j) k9[i * 3 + j] = fma(rho, acc[s][i * 3 + j], acc[s][j * 3 + i]) + (i == j ? tr : 0.0);
+#pragma unroll
+        for (int q = 0; q < 9; ++q) acc[s][q] = k9[q];
+      }
+      if (WITH_F) {
+        // partial f = sum over this group's 9 neighbours K_rc u_c; neighbour (dx,dy) of plane lay+dz
+        const int nl = lay + grp - 1;
+        const double *ub = ulay + ((nl & 1) ? UL * 3 : 0);
+#pragma unroll
+        for (int s = 0; s < 9; ++s) {
+          const double *uc = ub + ((py + s / 3) * UX + (px + s % 3)) * 3;
+          const double u0 = uc[0], u1 = uc[1], u2 = uc[2];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) fpart[i] += acc[s][i * 3] * u0 + acc[s][i * 3 + 1] * u1 + acc[s][i * 3 + 2] * u2;
+        }
+      }
+    }
+    if (WITH_F) {
+      // f of the lower node = carry(dz=-1, previous step) + dz=0 (finisher) + dz=+1 (role 3)
+      const int src3 = (lane & ~3) + 3;
+      double f3[3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) f3[i] = __shfl_sync(0xffffffffu, fpart[i], src3);
+      if (isA && r >= 0) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+          fint[3ll * (dm.nl2g[r] - 1) + i] = (fcarry[p * 3 + i] + fpart[i]) + f3[i];
+      }
+      __syncwarp();
+      if (role == 0) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) fcarry[p * 3 + i] = r >= 0 ? fpart[i] : 0.0;
+      }
+    }
+    __syncwarp();
+    double *st = stage + warp * (32 * 27);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      if (writer) {
+#pragma unroll
+        for (int s = 0; s < 9; ++s)
+#pragma unroll
+          for (int j = 0; j < 3; ++j) st[lane * 27 + s * 3 + j] = acc[s][i * 3 + j];
+      }
+      __syncwarp();
+      for (int t = 0; t < 32; ++t) {
+        const RunMeta &mt = meta[warp * 32 + t];
+        if (mt.nb == 0) continue;
+        if (lane < 27) {
+          const int k = mt.k[lane / 3];
+          if (k != 255) vals[mt.base + (long long)i * 3 * mt.nb + 3 * k + lane % 3] = st[t * 27 + lane];
+        }
+      }
+      __syncwarp();
+    }
+    if (isA) {
+#pragma unroll
+      for (int s = 0; s < 9; ++s)
+#pragma unroll
+        for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
+    }
+    __syncthreads();
+  }
+}
+
+template <int TX, int TY>
+size_t fused_smem_bytes(bool with_f) {
+  constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
+  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 27);
+  if (with_f) b += sizeof(double) * (2 * UL * 3 + NP * 3);
+  b += sizeof(RunMeta) * NT + sizeof(int) * EL;
+  return b;
+}
+
+template <int TX, int TY>
+int launch_tile(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int LZ) {
+  const DevHex &hx = c->dhex;
+  dim3 grid((hx.NI + TX - 1) / TX, (hx.NJ + TY - 1) / TY, (hx.NK + LZ - 1) / LZ);
+  const bool wf = d_u != nullptr;
+  const size_t smem = fused_smem_bytes<TX, TY>(wf);
+  if (wf) {
+    cudaFuncSetAttribute(hex_fused_kernel<TX, TY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    hex_fused_kernel<TX, TY, true><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ);
+  } else {
+    cudaFuncSetAttribute(hex_fused_kernel<TX, TY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    hex_fused_kernel<TX, TY, false><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ);
+  }
+  return 1;
+}
+
+}  // namespace
+
+int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+  const int tile = c->opts.reserved[0];      // 0 = default tile; bench sweeps set it
+  const int want = c->opts.reserved[1] > 0 ? c->opts.reserved[1] : 25;   // node layers per z-chunk
+  const int nchunk = (c->dhex.NK + want / 2) / want > 0 ? (c->dhex.NK + want / 2) / want : 1;
+  const int LZ = (c->dhex.NK + nchunk - 1) / nchunk;
+  switch (tile) {
+    case 1: return launch_tile<8, 8>(c, d_u, d_vals, d_fint, LZ);
+    case 2: return launch_tile<8, 6>(c, d_u, d_vals, d_fint, LZ);
+    default: return launch_tile<8, 4>(c, d_u, d_vals, d_fint, LZ);
+  }
+}
+
+}  // namespace femx

@@ -232,3 +232,75 @@ def test_large_mesh_properties(fx):
     G = 1e-3 * np.array([[1, 2, 0], [0, -1, 3], [2, 0, 1.0]])
     s = fx.stress(x @ G.T)
     assert np.abs(s - s[0]).max() <= 1e-9 * np.abs(s[0]).max()
+
+
+def _permuted(m, seed):
+    """Same mesh, random node numbering (exercises non-contiguous kmap runs)."""
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(m.nlnds)            # new id of old node i = perm[i]
+    inv = np.argsort(perm)
+    return dataclasses.replace(m, eind=(perm[m.eind - 1] + 1).astype(np.int32), coords=m.coords[inv],
+                               bcnode=np.zeros((0, 4), np.int32), bcval=np.zeros((0, 3)))
+
+
+def _l_shaped(n):
+    """Hex cube with one octant of elements removed; unused nodes dropped and renumbered."""
+    g = mg.jitter(mg.hex_cube(n, clamp=False))
+    conn = g.eind.reshape(-1, 8)
+    cen = g.coords[conn - 1].mean(1)
+    keep = ~((cen[:, 0] > n / 2) & (cen[:, 1] > n / 2) & (cen[:, 2] > n / 2))
+    conn = conn[keep]
+    used = np.unique(conn)
+    remap = np.zeros(g.nlnds + 1, np.int64)
+    remap[used] = np.arange(1, len(used) + 1)
+    return fm.from_uniform(3, fm.HEX, remap[conn], g.coords[used - 1])
+
+
+def test_fused_hex_variant_vs_oracle_and_twopass(orc):
+    g = mg.jitter(mg.hex_cube(7))
+    cases = {
+        "box_9x5x11": mg.hex_block(9, 5, 11),
+        "cube17_chunks": mg.jitter(mg.hex_cube(17, clamp=False)),
+        "permuted": _permuted(mg.jitter(mg.hex_cube(6, clamp=False)), 3),
+        "l_shaped": _l_shaped(8),
+        "rank2of3": fm.localize(g, mg.slab_partition(g, 3), 2),
+        "two_materials": dataclasses.replace(mg.jitter(mg.hex_cube(5, clamp=False)),
+                                             mat=np.array([[3e10, .25, 0, 0, 0], [7e9, .25, 0, 0, 0]]),
+                                             emat=(np.arange(125) % 2 + 1).astype(np.int32)),
+    }
+    for name, m in cases.items():
+        m = dataclasses.replace(m, bcnode=np.zeros((0, 4), np.int32), bcval=np.zeros((0, 3)))
+        u = mg.displacement_field(m)
+        om = orc.Mesh(m)
+        rp_o, ci_o, va_o = orc.assemble_K(om).export(om.ndof)
+        f_o = orc.fint(om, u.reshape(-1))
+        for tile in (0, 1, 2):
+            for lz in (25, 3):
+                f = api.Femx(quirks=api.Q_REFERENCE, assembly_variant=2, tile=tile, lz=lz)
+                f.set_mesh(m).build_plan()
+                rp, ci = f.pattern()
+                assert np.array_equal(rp, rp_o) and np.array_equal(ci, ci_o), name
+                vals, fint = f.assemble_K_fint(u)
+                assert close(vals, va_o, TOL_MAT), (name, tile, lz)
+                assert close(fint, f_o, TOL_MAT), (name, tile, lz)
+                assert np.array_equal(f.assemble_K(), vals), (name, tile, lz)     # K-only kernel, same bits
+                f.close()
+        with api.Femx(assembly_variant=1) as f1:
+            v1 = f1.set_mesh(m).build_plan().assemble_K()
+        assert close(v1, va_o, TOL_MAT), name
+
+
+def test_variant2_refuses_unqualified_mesh():
+    m = mg.tet_cube(2)
+    with api.Femx(assembly_variant=2) as f:
+        f.set_mesh(m)
+        with pytest.raises(api.FemxError, match="does not qualify"):
+            f.build_plan()
+    m2 = dataclasses.replace(mg.hex_cube(3, clamp=False), mat=np.array([[3e10, .25, 0, 0, 0], [3e10, .3, 0, 0, 0]]),
+                             emat=(np.arange(27) % 2 + 1).astype(np.int32))
+    with api.Femx(assembly_variant=2) as f:
+        f.set_mesh(m2)
+        with pytest.raises(api.FemxError, match="Poisson"):
+            f.build_plan()
+    with api.Femx(assembly_variant=0) as f:        # auto: falls back to the two-pass path
+        assert f.set_mesh(m2).build_plan().assemble_K().shape[0] == f.nnz
