@@ -226,7 +226,6 @@ int femx_build_plan(femx_ctx *c) {
   UP(c->d_cnode_ptr, P.cnode_ptr); UP(c->d_cnode_src, P.cnode_src);
   if ((rc = dev_alloc(c, &c->d_coh_ke, 64 * (int64_t)P.coh_elems.size()))) return rc;
   if ((rc = dev_alloc(c, &c->d_coh_fe, 8 * (int64_t)P.coh_elems.size()))) return rc;
-#undef UP
   // fused hex8 path (variant 2): only if the mesh provably is a logical grid of hex8
   c->hex = femx::HexPlan();
   if (c->opts.assembly_variant != 1) {
