@@ -239,6 +239,10 @@ int femx_build_plan(femx_ctx *c) {
         for (int d = 0; d < 3; ++d) c4[(size_t)i * 4 + d] = c->coords[(size_t)i * 3 + d];
       for (int m = 0; m < c->nmts; ++m) smu[m] = std::sqrt(lm[2 * m + 1]);
       UP(hx.coords4, c4); UP(hx.sqrt_mu, smu);
+      std::vector<double> cm(c->hex.elem_at.size(), 0.0);
+      for (size_t q = 0; q < cm.size(); ++q)
+        if (c->hex.elem_at[q] >= 0) cm[q] = smu[c->emat[c->hex.elem_at[q]] - 1];
+      UP(hx.cellmu, cm);
     } else if (c->opts.assembly_variant == 2) {
       c->err = "assembly_variant 2 requested but the mesh does not qualify: " + c->hex.why;
       return FEMX_ERR_UNSUPPORTED;

@@ -69,6 +69,7 @@ struct DevHex {
   uint8_t *kmap = nullptr;
   double *coords4 = nullptr;        // [nlnds][4] padded coordinates (128-bit loads)
   double *sqrt_mu = nullptr;        // [nmts]
+  double *cellmu = nullptr;         // [NK][NJ][NI] sqrt(mu) of the element in that cell, 0 = no element
 };
 int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,
                    HexPlan *H, std::string *why);

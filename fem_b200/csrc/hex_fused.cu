@@ -25,8 +25,13 @@ constexpr int kGeoStride = 194;   // doubles per element: 8*24 + 2 pad -> 16B-un
 
 struct RunMeta {       // destination of one thread's 9 blocks for the current step
   long long base;      // slot of (row i = 0, block position 0)
-  int nb;              // blocks in the node's row, 0 = nothing to store
+  int nb;              // blocks in the node's row
   unsigned char k[12]; // block position per canonical slot (255 = absent)
+};
+struct RowMeta {       // per cached node: where its row lives in the CSR value array
+  long long base;
+  int nb;
+  unsigned char k[28]; // [dz][dy][dx] -> block position, 255 = absent
 };
 
 __device__ __forceinline__ int hs_index(int sx, int sy) { return sy ? (sx ? 2 : 3) : (sx ? 1 : 0); }
@@ -41,18 +46,20 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]
   double *stage = geo + EL * kGeoStride;                                 // [NW][32][27]
-  double *ulay = stage + NW * 32 * 27;                                   // [2][UL][3]   (WITH_F)
-  double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]      (WITH_F)
-  RunMeta *meta = reinterpret_cast<RunMeta *>(fcarry + (WITH_F ? NP * 3 : 0));  // [NT]
-  int *eid = reinterpret_cast<int *>(meta + NT);                         // [EL]
+  double *xlay = stage + NW * 32 * 27;                                   // [2][UL][3] node coordinates
+  double *ulay = xlay + 2 * UL * 3;                                      // [2][UL][3] displacements (WITH_F)
+  double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]              (WITH_F)
+  double *esc = fcarry + (WITH_F ? NP * 3 : 0);                          // [EL] sqrt(mu) of the cell, 0 = absent
+  RowMeta *rowmeta = reinterpret_cast<RowMeta *>(esc + EL);              // [2][NP]
+  RunMeta *meta = reinterpret_cast<RunMeta *>(rowmeta + 2 * NP);         // [NT]
+  int *nid = reinterpret_cast<int *>(meta + NT);                         // [2][UL] node id, -1 = absent
+  unsigned char *wlist = reinterpret_cast<unsigned char *>(nid + 2 * UL);  // [NW][32] compacted writer lanes
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int p = tid >> 2, role = tid & 3;
   const int px = p % TX, py = p / TX;
   const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
   const int l0 = blockIdx.z * LZ, l1 = min(l0 + LZ, hx.NK) - 1;
-  const int gi = i0 + px, gj = j0 + py;
-  const bool in_xy = gi < hx.NI && gj < hx.NJ;
   const double rho = hx.rho;
 
   double acc[9][9];
@@ -61,23 +68,49 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
     for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
 
-  // displacement of one node layer (halo included) into buffer lay&1
-  auto load_u_layer = [&](int lay) {
-    double *ub = ulay + ((lay & 1) ? UL * 3 : 0);
+  // one node layer (halo included) into buffer lay&1: ids, coordinates, displacements, row metadata
+  auto load_layer = [&](int lay) {
+    const int buf = lay & 1;
     for (int t = tid; t < UL; t += NT) {
-      const int ni = i0 - 1 + t % UX, nj = j0 - 1 + t / UX;
+      const int ux = t % UX, uy = t / UX;
+      const int ni = i0 - 1 + ux, nj = j0 - 1 + uy;
       int r = -1;
       if (lay >= 0 && lay < hx.NK && ni >= 0 && nj >= 0 && ni < hx.NI && nj < hx.NJ)
         r = hx.node_at[((long long)lay * hx.NJ + nj) * hx.NI + ni];
-      ub[t * 3 + 0] = r >= 0 ? u[(long long)r * 3 + 0] : 0.0;
-      ub[t * 3 + 1] = r >= 0 ? u[(long long)r * 3 + 1] : 0.0;
-      ub[t * 3 + 2] = r >= 0 ? u[(long long)r * 3 + 2] : 0.0;
+      nid[buf * UL + t] = r;
+      double x0 = 0.0, x1 = 0.0, x2 = 0.0;
+      if (r >= 0) {
+        const double2 xy = *reinterpret_cast<const double2 *>(hx.coords4 + (long long)r * 4);
+        x0 = xy.x; x1 = xy.y; x2 = hx.coords4[(long long)r * 4 + 2];
+      }
+      double *xb = xlay + (buf * UL + t) * 3;
+      xb[0] = x0; xb[1] = x1; xb[2] = x2;
+      if (WITH_F) {
+        double *ub = ulay + (buf * UL + t) * 3;
+        ub[0] = r >= 0 ? u[(long long)r * 3 + 0] : 0.0;
+        ub[1] = r >= 0 ? u[(long long)r * 3 + 1] : 0.0;
+        ub[2] = r >= 0 ? u[(long long)r * 3 + 2] : 0.0;
+      }
+      if (ux >= 1 && ux <= TX && uy >= 1 && uy <= TY) {
+        RowMeta *rm = rowmeta + buf * NP + (uy - 1) * TX + (ux - 1);
+        if (r >= 0 && lay >= l0 && lay <= l1) {
+          const long long b0 = dm.bptr[r];
+          rm->base = 9 * b0;
+          rm->nb = (int)(dm.bptr[r + 1] - b0);
+          const uint4 kw0 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32);
+          const uint4 kw1 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32 + 16);
+          uint4 *kd = reinterpret_cast<uint4 *>(rm->k - 4);   // k starts 12 bytes into the struct; copy as words
+          (void)kd;
+          unsigned int *kw = reinterpret_cast<unsigned int *>(rm->k);
+          kw[0] = kw0.x; kw[1] = kw0.y; kw[2] = kw0.z; kw[3] = kw0.w; kw[4] = kw1.x; kw[5] = kw1.y; kw[6] = kw1.z;
+        } else {
+          rm->nb = 0;
+        }
+      }
     }
   };
-  if (WITH_F) {
-    if (tid < NP * 3) fcarry[tid] = 0.0;
-    load_u_layer(l0 - 1);
-  }
+  if (WITH_F && tid < NP * 3) fcarry[tid] = 0.0;
+  load_layer(l0 - 1);
   __syncthreads();
 
   for (int m = l0 - 1; m <= l1; ++m) {
@@ -85,63 +118,64 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
     const bool layer_ok = m >= 0 && m < hx.NK - 1;
     for (int t = tid; t < EL; t += NT) {
       const int ei = i0 - 1 + t % EX, ej = j0 - 1 + t / EX;
-      int e = -1;
+      double sm = 0.0;
       if (layer_ok && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
-        e = hx.elem_at[((long long)m * hx.NJ + ej) * hx.NI + ei];
-      eid[t] = e;
+        sm = hx.cellmu[((long long)m * hx.NJ + ej) * hx.NI + ei];
+      esc[t] = sm;
     }
-    if (WITH_F) load_u_layer(m + 1);   // layer m is already resident in the other buffer
+    load_layer(m + 1);   // layer m is resident in the other buffer
     __syncthreads();
-    for (int item = tid; item < EL * 8; item += NT) {
-      const int es = item % EL, ip = item / EL;
-      const int e = eid[es];
-      if (e < 0) continue;
-      double X[8][3];
-      const int4 c0 = *reinterpret_cast<const int4 *>(dm.conn0 + (long long)e * 8);
-      const int4 c1 = *reinterpret_cast<const int4 *>(dm.conn0 + (long long)e * 8 + 4);
-      const int nd[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    {
+      const double *xlo = xlay + ((m & 1) ? UL * 3 : 0), *xhi = xlay + (((m + 1) & 1) ? UL * 3 : 0);
+      for (int item = tid; item < EL * 8; item += NT) {
+        const int es = item % EL, ip = item / EL;
+        const double smu = esc[es];
+        if (smu == 0.0) continue;
+        const int ex = es % EX, ey = es / EX;
+        double X[8][3];
 #pragma unroll
-      for (int b = 0; b < 8; ++b) {
-        const double2 xy = *reinterpret_cast<const double2 *>(hx.coords4 + (long long)nd[b] * 4);
-        X[b][0] = xy.x; X[b][1] = xy.y; X[b][2] = hx.coords4[(long long)nd[b] * 4 + 2];
-      }
-      double dN[3][8];
-      parent_grad<FEMX_HEX>(ip, dN);
-      double J[3][3];
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-          double s = 0.0;
-#pragma unroll
-          for (int a = 0; a < 8; ++a) s += dN[i][a] * X[a][j];
-          J[i][j] = s;
+        for (int b = 0; b < 8; ++b) {
+          const int bx = (b == 1 || b == 2 || b == 5 || b == 6) ? 1 : 0, by = ((b & 3) >= 2) ? 1 : 0;
+          const double *xs = (b >= 4 ? xhi : xlo) + ((ey + by) * UX + (ex + bx)) * 3;
+          X[b][0] = xs[0]; X[b][1] = xs[1]; X[b][2] = xs[2];
         }
-      // adjugate (inverse * det): inv[i][j] = adj[i][j] / det
-      double adj[3][3];
-      adj[0][0] = J[1][1] * J[2][2] - J[1][2] * J[2][1];
-      adj[0][1] = J[0][2] * J[2][1] - J[0][1] * J[2][2];
-      adj[0][2] = J[0][1] * J[1][2] - J[0][2] * J[1][1];
-      adj[1][0] = J[1][2] * J[2][0] - J[1][0] * J[2][2];
-      adj[1][1] = J[0][0] * J[2][2] - J[0][2] * J[2][0];
-      adj[1][2] = J[0][2] * J[1][0] - J[0][0] * J[1][2];
-      adj[2][0] = J[1][0] * J[2][1] - J[1][1] * J[2][0];
-      adj[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
-      adj[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
-      const double det = J[0][0] * adj[0][0] + J[0][1] * adj[1][0] + J[0][2] * adj[2][0];
-      const double sc = hx.sqrt_mu[dm.emat[e] - 1] * sqrt(1.0 / det);   // hex weights are 1 (src/m_elems.F90:508)
+        double dN[3][8];
+        parent_grad<FEMX_HEX>(ip, dN);
+        double J[3][3];
 #pragma unroll
-      for (int i = 0; i < 3; ++i)
+        for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int j = 0; j < 3; ++j) adj[i][j] *= sc;
-      double *g = geo + es * kGeoStride + ip * 24;
+          for (int j = 0; j < 3; ++j) {
+            double s = 0.0;
 #pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        double row[8];
+            for (int a = 0; a < 8; ++a) s += dN[i][a] * X[a][j];
+            J[i][j] = s;
+          }
+        double adj[3][3];   // inverse * det
+        adj[0][0] = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+        adj[0][1] = J[0][2] * J[2][1] - J[0][1] * J[2][2];
+        adj[0][2] = J[0][1] * J[1][2] - J[0][2] * J[1][1];
+        adj[1][0] = J[1][2] * J[2][0] - J[1][0] * J[2][2];
+        adj[1][1] = J[0][0] * J[2][2] - J[0][2] * J[2][0];
+        adj[1][2] = J[0][2] * J[1][0] - J[0][0] * J[1][2];
+        adj[2][0] = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+        adj[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
+        adj[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+        const double det = J[0][0] * adj[0][0] + J[0][1] * adj[1][0] + J[0][2] * adj[2][0];
+        const double sc = smu * sqrt(1.0 / det);   // hex weights are 1 (src/m_elems.F90:508)
 #pragma unroll
-        for (int b = 0; b < 8; ++b) row[b] = adj[i][0] * dN[0][b] + adj[i][1] * dN[1][b] + adj[i][2] * dN[2][b];
+        for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int b = 0; b < 8; b += 2) *reinterpret_cast<double2 *>(g + i * 8 + b) = make_double2(row[b], row[b + 1]);
+          for (int j = 0; j < 3; ++j) adj[i][j] *= sc;
+        double *g = geo + es * kGeoStride + ip * 24;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          double row[8];
+#pragma unroll
+          for (int b = 0; b < 8; ++b) row[b] = adj[i][0] * dN[0][b] + adj[i][1] * dN[1][b] + adj[i][2] * dN[2][b];
+#pragma unroll
+          for (int b = 0; b < 8; b += 2) *reinterpret_cast<double2 *>(g + i * 8 + b) = make_double2(row[b], row[b + 1]);
+        }
       }
     }
     __syncthreads();
@@ -151,9 +185,8 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
     const bool isA = (role == 1 + par), isB = (role == 2 - par);
     const bool upper = role == 0 || isB;                 // works on node layer m+1
     const int lay = upper ? m + 1 : m;
-    const bool lay_ok = lay >= l0 && lay <= l1;
-    int r = -1;
-    if (in_xy && lay_ok) r = hx.node_at[((long long)lay * hx.NJ + gj) * hx.NI + gi];
+    const RowMeta *rm = rowmeta + (lay & 1) * NP + p;
+    const bool active = rm->nb > 0;                      // node exists and its layer belongs to this chunk
     const int atop = upper ? 4 : 0;                      // our node sits on the top face of layer-m elements
     const int btop = (role == 3 || isB) ? 4 : 0;
     if (!isA) {
@@ -162,13 +195,13 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
         for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
     }
-    if (r >= 0) {
+    if (active) {
 #pragma unroll
       for (int oy = 0; oy < 2; ++oy)
 #pragma unroll
         for (int ox = 0; ox < 2; ++ox) {
           const int es = (py + oy) * EX + (px + ox);
-          if (eid[es] < 0) continue;
+          if (esc[es] == 0.0) continue;
           const double *g = geo + es * kGeoStride;
           const int a = hs_index(1 - ox, 1 - oy) + atop;
 #pragma unroll 2
@@ -195,31 +228,18 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
         }
     }
     // ------------------------------------------------------------ store the groups completed by this step
-    const bool writer = r >= 0 && !isB;
+    const bool writer = active && !isB;
     const int grp = role == 0 ? 0 : (role == 3 ? 2 : 1);       // dz = -1, 0, +1
-    {
+    const unsigned wmask = __ballot_sync(0xffffffffu, writer);
+    const int nW = __popc(wmask);
+    if (writer) {
       RunMeta mt;
-      mt.nb = 0;
-      mt.base = 0;
-      if (writer) {
-        const long long b0 = dm.bptr[r];
-        mt.nb = (int)(dm.bptr[r + 1] - b0);
-        mt.base = 9 * b0;
-        const uint4 kw0 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32);
-        const uint4 kw1 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32 + 16);
-        const unsigned int w[8] = {kw0.x, kw0.y, kw0.z, kw0.w, kw1.x, kw1.y, kw1.z, kw1.w};
+      mt.base = rm->base;
+      mt.nb = rm->nb;
 #pragma unroll
-        for (int s = 0; s < 9; ++s) {
-          unsigned int byte = 255;
-#pragma unroll
-          for (int g3 = 0; g3 < 3; ++g3) {
-            const int idx = g3 * 9 + s;
-            if (g3 == grp) byte = (w[idx >> 2] >> ((idx & 3) * 8)) & 255u;
-          }
-          mt.k[s] = (unsigned char)byte;
-        }
-      }
+      for (int s = 0; s < 9; ++s) mt.k[s] = rm->k[grp * 9 + s];
       meta[tid] = mt;
+      wlist[warp * 32 + __popc(wmask & ((1u << lane) - 1u))] = (unsigned char)lane;
     }
     double fpart[3] = {0.0, 0.0, 0.0};
     if (writer) {
@@ -254,7 +274,8 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       double f3[3];
 #pragma unroll
       for (int i = 0; i < 3; ++i) f3[i] = __shfl_sync(0xffffffffu, fpart[i], src3);
-      if (isA && r >= 0) {
+      if (isA && active) {
+        const int r = nid[(lay & 1) * UL + (py + 1) * UX + (px + 1)];
 #pragma unroll
         for (int i = 0; i < 3; ++i)
           fint[3ll * (dm.nl2g[r] - 1) + i] = (fcarry[p * 3 + i] + fpart[i]) + f3[i];
@@ -262,11 +283,13 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       __syncwarp();
       if (role == 0) {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) fcarry[p * 3 + i] = r >= 0 ? fpart[i] : 0.0;
+        for (int i = 0; i < 3; ++i) fcarry[p * 3 + i] = active ? fpart[i] : 0.0;
       }
     }
     __syncwarp();
     double *st = stage + warp * (32 * 27);
+    const RunMeta *wm = meta + warp * 32;
+    const unsigned char *wl = wlist + warp * 32;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       if (writer) {
@@ -276,21 +299,16 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
           for (int j = 0; j < 3; ++j) st[lane * 27 + s * 3 + j] = acc[s][i * 3 + j];
       }
       __syncwarp();
-      for (int t = 0; t < 32; ++t) {
-        const RunMeta &mt = meta[warp * 32 + t];
-        if (mt.nb == 0) continue;
-        if (lane < 27) {
-          const int k = mt.k[lane / 3];
-          if (k != 255) vals[mt.base + (long long)i * 3 * mt.nb + 3 * k + lane % 3] = st[t * 27 + lane];
-        }
+      // all lanes in parallel over the flattened (writer, 27 values) list: contiguous runs in global memory
+#pragma unroll 4
+      for (int q = lane; q < nW * 27; q += 32) {
+        const int w = q / 27, idx = q - w * 27;
+        const int t = wl[w];
+        const RunMeta &mt = wm[t];
+        const int k = mt.k[idx / 3];
+        if (k != 255) vals[mt.base + (long long)(i * 3 * mt.nb + 3 * k + idx % 3)] = st[t * 27 + idx];
       }
       __syncwarp();
-    }
-    if (isA) {
-#pragma unroll
-      for (int s = 0; s < 9; ++s)
-#pragma unroll
-        for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
     }
     __syncthreads();
   }
@@ -299,9 +317,9 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 template <int TX, int TY>
 size_t fused_smem_bytes(bool with_f) {
   constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
-  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 27);
+  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 27 + 2 * UL * 3 + EL);
   if (with_f) b += sizeof(double) * (2 * UL * 3 + NP * 3);
-  b += sizeof(RunMeta) * NT + sizeof(int) * EL;
+  b += sizeof(RowMeta) * 2 * NP + sizeof(RunMeta) * NT + sizeof(int) * 2 * UL + NW * 32;
   return b;
 }
 
