@@ -24,8 +24,8 @@ namespace {
 constexpr int kGeoStride = 194;   // doubles per element: 8*24 + 2 pad -> 16B-unit stride 97 (odd)
 
 struct RunMeta {       // destination of one thread's 9 blocks for the current step
-  long long base;      // slot of (row i = 0, block position 0)
-  int nb;              // blocks in the node's row
+  double *row0;        // &vals[slot of (row i = 0, block position 0)]
+  int stride;          // doubles between scalar rows of the node: 3 * nb
   unsigned char k[12]; // block position per canonical slot (255 = absent)
 };
 struct RowMeta {       // per cached node: where its row lives in the CSR value array
@@ -45,15 +45,14 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
   constexpr int UX = TX + 2, UY = TY + 2, UL = UX * UY;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]
-  double *stage = geo + EL * kGeoStride;                                 // [NW][32][27]
-  double *xlay = stage + NW * 32 * 27;                                   // [2][UL][3] node coordinates
+  double *stage = geo + EL * kGeoStride;                                 // [NW][32][28]
+  double *xlay = stage + NW * 32 * 28;                                   // [2][UL][3] node coordinates
   double *ulay = xlay + 2 * UL * 3;                                      // [2][UL][3] displacements (WITH_F)
   double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]              (WITH_F)
   double *esc = fcarry + (WITH_F ? NP * 3 : 0);                          // [EL] sqrt(mu) of the cell, 0 = absent
   RowMeta *rowmeta = reinterpret_cast<RowMeta *>(esc + EL);              // [2][NP]
   RunMeta *meta = reinterpret_cast<RunMeta *>(rowmeta + 2 * NP);         // [NT]
   int *nid = reinterpret_cast<int *>(meta + NT);                         // [2][UL] node id, -1 = absent
-  unsigned char *wlist = reinterpret_cast<unsigned char *>(nid + 2 * UL);  // [NW][32] compacted writer lanes
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int p = tid >> 2, role = tid & 3;
@@ -99,8 +98,6 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
           rm->nb = (int)(dm.bptr[r + 1] - b0);
           const uint4 kw0 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32);
           const uint4 kw1 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32 + 16);
-          uint4 *kd = reinterpret_cast<uint4 *>(rm->k - 4);   // k starts 12 bytes into the struct; copy as words
-          (void)kd;
           unsigned int *kw = reinterpret_cast<unsigned int *>(rm->k);
           kw[0] = kw0.x; kw[1] = kw0.y; kw[2] = kw0.z; kw[3] = kw0.w; kw[4] = kw1.x; kw[5] = kw1.y; kw[6] = kw1.z;
         } else {
@@ -231,15 +228,13 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
     const bool writer = active && !isB;
     const int grp = role == 0 ? 0 : (role == 3 ? 2 : 1);       // dz = -1, 0, +1
     const unsigned wmask = __ballot_sync(0xffffffffu, writer);
-    const int nW = __popc(wmask);
     if (writer) {
       RunMeta mt;
-      mt.base = rm->base;
-      mt.nb = rm->nb;
+      mt.row0 = vals + rm->base;
+      mt.stride = 3 * rm->nb;
 #pragma unroll
       for (int s = 0; s < 9; ++s) mt.k[s] = rm->k[grp * 9 + s];
       meta[tid] = mt;
-      wlist[warp * 32 + __popc(wmask & ((1u << lane) - 1u))] = (unsigned char)lane;
     }
     double fpart[3] = {0.0, 0.0, 0.0};
     if (writer) {
@@ -287,26 +282,35 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       }
     }
     __syncwarp();
-    double *st = stage + warp * (32 * 27);
+    double *st = stage + warp * (32 * 28);
     const RunMeta *wm = meta + warp * 32;
-    const unsigned char *wl = wlist + warp * 32;
+    const int slot = lane / 3, jj = lane - 3 * slot;       // lane < 27: one value of a 27-double run
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       if (writer) {
+        double2 *dst = reinterpret_cast<double2 *>(st + lane * 28);
+        const double *row = &acc[0][0];
+        (void)row;
 #pragma unroll
-        for (int s = 0; s < 9; ++s)
-#pragma unroll
-          for (int j = 0; j < 3; ++j) st[lane * 27 + s * 3 + j] = acc[s][i * 3 + j];
+        for (int q = 0; q < 13; ++q) {
+          const int q0 = 2 * q, q1 = 2 * q + 1;
+          dst[q] = make_double2(acc[q0 / 3][i * 3 + q0 % 3], acc[q1 / 3][i * 3 + q1 % 3]);
+        }
+        st[lane * 28 + 26] = acc[8][i * 3 + 2];
       }
       __syncwarp();
-      // all lanes in parallel over the flattened (writer, 27 values) list: contiguous runs in global memory
+      // one writer per iteration, 27 lanes each move one double: contiguous 216-byte runs when the
+      // node's neighbours are numbered in canonical order, block-wise scattered otherwise
+      unsigned todo = wmask;
 #pragma unroll 4
-      for (int q = lane; q < nW * 27; q += 32) {
-        const int w = q / 27, idx = q - w * 27;
-        const int t = wl[w];
-        const RunMeta &mt = wm[t];
-        const int k = mt.k[idx / 3];
-        if (k != 255) vals[mt.base + (long long)(i * 3 * mt.nb + 3 * k + idx % 3)] = st[t * 27 + idx];
+      while (todo) {
+        const int t = __ffs(todo) - 1;
+        todo &= todo - 1;
+        if (lane < 27) {
+          const RunMeta &mt = wm[t];
+          const int k = mt.k[slot];
+          if (k != 255) mt.row0[i * mt.stride + 3 * k + jj] = st[t * 28 + lane];
+        }
       }
       __syncwarp();
     }
@@ -317,9 +321,9 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 template <int TX, int TY>
 size_t fused_smem_bytes(bool with_f) {
   constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
-  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 27 + 2 * UL * 3 + EL);
+  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 28 + 2 * UL * 3 + EL);
   if (with_f) b += sizeof(double) * (2 * UL * 3 + NP * 3);
-  b += sizeof(RowMeta) * 2 * NP + sizeof(RunMeta) * NT + sizeof(int) * 2 * UL + NW * 32;
+  b += sizeof(RowMeta) * 2 * NP + sizeof(RunMeta) * NT + sizeof(int) * 2 * UL;
   return b;
 }
 
