@@ -301,17 +301,19 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       __syncwarp();
       // one writer per iteration, 27 lanes each move one double: contiguous 216-byte runs when the
       // node's neighbours are numbered in canonical order, block-wise scattered otherwise
-      unsigned todo = wmask;
-#pragma unroll 4
-      while (todo) {
-        const int t = __ffs(todo) - 1;
-        todo &= todo - 1;
-        if (lane < 27) {
-          const RunMeta &mt = wm[t];
-          const int k = mt.k[slot];
-          if (k != 255) mt.row0[i * mt.stride + 3 * k + jj] = st[t * 28 + lane];
+      // fixed schedule: the three storing roles of each of the warp's 8 positions (unrolled, so the
+      // shared-memory reads of several runs are in flight together)
+#pragma unroll
+      for (int pp = 0; pp < 8; ++pp)
+#pragma unroll
+        for (int ws = 0; ws < 3; ++ws) {
+          const int t = 4 * pp + (ws == 0 ? 0 : (ws == 1 ? 1 + par : 3));
+          if (((wmask >> t) & 1u) && lane < 27) {
+            const RunMeta &mt = wm[t];
+            const int k = mt.k[slot];
+            if (k != 255) mt.row0[i * mt.stride + 3 * k + jj] = st[t * 28 + lane];
+          }
         }
-      }
       __syncwarp();
     }
     __syncthreads();
