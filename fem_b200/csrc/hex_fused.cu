@@ -22,12 +22,8 @@ namespace femx {
 namespace {
 
 constexpr int kGeoStride = 194;   // doubles per element: 8*24 + 2 pad -> 16B-unit stride 97 (odd)
+constexpr int kDumpStride = 82;   // doubles per storing thread: 81 + 1 pad -> 16B-unit stride 41 (odd)
 
-struct RunMeta {       // destination of one thread's 9 blocks for the current step
-  double *row0;        // &vals[slot of (row i = 0, block position 0)]
-  int stride;          // doubles between scalar rows of the node: 3 * nb
-  unsigned char k[12]; // block position per canonical slot (255 = absent)
-};
 struct RowMeta {       // per cached node: where its row lives in the CSR value array
   long long base;
   int nb;
@@ -44,15 +40,15 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
   constexpr int EX = TX + 1, EY = TY + 1, EL = EX * EY;
   constexpr int UX = TX + 2, UY = TY + 2, UL = UX * UY;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]
-  double *stage = geo + EL * kGeoStride;                                 // [NW][32][28]
-  double *xlay = stage + NW * 32 * 28;                                   // [2][UL][3] node coordinates
+  constexpr int GEO = (EL * kGeoStride > NP * 3 * kDumpStride) ? EL * kGeoStride : NP * 3 * kDumpStride;
+  double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]; after the FMA
+                                                                         // loop reused as [NP*3][kDumpStride]
+  double *xlay = geo + GEO;                                              // [2][UL][3] node coordinates
   double *ulay = xlay + 2 * UL * 3;                                      // [2][UL][3] displacements (WITH_F)
   double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]              (WITH_F)
   double *esc = fcarry + (WITH_F ? NP * 3 : 0);                          // [EL] sqrt(mu) of the cell, 0 = absent
   RowMeta *rowmeta = reinterpret_cast<RowMeta *>(esc + EL);              // [2][NP]
-  RunMeta *meta = reinterpret_cast<RunMeta *>(rowmeta + 2 * NP);         // [NT]
-  int *nid = reinterpret_cast<int *>(meta + NT);                         // [2][UL] node id, -1 = absent
+  int *nid = reinterpret_cast<int *>(rowmeta + 2 * NP);                  // [2][UL] node id, -1 = absent
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int p = tid >> 2, role = tid & 3;
@@ -60,6 +56,12 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
   const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
   const int l0 = blockIdx.z * LZ, l1 = min(l0 + LZ, hx.NK) - 1;
   const double rho = hx.rho;
+  int lane_i[3], lane_s[3], lane_j[3];     // value v = it*32 + lane of an 81-value dump -> (row i, slot, j)
+#pragma unroll
+  for (int it = 0; it < 3; ++it) {
+    const int v = min(it * 32 + lane, 80);
+    lane_i[it] = v / 27; lane_s[it] = (v % 27) / 3; lane_j[it] = v % 3;
+  }
 
   double acc[9][9];
 #pragma unroll
@@ -228,14 +230,6 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
     const bool writer = active && !isB;
     const int grp = role == 0 ? 0 : (role == 3 ? 2 : 1);       // dz = -1, 0, +1
     const unsigned wmask = __ballot_sync(0xffffffffu, writer);
-    if (writer) {
-      RunMeta mt;
-      mt.row0 = vals + rm->base;
-      mt.stride = 3 * rm->nb;
-#pragma unroll
-      for (int s = 0; s < 9; ++s) mt.k[s] = rm->k[grp * 9 + s];
-      meta[tid] = mt;
-    }
     double fpart[3] = {0.0, 0.0, 0.0};
     if (writer) {
       // G' -> K per block: K = rho G' + G'^T + tr(G') I
@@ -282,50 +276,49 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       }
     }
     __syncwarp();
-    double *st = stage + warp * (32 * 28);
-    const RunMeta *wm = meta + warp * 32;
-    const int slot = lane / 3, jj = lane - 3 * slot;       // lane < 27: one value of a 27-double run
+    // every warp is done reading the gradients: the buffer becomes the transpose area
+    __syncthreads();
+    if (writer) {
+      double2 *dst = reinterpret_cast<double2 *>(geo + (p * 3 + grp) * kDumpStride);
 #pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      if (writer) {
-        double2 *dst = reinterpret_cast<double2 *>(st + lane * 28);
-        const double *row = &acc[0][0];
-        (void)row;
-#pragma unroll
-        for (int q = 0; q < 13; ++q) {
-          const int q0 = 2 * q, q1 = 2 * q + 1;
-          dst[q] = make_double2(acc[q0 / 3][i * 3 + q0 % 3], acc[q1 / 3][i * 3 + q1 % 3]);
-        }
-        st[lane * 28 + 26] = acc[8][i * 3 + 2];
+      for (int q = 0; q < 40; ++q) {
+        const int v0 = 2 * q, v1 = 2 * q + 1;      // v = i*27 + slot*3 + j
+        dst[q] = make_double2(acc[(v0 % 27) / 3][(v0 / 27) * 3 + v0 % 3], acc[(v1 % 27) / 3][(v1 / 27) * 3 + v1 % 3]);
       }
-      __syncwarp();
-      // one writer per iteration, 27 lanes each move one double: contiguous 216-byte runs when the
-      // node's neighbours are numbered in canonical order, block-wise scattered otherwise
-      // fixed schedule: the three storing roles of each of the warp's 8 positions (unrolled, so the
-      // shared-memory reads of several runs are in flight together)
-#pragma unroll
-      for (int pp = 0; pp < 8; ++pp)
-#pragma unroll
-        for (int ws = 0; ws < 3; ++ws) {
-          const int t = 4 * pp + (ws == 0 ? 0 : (ws == 1 ? 1 + par : 3));
-          if (((wmask >> t) & 1u) && lane < 27) {
-            const RunMeta &mt = wm[t];
-            const int k = mt.k[slot];
-            if (k != 255) mt.row0[i * mt.stride + 3 * k + jj] = st[t * 28 + lane];
-          }
-        }
-      __syncwarp();
+      geo[(p * 3 + grp) * kDumpStride + 80] = acc[8][8];
     }
+    __syncwarp();
+    // 24 storing threads per warp (8 positions x 3 groups); all 32 lanes move the 81 values of one
+    // of them per pass: contiguous 216-byte runs when the node's neighbours are numbered canonically
+#pragma unroll
+    for (int pw = 0; pw < 8; ++pw)
+#pragma unroll
+      for (int g3 = 0; g3 < 3; ++g3) {
+        const int t = 4 * pw + (g3 == 0 ? 0 : (g3 == 1 ? 1 + par : 3));
+        const bool on = (wmask >> t) & 1u;
+        const RowMeta *wr = rowmeta + (((g3 == 0 ? m + 1 : m) & 1) ? NP : 0) + warp * 8 + pw;
+        const double *src = geo + ((warp * 8 + pw) * 3 + g3) * kDumpStride;
+        double *row0 = vals + wr->base;
+        const int stride = 3 * wr->nb;
+#pragma unroll
+        for (int it = 0; it < 3; ++it) {
+          const int v = it * 32 + lane;
+          const int ii = lane_i[it], sl = lane_s[it], jj = lane_j[it];
+          const int k = wr->k[g3 * 9 + sl];
+          if (on && v < 81 && k != 255) row0[ii * stride + 3 * k + jj] = src[v];
+        }
+      }
     __syncthreads();
   }
 }
 
 template <int TX, int TY>
 size_t fused_smem_bytes(bool with_f) {
-  constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
-  size_t b = sizeof(double) * (EL * kGeoStride + NW * 32 * 28 + 2 * UL * 3 + EL);
+  constexpr int NP = TX * TY, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
+  constexpr int GEO = (EL * kGeoStride > NP * 3 * kDumpStride) ? EL * kGeoStride : NP * 3 * kDumpStride;
+  size_t b = sizeof(double) * (GEO + 2 * UL * 3 + EL);
   if (with_f) b += sizeof(double) * (2 * UL * 3 + NP * 3);
-  b += sizeof(RowMeta) * 2 * NP + sizeof(RunMeta) * NT + sizeof(int) * 2 * UL;
+  b += sizeof(RowMeta) * 2 * NP + sizeof(int) * 2 * UL;
   return b;
 }
 
