@@ -125,6 +125,7 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--tile", type=int, default=0)
     ap.add_argument("--lz", type=int, default=0)
+    ap.add_argument("--dbg", type=int, default=0, help="diagnostic: skip parts of the fused kernel (results invalid)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -144,7 +145,7 @@ def main():
 
     from fem_b200 import api
     m, u = build_workload(args.n, world, rank)
-    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz)
+    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz, dbg=args.dbg)
     t0 = time.time()
     fx.set_mesh(m).build_plan()
     plan_s = time.time() - t0

@@ -62,6 +62,11 @@ struct HexPlan {
   std::vector<uint8_t> kmap;        // [nlnds][32]: block position of neighbour (dz,dy,dx), 255 = none
   std::string why;                  // reason the mesh does not qualify
 };
+struct HexRowMeta {                 // 40 bytes, copied to shared memory with five 8-byte cp.async
+  long long base;                   // slot of (row i = 0, block position 0) = 9 * bptr[node]
+  int nb;                           // blocks in the node's row, 0 = no node at this logical position
+  unsigned char k[28];              // [dz][dy][dx] -> block position, 255 = absent
+};
 struct DevHex {
   int NI = 0, NJ = 0, NK = 0;
   double rho = 0.0;
@@ -69,6 +74,8 @@ struct DevHex {
   uint8_t *kmap = nullptr;
   double *coords4 = nullptr;        // [nlnds][4] padded coordinates (128-bit loads)
   double *sqrt_mu = nullptr;        // [nmts]
+  double *pos_x = nullptr;          // [NK][NJ][NI][3] coordinates by logical position
+  HexRowMeta *pos_meta = nullptr;   // [NK][NJ][NI]
   double *cellmu = nullptr;         // [NK][NJ][NI] sqrt(mu) of the element in that cell, 0 = no element
 };
 int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,

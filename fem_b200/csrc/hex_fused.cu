@@ -24,18 +24,24 @@ namespace {
 constexpr int kGeoStride = 194;   // doubles per element: 8*24 + 2 pad -> 16B-unit stride 97 (odd)
 constexpr int kDumpStride = 82;   // doubles per storing thread: 81 + 1 pad -> 16B-unit stride 41 (odd)
 
-struct RowMeta {       // per cached node: where its row lives in the CSR value array
-  long long base;
-  int nb;
-  unsigned char k[28]; // [dz][dy][dx] -> block position, 255 = absent
-};
+using RowMeta = HexRowMeta;   // per node position: where its row lives in the CSR value array
+
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ int hs_index(int sx, int sy) { return sy ? (sx ? 2 : 3) : (sx ? 1 : 0); }
 
 template <int TX, int TY, bool WITH_F>
 __global__ void __launch_bounds__(4 * TX * TY, (TX * TY <= 32) ? 2 : 1)
 hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__restrict__ vals,
-                 double *__restrict__ fint, int LZ) {
+                 double *__restrict__ fint, int LZ, int dbg) {
   constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32;
   constexpr int EX = TX + 1, EY = TY + 1, EL = EX * EY;
   constexpr int UX = TX + 2, UY = TY + 2, UL = UX * UY;
@@ -43,12 +49,13 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
   constexpr int GEO = (EL * kGeoStride > NP * 3 * kDumpStride) ? EL * kGeoStride : NP * 3 * kDumpStride;
   double *geo = reinterpret_cast<double *>(smem_raw);                    // [EL][kGeoStride]; after the FMA
                                                                          // loop reused as [NP*3][kDumpStride]
-  double *xlay = geo + GEO;                                              // [2][UL][3] node coordinates
-  double *ulay = xlay + 2 * UL * 3;                                      // [2][UL][3] displacements (WITH_F)
-  double *fcarry = ulay + (WITH_F ? 2 * UL * 3 : 0);                     // [NP][3]              (WITH_F)
-  double *esc = fcarry + (WITH_F ? NP * 3 : 0);                          // [EL] sqrt(mu) of the cell, 0 = absent
-  RowMeta *rowmeta = reinterpret_cast<RowMeta *>(esc + EL);              // [2][NP]
-  int *nid = reinterpret_cast<int *>(rowmeta + 2 * NP);                  // [2][UL] node id, -1 = absent
+  // node-layer cache, 3 layers deep (two in use, one being prefetched with cp.async)
+  double *xlay = geo + GEO;                                              // [3][UL][3] node coordinates
+  double *ulay = xlay + 3 * UL * 3;                                      // [3][UL][3] displacements (WITH_F)
+  double *fcarry = ulay + (WITH_F ? 3 * UL * 3 : 0);                     // [NP][3]              (WITH_F)
+  double *esc = fcarry + (WITH_F ? NP * 3 : 0);                          // [2][EL] sqrt(mu) of the cell, 0 = absent
+  RowMeta *rowmeta = reinterpret_cast<RowMeta *>(esc + 2 * EL);          // [3][NP]
+  int *nid = reinterpret_cast<int *>(rowmeta + 3 * NP);                  // [4][UL] node id, -1 = absent
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int p = tid >> 2, role = tid & 3;
@@ -69,66 +76,91 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
     for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
 
-  // one node layer (halo included) into buffer lay&1: ids, coordinates, displacements, row metadata
-  auto load_layer = [&](int lay) {
-    const int buf = lay & 1;
+  // ---- asynchronous loaders (global -> shared without registers); a layer is identified by lay,
+  //      ring slots are (lay+3)%3 for data and (lay+4)&3 for node ids
+  auto cell_of = [&](int t, int lay, bool &ok) -> long long {
+    const int ni = i0 - 1 + t % UX, nj = j0 - 1 + t / UX;
+    ok = lay >= 0 && lay < hx.NK && ni >= 0 && nj >= 0 && ni < hx.NI && nj < hx.NJ;
+    return ((long long)lay * hx.NJ + nj) * hx.NI + ni;
+  };
+  auto fetch_nid = [&](int lay) {
+    int *dst = nid + ((lay + 4) & 3) * UL;
     for (int t = tid; t < UL; t += NT) {
-      const int ux = t % UX, uy = t / UX;
-      const int ni = i0 - 1 + ux, nj = j0 - 1 + uy;
-      int r = -1;
-      if (lay >= 0 && lay < hx.NK && ni >= 0 && nj >= 0 && ni < hx.NI && nj < hx.NJ)
-        r = hx.node_at[((long long)lay * hx.NJ + nj) * hx.NI + ni];
-      nid[buf * UL + t] = r;
-      double x0 = 0.0, x1 = 0.0, x2 = 0.0;
-      if (r >= 0) {
-        const double2 xy = *reinterpret_cast<const double2 *>(hx.coords4 + (long long)r * 4);
-        x0 = xy.x; x1 = xy.y; x2 = hx.coords4[(long long)r * 4 + 2];
-      }
+      bool ok;
+      const long long c = cell_of(t, lay, ok);
+      if (ok) cp_async4(dst + t, hx.node_at + c);
+      else dst[t] = -1;
+    }
+  };
+  auto fetch_layer = [&](int lay) {   // needs nid of that layer resident (WITH_F)
+    const int buf = (lay + 3) % 3;
+    for (int t = tid; t < UL; t += NT) {
+      bool ok;
+      const long long c = cell_of(t, lay, ok);
       double *xb = xlay + (buf * UL + t) * 3;
-      xb[0] = x0; xb[1] = x1; xb[2] = x2;
+      if (ok) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) cp_async8(xb + d, hx.pos_x + c * 3 + d);
+      } else {
+        xb[0] = 0.0; xb[1] = 0.0; xb[2] = 0.0;
+      }
       if (WITH_F) {
         double *ub = ulay + (buf * UL + t) * 3;
-        ub[0] = r >= 0 ? u[(long long)r * 3 + 0] : 0.0;
-        ub[1] = r >= 0 ? u[(long long)r * 3 + 1] : 0.0;
-        ub[2] = r >= 0 ? u[(long long)r * 3 + 2] : 0.0;
+        const int r = nid[((lay + 4) & 3) * UL + t];
+        if (r >= 0) {
+#pragma unroll
+          for (int d = 0; d < 3; ++d) cp_async8(ub + d, u + (long long)r * 3 + d);
+        } else {
+          ub[0] = 0.0; ub[1] = 0.0; ub[2] = 0.0;
+        }
       }
+      const int ux = t % UX, uy = t / UX;
       if (ux >= 1 && ux <= TX && uy >= 1 && uy <= TY) {
         RowMeta *rm = rowmeta + buf * NP + (uy - 1) * TX + (ux - 1);
-        if (r >= 0 && lay >= l0 && lay <= l1) {
-          const long long b0 = dm.bptr[r];
-          rm->base = 9 * b0;
-          rm->nb = (int)(dm.bptr[r + 1] - b0);
-          const uint4 kw0 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32);
-          const uint4 kw1 = *reinterpret_cast<const uint4 *>(hx.kmap + (long long)r * 32 + 16);
-          unsigned int *kw = reinterpret_cast<unsigned int *>(rm->k);
-          kw[0] = kw0.x; kw[1] = kw0.y; kw[2] = kw0.z; kw[3] = kw0.w; kw[4] = kw1.x; kw[5] = kw1.y; kw[6] = kw1.z;
+        if (ok) {
+          const double *src = reinterpret_cast<const double *>(hx.pos_meta + c);
+#pragma unroll
+          for (int d = 0; d < 5; ++d) cp_async8(reinterpret_cast<double *>(rm) + d, src + d);
         } else {
           rm->nb = 0;
         }
       }
     }
   };
+  auto fetch_esc = [&](int lay) {     // element layer
+    double *dst = esc + (lay & 1) * EL;
+    for (int t = tid; t < EL; t += NT) {
+      const int ei = i0 - 1 + t % EX, ej = j0 - 1 + t / EX;
+      if (lay >= 0 && lay < hx.NK - 1 && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
+        cp_async8(dst + t, hx.cellmu + ((long long)lay * hx.NJ + ej) * hx.NI + ei);
+      else
+        dst[t] = 0.0;
+    }
+  };
   if (WITH_F && tid < NP * 3) fcarry[tid] = 0.0;
-  load_layer(l0 - 1);
+  fetch_nid(l0 - 1); fetch_nid(l0); fetch_nid(l0 + 1);
+  fetch_esc(l0 - 1);
+  cp_async_wait_all();
+  __syncthreads();
+  fetch_layer(l0 - 1); fetch_layer(l0);
+  cp_async_wait_all();
   __syncthreads();
 
   for (int m = l0 - 1; m <= l1; ++m) {
     // ------------------------------------------------------------ phase A: geometry of element layer m
-    const bool layer_ok = m >= 0 && m < hx.NK - 1;
-    for (int t = tid; t < EL; t += NT) {
-      const int ei = i0 - 1 + t % EX, ej = j0 - 1 + t / EX;
-      double sm = 0.0;
-      if (layer_ok && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
-        sm = hx.cellmu[((long long)m * hx.NJ + ej) * hx.NI + ei];
-      esc[t] = sm;
+    // prefetch what the NEXT steps need; it lands while this step computes
+    if (!(dbg & 8)) {
+      fetch_nid(m + 3);
+      fetch_layer(m + 2);
+      fetch_esc(m + 1);
     }
-    load_layer(m + 1);   // layer m is resident in the other buffer
-    __syncthreads();
+    const double *escm = esc + (m & 1) * EL;
     {
-      const double *xlo = xlay + ((m & 1) ? UL * 3 : 0), *xhi = xlay + (((m + 1) & 1) ? UL * 3 : 0);
+      const double *xlo = xlay + ((m + 3) % 3) * UL * 3, *xhi = xlay + ((m + 4) % 3) * UL * 3;
       for (int item = tid; item < EL * 8; item += NT) {
+        if ((dbg & 2) && m > l0) break;
         const int es = item % EL, ip = item / EL;
-        const double smu = esc[es];
+        const double smu = escm[es];
         if (smu == 0.0) continue;
         const int ex = es % EX, ey = es / EX;
         double X[8][3];
@@ -184,8 +216,8 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
     const bool isA = (role == 1 + par), isB = (role == 2 - par);
     const bool upper = role == 0 || isB;                 // works on node layer m+1
     const int lay = upper ? m + 1 : m;
-    const RowMeta *rm = rowmeta + (lay & 1) * NP + p;
-    const bool active = rm->nb > 0;                      // node exists and its layer belongs to this chunk
+    const RowMeta *rm = rowmeta + ((lay + 3) % 3) * NP + p;
+    const bool active = rm->nb > 0 && lay >= l0 && lay <= l1;   // node exists and its layer belongs to this chunk
     const int atop = upper ? 4 : 0;                      // our node sits on the top face of layer-m elements
     const int btop = (role == 3 || isB) ? 4 : 0;
     if (!isA) {
@@ -194,13 +226,13 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
         for (int q = 0; q < 9; ++q) acc[s][q] = 0.0;
     }
-    if (active) {
+    if (active && !(dbg & 4)) {
 #pragma unroll
       for (int oy = 0; oy < 2; ++oy)
 #pragma unroll
         for (int ox = 0; ox < 2; ++ox) {
           const int es = (py + oy) * EX + (px + ox);
-          if (esc[es] == 0.0) continue;
+          if (escm[es] == 0.0) continue;
           const double *g = geo + es * kGeoStride;
           const int a = hs_index(1 - ox, 1 - oy) + atop;
 #pragma unroll 2
@@ -247,7 +279,7 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       if (WITH_F) {
         // partial f = sum over this group's 9 neighbours K_rc u_c; neighbour (dx,dy) of plane lay+dz
         const int nl = lay + grp - 1;
-        const double *ub = ulay + ((nl & 1) ? UL * 3 : 0);
+        const double *ub = ulay + ((nl + 3) % 3) * UL * 3;
 #pragma unroll
         for (int s = 0; s < 9; ++s) {
           const double *uc = ub + ((py + s / 3) * UX + (px + s % 3)) * 3;
@@ -264,7 +296,7 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
       for (int i = 0; i < 3; ++i) f3[i] = __shfl_sync(0xffffffffu, fpart[i], src3);
       if (isA && active) {
-        const int r = nid[(lay & 1) * UL + (py + 1) * UX + (px + 1)];
+        const int r = nid[((lay + 4) & 3) * UL + (py + 1) * UX + (px + 1)];
 #pragma unroll
         for (int i = 0; i < 3; ++i)
           fint[3ll * (dm.nl2g[r] - 1) + i] = (fcarry[p * 3 + i] + fpart[i]) + f3[i];
@@ -296,7 +328,7 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
       for (int g3 = 0; g3 < 3; ++g3) {
         const int t = 4 * pw + (g3 == 0 ? 0 : (g3 == 1 ? 1 + par : 3));
         const bool on = (wmask >> t) & 1u;
-        const RowMeta *wr = rowmeta + (((g3 == 0 ? m + 1 : m) & 1) ? NP : 0) + warp * 8 + pw;
+        const RowMeta *wr = rowmeta + (((g3 == 0 ? m + 4 : m + 3)) % 3) * NP + warp * 8 + pw;
         const double *src = geo + ((warp * 8 + pw) * 3 + g3) * kDumpStride;
         double *row0 = vals + wr->base;
         const int stride = 3 * wr->nb;
@@ -305,9 +337,10 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
           const int v = it * 32 + lane;
           const int ii = lane_i[it], sl = lane_s[it], jj = lane_j[it];
           const int k = wr->k[g3 * 9 + sl];
-          if (on && v < 81 && k != 255) row0[ii * stride + 3 * k + jj] = src[v];
+          if (on && v < 81 && k != 255 && !(dbg & 1)) row0[ii * stride + 3 * k + jj] = src[v];
         }
       }
+    cp_async_wait_all();
     __syncthreads();
   }
 }
@@ -316,9 +349,9 @@ template <int TX, int TY>
 size_t fused_smem_bytes(bool with_f) {
   constexpr int NP = TX * TY, EL = (TX + 1) * (TY + 1), UL = (TX + 2) * (TY + 2);
   constexpr int GEO = (EL * kGeoStride > NP * 3 * kDumpStride) ? EL * kGeoStride : NP * 3 * kDumpStride;
-  size_t b = sizeof(double) * (GEO + 2 * UL * 3 + EL);
-  if (with_f) b += sizeof(double) * (2 * UL * 3 + NP * 3);
-  b += sizeof(RowMeta) * 2 * NP + sizeof(int) * 2 * UL;
+  size_t b = sizeof(double) * (GEO + 3 * UL * 3 + 2 * EL);
+  if (with_f) b += sizeof(double) * (3 * UL * 3 + NP * 3);
+  b += sizeof(RowMeta) * 3 * NP + sizeof(int) * 4 * UL;
   return b;
 }
 
@@ -330,10 +363,10 @@ int launch_tile(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, 
   const size_t smem = fused_smem_bytes<TX, TY>(wf);
   if (wf) {
     cudaFuncSetAttribute(hex_fused_kernel<TX, TY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_fused_kernel<TX, TY, true><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ);
+    hex_fused_kernel<TX, TY, true><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   } else {
     cudaFuncSetAttribute(hex_fused_kernel<TX, TY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_fused_kernel<TX, TY, false><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ);
+    hex_fused_kernel<TX, TY, false><<<grid, 4 * TX * TY, smem, c->stream>>>(c->dm, hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   }
   return 1;
 }
