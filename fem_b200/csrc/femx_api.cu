@@ -248,12 +248,13 @@ int femx_build_plan(femx_ctx *c) {
       for (size_t q = 0; q < pm.size(); ++q) {
         const int r = c->hex.node_at[q];
         femx::HexRowMeta &mm = pm[q];
-        mm.base = 0; mm.nb = 0;
+        mm.base = 0; mm.nb = 0; mm.grow = 0;
         for (int t = 0; t < 28; ++t) mm.k[t] = 255;
         if (r < 0) continue;
         for (int d = 0; d < 3; ++d) px[q * 3 + d] = c->coords[(size_t)r * 3 + d];
         mm.base = 9 * P.bptr[r];
         mm.nb = (int)(P.bptr[r + 1] - P.bptr[r]);
+        mm.grow = 3 * (c->nl2g[r] - 1);
         for (int t = 0; t < 27; ++t) mm.k[t] = c->hex.kmap[(size_t)r * 32 + t];
       }
       UP(hx.pos_x, px); UP(hx.pos_meta, pm);

@@ -62,9 +62,10 @@ struct HexPlan {
   std::vector<uint8_t> kmap;        // [nlnds][32]: block position of neighbour (dz,dy,dx), 255 = none
   std::string why;                  // reason the mesh does not qualify
 };
-struct HexRowMeta {                 // 40 bytes, copied to shared memory with five 8-byte cp.async
+struct HexRowMeta {                 // 48 bytes, copied to shared memory with six 8-byte cp.async
   long long base;                   // slot of (row i = 0, block position 0) = 9 * bptr[node]
   int nb;                           // blocks in the node's row, 0 = no node at this logical position
+  int grow;                         // first global row of the node: 3 * (nl2g - 1)
   unsigned char k[28];              // [dz][dy][dx] -> block position, 255 = absent
 };
 struct DevHex {

@@ -39,7 +39,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 __device__ __forceinline__ int hs_index(int sx, int sy) { return sy ? (sx ? 2 : 3) : (sx ? 1 : 0); }
 
 template <int TX, int TY, bool WITH_F>
-__global__ void __launch_bounds__(4 * TX * TY, (TX * TY <= 32) ? 2 : 1)
+__global__ void __launch_bounds__(4 * TX * TY, (TX * TY <= 16) ? 4 : ((TX * TY <= 32) ? 2 : 1))
 hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__restrict__ vals,
                  double *__restrict__ fint, int LZ, int dbg) {
   constexpr int NP = TX * TY, NT = 4 * NP, NW = NT / 32;
@@ -120,7 +120,7 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
         if (ok) {
           const double *src = reinterpret_cast<const double *>(hx.pos_meta + c);
 #pragma unroll
-          for (int d = 0; d < 5; ++d) cp_async8(reinterpret_cast<double *>(rm) + d, src + d);
+          for (int d = 0; d < 6; ++d) cp_async8(reinterpret_cast<double *>(rm) + d, src + d);
         } else {
           rm->nb = 0;
         }
@@ -296,10 +296,8 @@ hex_fused_kernel(DevMesh dm, DevHex hx, const double *__restrict__ u, double *__
 #pragma unroll
       for (int i = 0; i < 3; ++i) f3[i] = __shfl_sync(0xffffffffu, fpart[i], src3);
       if (isA && active) {
-        const int r = nid[((lay + 4) & 3) * UL + (py + 1) * UX + (px + 1)];
 #pragma unroll
-        for (int i = 0; i < 3; ++i)
-          fint[3ll * (dm.nl2g[r] - 1) + i] = (fcarry[p * 3 + i] + fpart[i]) + f3[i];
+        for (int i = 0; i < 3; ++i) fint[(long long)rm->grow + i] = (fcarry[p * 3 + i] + fpart[i]) + f3[i];
       }
       __syncwarp();
       if (role == 0) {
@@ -374,14 +372,17 @@ int launch_tile(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, 
 }  // namespace
 
 int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
-  const int tile = c->opts.reserved[0];      // 0 = default tile; bench sweeps set it
-  const int want = c->opts.reserved[1] > 0 ? c->opts.reserved[1] : 25;   // node layers per z-chunk
+  const int tile = c->opts.reserved[0] ? c->opts.reserved[0] : 3;   // tuning knob; 3 = 4x4 positions, 4 CTAs/SM
+  const int want = c->opts.reserved[1] > 0 ? c->opts.reserved[1] : 17;   // node layers per z-chunk
   const int nchunk = (c->dhex.NK + want / 2) / want > 0 ? (c->dhex.NK + want / 2) / want : 1;
   const int LZ = (c->dhex.NK + nchunk - 1) / nchunk;
   switch (tile) {
     case 1: return launch_tile<8, 8>(c, d_u, d_vals, d_fint, LZ);
     case 2: return launch_tile<8, 6>(c, d_u, d_vals, d_fint, LZ);
-    default: return launch_tile<8, 4>(c, d_u, d_vals, d_fint, LZ);
+    case 3: return launch_tile<4, 4>(c, d_u, d_vals, d_fint, LZ);
+    case 4: return launch_tile<8, 2>(c, d_u, d_vals, d_fint, LZ);
+    case 5: return launch_tile<8, 4>(c, d_u, d_vals, d_fint, LZ);
+    default: return launch_tile<4, 4>(c, d_u, d_vals, d_fint, LZ);
   }
 }
 
