@@ -152,12 +152,29 @@ def main():
     nnz, nrows = fx.nnz, fx.nrows
 
     d_u = fx.device_buffer(u.nbytes).upload(u)
-    d_vals = fx.device_buffer(8 * nnz)
     d_f = fx.device_buffer(8 * nrows)
+    da = None
+    if world > 1:
+        # interface rows go to their PETSc owners over NCCL every step (fem_b200/parallel.py)
+        import ctypes as C
+        from fem_b200 import parallel as par
+        da = par.DistributedAssembly(fx, dist, torch.device("cuda", local_rank), with_merge=False)
+        vals_ptr = C.c_void_p(da.vals_local.data_ptr())
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    else:
+        d_vals = fx.device_buffer(8 * nnz)
+        vals_ptr = d_vals.ptr
 
     def step_device():
-        fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_vals.ptr, d_f.ptr, api.DEVICE))
-        return fx.last_kernel_ms
+        fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, vals_ptr, d_f.ptr, api.DEVICE))
+        ms = fx.last_kernel_ms
+        if da is not None:
+            ev0.record()
+            da.exchange()
+            ev1.record()
+            ev1.synchronize()
+            ms += ev0.elapsed_time(ev1)
+        return ms
 
     def barrier():
         if world > 1:
@@ -224,7 +241,8 @@ def main():
                 "config": {"workload": f"hex8 cube {args.n}^3 per GPU, jittered, K + f_int (BASELINE configs[1])",
                            "elements_per_gpu": m.nels, "dof_per_gpu": int(m.pdim * m.nlnds), "nnz_per_gpu": int(nnz),
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
-                           "parallelism": f"element partition x{world}, no exchange" if world > 1 else "1 GPU",
+                           "parallelism": (f"z-slab element partition x{world}, PETSc row split, NCCL all_to_all of interface rows "
+                                           f"({int(da.ep.recv_counts.sum()) * 8} B received on rank 0 per step)") if world > 1 else "1 GPU",
                            "variant": args.variant, "tile": args.tile, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
                 "gpu_launches": int(launches),
                 "clocks": sampler.summary(),

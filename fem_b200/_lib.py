@@ -53,6 +53,7 @@ SIGNATURES = {
     "femx_residual_forces": (C.c_int, [V, V, V, C.c_double, C.c_double, V, C.c_int]),
     "femx_stress": (C.c_int, [V, V, V, C.c_int, C.c_int]),
     "femx_set_ownership": (C.c_int, [V, C.c_int, C.c_int, C.c_int64, C.c_int64]),
+    "femx_gather_sum": (C.c_int, [V, V, C.c_int64, V, V, V, C.c_int64, V]),
     "femx_nccl_unique_id": (C.c_int, [C.c_char_p]),
     "femx_comm_init": (C.c_int, [V, C.c_char_p]),
     "femx_launch_count": (C.c_int64, [V]),

@@ -231,6 +231,18 @@ int femx_residual_forces(femx_ctx *c, const double *u_total_local, const double 
   return residual_impl(c, nullptr, u_total_local, nullptr, f_ext, dt, t_total, out, where);
 }
 
+int femx_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, const int64_t *ptr, const int64_t *idx,
+                    int64_t nout, double *out) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(ptr && idx && out && nout >= 0, "femx_gather_sum: NULL argument");
+  CK(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = begin_timing(c))) return rc;
+  c->launches += launch_gather_sum(c, a, na, b, ptr, idx, nout, out);
+  if ((rc = end_timing(c))) return rc;
+  return finish_call(c, true);
+}
+
 int femx_stress(femx_ctx *c, const double *uu_local, double *stress_node, int layout, int where) {
   if (!c) return FEMX_ERR_ARG;
   ARG(c->has_plan && uu_local && stress_node, "femx_build_plan first / NULL argument");

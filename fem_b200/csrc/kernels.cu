@@ -373,6 +373,21 @@ __global__ void cohesive_force_gather_kernel(DevMesh dm, int n, const int32_t *_
   }
 }
 
+// ordered merge of own + received contributions per owned nonzero (receiver adds in
+// (source rank, position) order)
+__global__ void gather_sum_kernel(const double *__restrict__ a, int64_t na, const double *__restrict__ b,
+                                  const int64_t *__restrict__ ptr, const int64_t *__restrict__ idx, int64_t nout,
+                                  double *__restrict__ out) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nout) return;
+  double v = 0.0;
+  for (int64_t q = ptr[s]; q < ptr[s + 1]; ++q) {
+    const int64_t i = idx[q];
+    v += i < na ? a[i] : b[i - na];
+  }
+  out[s] = v;
+}
+
 // ================================================================= launchers
 static inline int nblocks(int64_t n, int bs) { return (int)((n + bs - 1) / bs); }
 
@@ -495,6 +510,13 @@ int launch_jacobian_overlay(femx_ctx *c, const double *d_kvals, double *d_jvals)
   if (!n) return 0;
   jacobian_overlay_kernel<<<nblocks(n, 128), 128, 0, c->stream>>>(c->dm, n, c->d_cblk_id, c->d_cblk_row, c->d_cblk_ptr,
                                                                  c->d_cblk_src, c->d_coh_ke, d_kvals, d_jvals);
+  return 1;
+}
+
+int launch_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, const int64_t *ptr, const int64_t *idx,
+                      int64_t nout, double *out) {
+  if (nout <= 0) return 0;
+  gather_sum_kernel<<<nblocks(nout, 256), 256, 0, c->stream>>>(a, na, b, ptr, idx, nout, out);
   return 1;
 }
 

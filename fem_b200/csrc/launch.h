@@ -21,6 +21,8 @@ int launch_cohesive_unit(femx_ctx *c, int n, const double *d_x, const int32_t *d
                          const double *d_props, double dt, double *d_force, double *d_stiff);
 int launch_jacobian_overlay(femx_ctx *c, const double *d_kvals, double *d_jvals);
 int launch_cohesive_force_gather(femx_ctx *c, double *d_out);
+int launch_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, const int64_t *ptr, const int64_t *idx,
+                      int64_t nout, double *out);
 int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 
 }  // namespace femx

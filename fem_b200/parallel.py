@@ -1,0 +1,169 @@
+"""Multi-GPU assembly: one rank per GPU, element partition, interface-row exchange.
+
+Mirrors what the reference gets from PETSc for free: every rank assembles the
+contributions of ITS elements (METIS `epart`, src/m_io.F90:137-141; here any `epart`), while
+matrix rows are owned by the contiguous PETSC_DECIDE split of `MatCreateAIJ`
+(src/main.F90:154).  Contributions to rows another rank owns are what
+`MatAssemblyBegin/End` ships through its stash (src/main.F90:167-168).
+
+B200 design: the rank-local CSR lists rows in ascending global order, so
+  * the values of this rank's OWNED rows are one contiguous slice of the local value array,
+  * the values destined to peer q are one contiguous slice as well (no pack kernel: the
+    assembly kernel has already written the send buffer),
+and the only per-assembly traffic is those fp64 slices, sent with NCCL (`all_to_all_single`
+over NVLink; gloo on CPU for the tests).  Integer (row, col) lists travel once, at setup.
+
+A rank's assembled output is COO with duplicates, the form `MatSetValuesCOO` takes:
+    [own slice | values received from rank 0 | from rank 1 | ...]   with fixed (i, j) lists.
+`merge()` additionally produces the owned rows as a CSR (union pattern, explicit zeros kept,
+sum in (own, source-rank) order -- deterministic) for hosts that want AIJ arrays and for the
+parity tests.  This module holds index logic only; values move through torch tensors that
+alias femx device buffers, and sums run in the femx_gather_sum kernel.
+"""
+from __future__ import annotations
+
+import dataclasses
+
+import numpy as np
+
+from .mesh import petsc_ownership
+
+
+@dataclasses.dataclass
+class ExchangePlan:
+    nranks: int
+    rank: int
+    row_start: int
+    row_end: int
+    own_lo: int                 # local value slice [own_lo, own_hi) = owned rows
+    own_hi: int
+    send_lo: np.ndarray         # [nranks] local value slice per destination
+    send_hi: np.ndarray
+    send_rows: list             # per destination: global rows / cols of the slice (setup only)
+    send_cols: list
+    recv_counts: np.ndarray = None
+    coo_i: np.ndarray = None    # COO of the rank's output (own slice first, then per source rank)
+    coo_j: np.ndarray = None
+    # merged owned CSR
+    rowptr: np.ndarray = None   # [row_end-row_start+1]
+    colidx: np.ndarray = None
+    merge_ptr: np.ndarray = None
+    merge_idx: np.ndarray = None
+
+
+def plan_sends(rowptr: np.ndarray, colidx: np.ndarray, nrows: int, nranks: int, rank: int) -> ExchangePlan:
+    """Split the rank-local CSR (global row numbering, rows of absent nodes empty) by row owner."""
+    bounds = np.array([petsc_ownership(nrows, nranks, r)[0] for r in range(nranks)] + [nrows], dtype=np.int64)
+    lo = rowptr[bounds[:-1]].astype(np.int64)
+    hi = rowptr[bounds[1:]].astype(np.int64)
+    rows_of = lambda r0, r1: np.repeat(np.arange(r0, r1, dtype=np.int64), np.diff(rowptr[r0:r1 + 1]))
+    send_rows, send_cols = [], []
+    for q in range(nranks):
+        if q == rank:
+            send_rows.append(np.zeros(0, np.int64)); send_cols.append(np.zeros(0, np.int64))
+        else:
+            send_rows.append(rows_of(bounds[q], bounds[q + 1]))
+            send_cols.append(colidx[lo[q]:hi[q]].astype(np.int64))
+    return ExchangePlan(nranks=nranks, rank=rank, row_start=int(bounds[rank]), row_end=int(bounds[rank + 1]),
+                        own_lo=int(lo[rank]), own_hi=int(hi[rank]), send_lo=lo, send_hi=hi,
+                        send_rows=send_rows, send_cols=send_cols)
+
+
+def finish_plan(ep: ExchangePlan, rowptr: np.ndarray, colidx: np.ndarray, recv_rows: list, recv_cols: list,
+                with_merge: bool = True) -> ExchangePlan:
+    """After the one-time (row, col) exchange: COO lists and the merged owned CSR."""
+    r0, r1 = ep.row_start, ep.row_end
+    ep.recv_counts = np.array([len(x) for x in recv_rows], dtype=np.int64)
+    for x in recv_rows:
+        assert np.all((np.asarray(x) >= r0) & (np.asarray(x) < r1)), "received a row this rank does not own"
+    if not with_merge:          # COO lists of the received part only (the own part is the local CSR slice)
+        ep.coo_i = np.concatenate([np.asarray(x, np.int64) for x in recv_rows]) if recv_rows else np.zeros(0, np.int64)
+        ep.coo_j = np.concatenate([np.asarray(x, np.int64) for x in recv_cols]) if recv_cols else np.zeros(0, np.int64)
+        return ep
+    own_rows = np.repeat(np.arange(r0, r1, dtype=np.int64), np.diff(rowptr[r0:r1 + 1]))
+    own_cols = colidx[ep.own_lo:ep.own_hi].astype(np.int64)
+    ep.coo_i = np.concatenate([own_rows] + [np.asarray(x, np.int64) for x in recv_rows])
+    ep.coo_j = np.concatenate([own_cols] + [np.asarray(x, np.int64) for x in recv_cols])
+    # union pattern; stable sort keeps (own, source rank, sender position) order inside each nonzero
+    ncols = int(ep.coo_j.max()) + 1 if len(ep.coo_j) else 1
+    key = (ep.coo_i - r0) * ncols + ep.coo_j
+    order = np.argsort(key, kind="stable")
+    ks = key[order]
+    first = np.ones(len(ks), bool)
+    first[1:] = ks[1:] != ks[:-1]
+    starts = np.nonzero(first)[0]
+    ep.merge_ptr = np.concatenate([starts, [len(ks)]]).astype(np.int64)
+    ep.merge_idx = order.astype(np.int64)
+    urow = (ks[starts] // ncols).astype(np.int64)
+    ep.colidx = (ks[starts] % ncols).astype(np.int32)
+    ep.rowptr = np.zeros(r1 - r0 + 1, np.int64)
+    np.add.at(ep.rowptr, urow + 1, 1)
+    np.cumsum(ep.rowptr, out=ep.rowptr)
+    return ep
+
+
+def exchange_lists(ep: ExchangePlan, dist, device="cpu"):
+    """One-time exchange of the (row, col) lists with torch.distributed (gloo or NCCL)."""
+    import torch
+    P = ep.nranks
+    counts = torch.tensor([len(x) for x in ep.send_rows], dtype=torch.int64, device=device)
+    rcounts = torch.empty(P, dtype=torch.int64, device=device)
+    dist.all_to_all_single(rcounts, counts)
+    rc = rcounts.cpu().tolist()
+    sc = counts.cpu().tolist()
+    out = []
+    for lists in (ep.send_rows, ep.send_cols):
+        send = torch.from_numpy(np.concatenate(lists)).to(device)
+        recv = torch.empty(int(sum(rc)), dtype=torch.int64, device=device)
+        dist.all_to_all_single(recv, send, output_split_sizes=rc, input_split_sizes=sc)
+        out.append(np.split(recv.cpu().numpy(), np.cumsum(rc)[:-1]))
+    return out[0], out[1]
+
+
+class DistributedAssembly:
+    """Per-rank driver: femx context on the local mesh + the exchange plan.
+
+    `vals_local` lives in a torch tensor so that torch.distributed (NCCL) can send slices of it;
+    femx writes into it through its raw device pointer.
+    """
+
+    def __init__(self, fx, dist, device, with_merge=True):
+        import torch
+        self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
+        rowptr, colidx = fx.pattern()
+        nranks, rank = dist.get_world_size(), dist.get_rank()
+        ep = plan_sends(rowptr, colidx, fx.nrows, nranks, rank)
+        rr, rcs = exchange_lists(ep, dist, device)
+        self.ep = finish_plan(ep, rowptr, colidx, rr, rcs, with_merge)
+        self.vals_local = torch.empty(fx.nnz, dtype=torch.float64, device=device)
+        self.recv = torch.empty(int(self.ep.recv_counts.sum()), dtype=torch.float64, device=device)
+        self.send_splits = [int(h - l) if q != rank else 0 for q, (l, h) in enumerate(zip(ep.send_lo, ep.send_hi))]
+        self.recv_splits = [int(x) for x in self.ep.recv_counts]
+        self.n_own = self.ep.own_hi - self.ep.own_lo
+        self._merge_dev = None
+
+    def exchange(self):
+        """Ship the interface-row values (contiguous slices of vals_local, no pack kernel);
+        returns (own slice view, received values ordered by source rank)."""
+        ep = self.ep
+        ins = [self.vals_local[int(ep.send_lo[q]):int(ep.send_hi[q])] if q != ep.rank else self.vals_local[:0]
+               for q in range(ep.nranks)]
+        offs = np.concatenate([[0], np.cumsum(self.recv_splits)])
+        outs = [self.recv[int(offs[q]):int(offs[q + 1])] for q in range(ep.nranks)]
+        self.dist.all_to_all(outs, ins)
+        return self.vals_local[ep.own_lo:ep.own_hi], self.recv
+
+    def merged(self):
+        """Owned rows as CSR values (union pattern), summed in (own, source rank) order on the device."""
+        import ctypes as C
+        torch, ep, fx = self.torch, self.ep, self.fx
+        if self._merge_dev is None:
+            self._merge_dev = (torch.from_numpy(ep.merge_ptr).to(self.device), torch.from_numpy(ep.merge_idx).to(self.device),
+                               torch.empty(len(ep.colidx), dtype=torch.float64, device=self.device))
+        ptr, idx, out = self._merge_dev
+        own = self.vals_local[ep.own_lo:ep.own_hi]
+        torch.cuda.synchronize()
+        fx._ck(fx.L.femx_gather_sum(fx.h, C.c_void_p(own.data_ptr()), self.n_own, C.c_void_p(self.recv.data_ptr()),
+                                    C.c_void_p(ptr.data_ptr()), C.c_void_p(idx.data_ptr()), len(ep.colidx),
+                                    C.c_void_p(out.data_ptr())))
+        return out

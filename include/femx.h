@@ -149,6 +149,11 @@ int femx_stress(femx_ctx *ctx, const double *uu_local, double *stress_node, int 
 /* rows [row_start,row_end) of the global matrix are owned by this rank: the PETSC_DECIDE
  * split of MatCreateAIJ, src/main.F90:154.  Must precede femx_build_plan. */
 int femx_set_ownership(femx_ctx *ctx, int nranks, int rank, int64_t row_start, int64_t row_end);
+/* Ordered merge used after the interface exchange: out[s] = sum_{q in [ptr[s], ptr[s+1])} src(idx[q]) in list
+ * order (deterministic), src = a for idx < na else b[idx - na].  All pointers are DEVICE pointers.
+ * a = this rank's own values of its owned rows, b = the values received from the other ranks. */
+int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b, const int64_t *ptr,
+                    const int64_t *idx, int64_t nout, double *out);
 int femx_nccl_unique_id(char id[128]);
 int femx_comm_init(femx_ctx *ctx, const char id[128]);
 
