@@ -235,6 +235,13 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         alg = algorithmic_bytes(m, nnz)
         achieved = alg / (ms_step * 1e-3) / 1e9
+        traffic = None
+        try:   # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu capture
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            if args.n == 100:
+                traffic = tj["traffic_bytes_per_launch"]
+        except Exception:
+            pass
         line = {"metric": "elements/sec (Ke+f_int assembly)", "value": value, "unit": "elements/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -248,7 +255,8 @@ def main():
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                             "frac_of_8TBs_nominal": achieved / 8000.0, "bytes_per_element": alg / m.nels, "traffic": None}}
+                             "frac_of_8TBs_nominal": achieved / 8000.0, "bytes_per_element": alg / m.nels, "algorithmic_bytes_per_launch": alg,
+                             "kernel": "hex_fused_kernel (one launch per step)", "traffic": traffic}}
         if e2e:
             line["e2e"] = {"value": nels_total / (e2e_ms * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": e2e["h2d"],
                            "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms}
