@@ -1,0 +1,145 @@
+! femx_mod.F90 -- ISO_C_BINDING interface to libfemx.so (include/femx.h).
+!
+! This is the reference-side binding a defmod maintainer adds next to src/m_global.F90.
+! No Fortran compiler exists in the build image, so this file is not compiled by the test
+! suite; the same entry points are exercised through ctypes (fem_b200/_lib.py) with the same
+! argument order and types.  See INTEGRATION.md for the call sites it replaces.
+module femx
+  use iso_c_binding
+  implicit none
+
+  integer(c_int), parameter :: FEMX_HOST = 0, FEMX_DEVICE = 1
+  integer(c_int), parameter :: FEMX_ROW_MAJOR = 0, FEMX_COL_MAJOR = 1
+  integer(c_int), parameter :: FEMX_Q_REFERENCE = 15, FEMX_Q_UEL = 0
+
+  type, bind(C) :: femx_opts
+    integer(c_int) :: quirks = FEMX_Q_REFERENCE
+    integer(c_int) :: assembly_variant = 0
+    integer(c_int) :: reserved(6) = 0
+  end type femx_opts
+
+  interface
+    integer(c_int) function femx_create(ctx, device, opts) bind(C, name="femx_create")
+      import :: c_ptr, c_int, femx_opts
+      type(c_ptr), intent(out) :: ctx
+      integer(c_int), value :: device
+      type(femx_opts), intent(in) :: opts
+    end function
+    integer(c_int) function femx_destroy(ctx) bind(C, name="femx_destroy")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
+    function femx_last_error(ctx) bind(C, name="femx_last_error") result(msg)
+      import :: c_ptr
+      type(c_ptr), value :: ctx
+      type(c_ptr) :: msg
+    end function
+    ! local_elements(:) flattened: etype = getElTypeNo, eptr/eind as PartitionBroadcast builds them
+    ! (src/m_io.F90:128-135) but with the 1-based LOCAL node ids of src/main.F90:68-73
+    integer(c_int) function femx_set_mesh(ctx, pdim, nels, etype, eptr, eind, emat, enlmat, nlnds, coords, &
+                                          coords_layout, nl2g, nnds) bind(C, name="femx_set_mesh")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: pdim, nels, nlnds, coords_layout, nnds
+      integer(c_int), intent(in) :: etype(*), eptr(*), eind(*), emat(*), enlmat(*), nl2g(*)
+      real(c_double), intent(in) :: coords(*)
+    end function
+    integer(c_int) function femx_set_materials(ctx, nmts, E_nu, ncoh, cohprops) bind(C, name="femx_set_materials")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nmts, ncoh
+      real(c_double), intent(in) :: E_nu(*), cohprops(*)
+    end function
+    integer(c_int) function femx_set_bcs(ctx, nbcs, bcnode, bcval) bind(C, name="femx_set_bcs")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nbcs
+      integer(c_int), intent(in) :: bcnode(*)
+      real(c_double), intent(in) :: bcval(*)
+    end function
+    integer(c_int) function femx_build_plan(ctx) bind(C, name="femx_build_plan")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
+    integer(c_int) function femx_pattern_size(ctx, nrows, nnz) bind(C, name="femx_pattern_size")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), intent(out) :: nrows, nnz
+    end function
+    integer(c_int) function femx_get_pattern(ctx, rowptr, colidx, where) bind(C, name="femx_get_pattern")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, rowptr, colidx      ! int64 rowptr(nrows+1), int32 colidx(nnz); c_null_ptr to skip
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_assemble_K(ctx, vals, where) bind(C, name="femx_assemble_K")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, vals                ! c_loc(host array) or a device pointer from PETSc
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_assemble_K_fint(ctx, u_local, vals, fint, where) bind(C, name="femx_assemble_K_fint")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, u_local, vals, fint
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_apply_kbc(ctx, vals, where) bind(C, name="femx_apply_kbc")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, vals
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_jacobian(ctx, kvals, u_total_local, dt, jvals, where) bind(C, name="femx_jacobian")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx, kvals, u_total_local, jvals
+      real(c_double), value :: dt
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_residual(ctx, jvals, u_total_local, du, f_ext, dt, t_total, r, where) &
+        bind(C, name="femx_residual")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx, jvals, u_total_local, du, f_ext, r
+      real(c_double), value :: dt, t_total
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_residual_forces(ctx, u_total_local, f_ext, dt, t_total, out, where) &
+        bind(C, name="femx_residual_forces")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx, u_total_local, f_ext, out
+      real(c_double), value :: dt, t_total
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_stress(ctx, uu_local, stress_node, layout, where) bind(C, name="femx_stress")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, uu_local, stress_node
+      integer(c_int), value :: layout, where
+    end function
+    integer(c_int) function femx_element_ke(ctx, etype, n, ecoords, E_nu, ke) bind(C, name="femx_element_ke")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: etype, n
+      real(c_double), intent(in) :: ecoords(*), E_nu(*)
+      real(c_double), intent(out) :: ke(*)
+    end function
+    integer(c_int) function femx_set_ownership(ctx, nranks, rank, row_start, row_end) bind(C, name="femx_set_ownership")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nranks, rank
+      integer(c_int64_t), value :: row_start, row_end
+    end function
+    integer(c_int) function femx_gather_sum(ctx, a, na, b, ptr, idx, nout, out) bind(C, name="femx_gather_sum")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx, a, b, ptr, idx, out
+      integer(c_int64_t), value :: na, nout
+    end function
+  end interface
+
+contains
+
+  ! Flattens module global's local_elements(:) (src/m_global.F90:40) into the arrays femx_set_mesh takes.
+  ! `elems` components used: eltype -> type code, nodes(:), mat, nlMat (src/m_elems.F90:6-12).
+  subroutine femx_check(ierr_c, ierr)
+    integer(c_int), intent(in) :: ierr_c
+    integer, intent(out) :: ierr
+    ierr = int(ierr_c)     ! PETSc-style trailing ierr (the reference never checks it; femx keeps the text
+                           ! in femx_last_error)
+  end subroutine femx_check
+
+end module femx
