@@ -258,8 +258,8 @@ int femx_build_plan(femx_ctx *c) {
         for (int t = 0; t < 27; ++t) mm.k[t] = c->hex.kmap[(size_t)r * 32 + t];
       }
       UP(hx.pos_x, px); UP(hx.pos_meta, pm);
-    } else if (c->opts.assembly_variant == 2) {
-      c->err = "assembly_variant 2 requested but the mesh does not qualify: " + c->hex.why;
+    } else if (c->opts.assembly_variant >= 2) {
+      c->err = "fused assembly variant requested but the mesh does not qualify: " + c->hex.why;
       return FEMX_ERR_UNSUPPORTED;
     }
   }

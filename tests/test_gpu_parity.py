@@ -285,6 +285,13 @@ def test_fused_hex_variant_vs_oracle_and_twopass(orc):
                 assert close(fint, f_o, TOL_MAT), (name, tile, lz)
                 assert np.array_equal(f.assemble_K(), vals), (name, tile, lz)     # K-only kernel, same bits
                 f.close()
+        for lz in (25, 3):                                   # warp-specialised kernel (variant 3)
+            with api.Femx(assembly_variant=3, lz=lz) as f3:
+                f3.set_mesh(m).build_plan()
+                v3, f3int = f3.assemble_K_fint(u)
+                assert close(v3, va_o, TOL_MAT), (name, "ws", lz)
+                assert close(f3int, f_o, TOL_MAT), (name, "ws", lz)
+                assert np.array_equal(f3.assemble_K(), v3), (name, "ws", lz)
         with api.Femx(assembly_variant=1) as f1:
             v1 = f1.set_mesh(m).build_plan().assemble_K()
         assert close(v1, va_o, TOL_MAT), name
