@@ -194,7 +194,8 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int buf, int h) {
   }
 }
 
-// global stores of one dump: helper warp hw moves the 81 values of 12 storing threads, 32 lanes per pass
+// global stores of one dump: helper warp hw moves the 81 values of 12 storing threads, 32 lanes per pass.
+// Branch-free (predicated stores) so that the shared-memory reads of four storing threads overlap.
 __device__ __forceinline__ void store_dump(Smem &S, int hw, int lane, const int (&lane_i)[3], const int (&lane_s)[3],
                                            const int (&lane_j)[3]) {
 #pragma unroll 4
@@ -202,14 +203,20 @@ __device__ __forceinline__ void store_dump(Smem &S, int hw, int lane, const int 
     const int w = hw * (NWRITER / 8) + q;
     const DumpHdr &hd = S.hdr[w];
     double *row0 = hd.row0;
-    if (row0 == nullptr) continue;
     const int stride = hd.stride;
     const double *src = &S.dump[w * kDumpStride];
+    int k[3];
+    double v[3];
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
-      const int v = it * 32 + lane;
-      const int k = hd.k[lane_s[it]];
-      if (v < 81 && k != 255) row0[lane_i[it] * stride + 3 * k + lane_j[it]] = src[v];
+      k[it] = hd.k[lane_s[it]];
+      v[it] = src[min(it * 32 + lane, 80)];
+    }
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const bool on = row0 != nullptr && (it * 32 + lane) < 81 && k[it] != 255;
+      double *dst = on ? row0 + (lane_i[it] * stride + 3 * k[it] + lane_j[it]) : nullptr;
+      if (on) *dst = v[it];
     }
   }
 }
