@@ -4,7 +4,7 @@
 // does what, so that the latency-bound parts overlap the FP64 loop instead of alternating with it:
 //   warps 0-3  "consumers" (128 threads, 240 registers each after setmaxnreg.inc): the 16-contribution
 //              FMA loop into 9 register blocks, G' -> K, f partials, transpose dump to shared memory;
-//   warps 4-11 "helpers"   (256 threads, 104 registers): cp.async prefetch ring of node layers,
+//   warps 4-15 "helpers"   (384 threads, 88 registers): cp.async prefetch ring of node layers,
 //              geometry of the NEXT element layer into the other gradient buffer, and the global
 //              stores of the PREVIOUS step's dump.
 // Hand-over through named barriers (bar.arrive / bar.sync): full[2] / empty[2] for the double-buffered
@@ -19,7 +19,7 @@ namespace {
 
 constexpr int TX = 8, TY = 4, NP = TX * TY;
 constexpr int NCONS = 4 * NP;          // 128 consumer threads
-constexpr int NHELP = 256;             // helper threads
+constexpr int NHELP = 384;             // helper threads (12 warps: one geometry item each per layer)
 constexpr int NTHREADS = NCONS + NHELP;
 constexpr int EX = TX + 1, EY = TY + 1, EL = EX * EY;
 constexpr int UX = TX + 2, UY = TY + 2, UL = UX * UY;
@@ -199,8 +199,8 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int buf, int h) {
 __device__ __forceinline__ void store_dump(Smem &S, int hw, int lane, const int (&lane_i)[3], const int (&lane_s)[3],
                                            const int (&lane_j)[3]) {
 #pragma unroll 4
-  for (int q = 0; q < NWRITER / 8; ++q) {
-    const int w = hw * (NWRITER / 8) + q;
+  for (int q = 0; q < NWRITER / 12; ++q) {
+    const int w = hw * (NWRITER / 12) + q;
     const DumpHdr &hd = S.hdr[w];
     double *row0 = hd.row0;
     const int stride = hd.stride;
@@ -236,7 +236,7 @@ hex_ws_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals
 
   if (tid >= NCONS) {
     // =========================================================================== helper warps
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
     const int h = tid - NCONS, lane = h & 31, hw = h >> 5;
     int lane_i[3], lane_s[3], lane_j[3];
 #pragma unroll
@@ -364,13 +364,22 @@ hex_ws_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals
       }
       if (WITH_F) {
         const double *ub = &S.ulay[(lay + grp - 1) & 3][0][0];
+        double fp[3][3];   // three independent chains per component (fixed order), summed at the end
 #pragma unroll
-        for (int s = 0; s < 9; ++s) {
-          const double *uc = ub + ((py + s / 3) * UX + (px + s % 3)) * 3;
-          const double u0 = uc[0], u1 = uc[1], u2 = uc[2];
+        for (int sy = 0; sy < 3; ++sy) {
 #pragma unroll
-          for (int i = 0; i < 3; ++i) fpart[i] += acc[s][i * 3] * u0 + acc[s][i * 3 + 1] * u1 + acc[s][i * 3 + 2] * u2;
+          for (int i = 0; i < 3; ++i) fp[sy][i] = 0.0;
+#pragma unroll
+          for (int sx = 0; sx < 3; ++sx) {
+            const int s = sy * 3 + sx;
+            const double *uc = ub + ((py + sy) * UX + (px + sx)) * 3;
+            const double u0 = uc[0], u1 = uc[1], u2 = uc[2];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) fp[sy][i] += acc[s][i * 3] * u0 + acc[s][i * 3 + 1] * u1 + acc[s][i * 3 + 2] * u2;
+          }
         }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) fpart[i] = (fp[0][i] + fp[1][i]) + fp[2][i];
       }
     }
     // header of this thread's dump (read before the layer ring slot can be recycled)
