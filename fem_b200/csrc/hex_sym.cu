@@ -30,8 +30,10 @@ constexpr int UX = NX + 2, UY = NY + 2, UL = UX * UY;   // node positions per la
 constexpr int NT = 4 * EL;                    // 256 threads: 4 per cell
 constexpr int NW = NT / 32;
 constexpr int GS = 194;                       // doubles per cell in the gradient buffer (8 ip x 24 + 2; 16-byte stride odd)
-constexpr int SS = 234;                       // doubles per cell of block scratch: 10 face blocks + 16 bottom x top blocks
-constexpr int BT_OFF = 90;
+constexpr int SS = 290;                       // doubles per cell of scratch: 10 face + 16 bottom x top blocks, 48 f partials, 8 zeros
+constexpr int BT_OFF = 90, F_OFF = 234;       // f partials: face 12, then per bottom x top thread 6 (its bottom nodes) + 12 (top nodes)
+constexpr int ZERO_OFF = 282;                 // scr[cell][ZERO_OFF..+7] = 0: target of the unused gather-table entries
+constexpr int XP = 40;                        // doubles per row of the coordinate layer (27 used; 40 = 8 mod 16 keeps two cell rows on distinct banks)
 static_assert(EL == 64 && NT == 256, "thread mapping assumes 64 cells per layer");
 
 struct Smem {
@@ -39,12 +41,12 @@ struct Smem {
     double geo[EL * GS];   // scaled gradients [cell][ip][i][node]
     double scr[EL * SS];   // K blocks [cell][block][i][j] (written after the FMA phase has left geo)
   } a;
-  double xlay[4][UL][3];
+  double xlay[4][UY * XP];
   double ulay[4][UL][3];
   double esc[4][EL];
   double fcarry[NP][3];
   HexRowMeta rowmeta[4][NP];
-  uint2 tab[9][32];        // gather table: [i*3+g][lane] -> four 16-bit scratch offsets (0xffff = none)
+  uint2 tab[5][32];        // gather table: {dz=-1, dz=+1, dz=0 rows i=0..2}[lane] -> four 16-bit byte offsets into the scratch
   int nid[8][UL];
 };
 
@@ -79,7 +81,7 @@ __device__ __forceinline__ void fetch_layer(Smem &S, const DevHex &hx, const Til
   for (int t = tid; t < UL; t += NT) {
     bool ok;
     const long long c = cell_of(hx, T, t, lay, ok);
-    double *xb = S.xlay[buf][t];
+    double *xb = &S.xlay[buf][(t / UX) * XP + (t % UX) * 3];
     if (ok) {
 #pragma unroll
       for (int d = 0; d < 3; ++d) cp_async8(xb + d, hx.pos_x + c * 3 + d);
@@ -131,7 +133,7 @@ __device__ __forceinline__ void fetch_esc(Smem &S, const DevHex &hx, const Tile 
 
 // gather table entry of lane l (value (kk, j) of a 27-value run) for scalar row i and group g = dz + 1
 __device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
-  unsigned o[4] = {0xffffu, 0xffffu, 0xffffu, 0xffffu};
+  unsigned o[4] = {ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8};   // byte offsets from the node's base cell
   if (l < 27) {
     const int kk = l / 3, j = l % 3, dy = kk / 3 - 1, dx = kk % 3 - 1;
     int n = 0;
@@ -144,7 +146,7 @@ __device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
         if (g == 1) off = fa <= fb ? pair_q(fa, fb) * 9 + i * 3 + j : pair_q(fb, fa) * 9 + j * 3 + i;
         else if (g == 2) off = BT_OFF + (fa * 4 + fb) * 9 + i * 3 + j;     // row node on the bottom face
         else off = BT_OFF + (fb * 4 + fa) * 9 + j * 3 + i;                 // row node on the top face: transposed block
-        o[n++] = (unsigned)((oy * EX + ox) * SS + off);
+        o[n++] = (unsigned)((oy * EX + ox) * SS + off) * 8u;
       }
   }
   return make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
@@ -153,12 +155,12 @@ __device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
 // scaled physical gradients g~_b(ip) = adj(J)^T grad N_b * sqrt(mu w / detJ) of cell layer m (FormdNdetJ,
 // src/m_local.F90:175-189, with the closed-form adjugate instead of dgetrf/dgetri)
 __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
-  const double *xlo = &S.xlay[m & 3][0][0], *xhi = &S.xlay[(m + 1) & 3][0][0];
+  const double *xlo = &S.xlay[m & 3][0], *xhi = &S.xlay[(m + 1) & 3][0];
   const int es = tid & (EL - 1);
   const double smu = S.esc[m & 3][es];
   if (smu == 0.0) return;
   const int ex = es % EX, ey = es / EX;
-#pragma unroll 1
+#pragma unroll
   for (int q = 0; q < 2; ++q) {
     const int ip = (tid >> 6) + 4 * q;
     // integration point ip sits beside node ip (SamPtsHex, src/m_elems.F90:500-507)
@@ -173,7 +175,7 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
       const int bx = (b == 1 || b == 2 || b == 5 || b == 6) ? 1 : 0, by = ((b & 3) >= 2) ? 1 : 0, bz = b >> 2;
-      const double *xs = (bz ? xhi : xlo) + ((ey + by) * UX + (ex + bx)) * 3;
+      const double *xs = (bz ? xhi : xlo) + (ey + by) * XP + (ex + bx) * 3;
       const double X0 = xs[0], X1 = xs[1], X2 = xs[2];
       // ShapeFuncdHex, src/m_elems.F90:574-579
       const double d0 = (bx ? 0.125 : -0.125) * fy[by] * fz[bz];
@@ -194,7 +196,7 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
     adj[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
     adj[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
     const double det = J[0][0] * adj[0][0] + J[0][1] * adj[1][0] + J[0][2] * adj[2][0];
-    const double sc = smu * sqrt(1.0 / det);   // hex weights are 1 (src/m_elems.F90:508)
+    const double sc = smu * rsqrt(det);   // hex weights are 1 (src/m_elems.F90:508)
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
@@ -301,36 +303,98 @@ __device__ __forceinline__ double face_out(const double (&acc)[78], int off) {
   return acc[offdiag_p(a, b) * 9 + r];
 }
 
-// ---------------------------------------------------------------------------------- gather phase
-template <int I, int G, bool WITH_F>
-__device__ __forceinline__ double gather_pass(const double *eb, const uint2 t, const HexRowMeta *rm, bool act, int kk, int j,
-                                              double *__restrict__ vals, const double *ub) {
-  const unsigned o0 = t.x & 0xffffu, o1 = t.x >> 16, o2 = t.y & 0xffffu, o3 = t.y >> 16;
-  double v = 0.0;
-  if (o0 != 0xffffu) v = eb[o0];
-  if (o1 != 0xffffu) v += eb[o1];
-  if (o2 != 0xffffu) v += eb[o2];
-  if (o3 != 0xffffu) v += eb[o3];
-  const int k = rm->k[G * 9 + kk];
-  if (act && o0 != 0xffffu && k != 255) vals[rm->base + (long long)(I * 3) * rm->nb + 3 * k + j] = v;
-  if (WITH_F) return v * ub[0];
-  return 0.0;
+// f partials of one cell from its K blocks (f_a += K_ab u_b, f_b += K_ab^T u_a); un = u of the cell's node (0,0) on that layer
+__device__ __forceinline__ void load_u4(const double *un, double (&uu)[4][3]) {
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int lx = (a == 1 || a == 2) ? 1 : 0, ly = a >= 2 ? 1 : 0;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) uu[a][d] = un[(ly * UX + lx) * 3 + d];
+  }
+}
+__device__ __forceinline__ void face_force(const double (&acc)[78], const double *un, double *out) {
+  double uu[4][3], fp[4][3];
+  load_u4(un, uu);
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      double t = 0.0;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) t = fma(acc[54 + a * 6 + sym_s(i < j ? i : j, i < j ? j : i)], uu[a][j], t);
+      fp[a][i] = t;
+    }
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = a + 1; b < 4; ++b)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const double k = acc[offdiag_p(a, b) * 9 + i * 3 + j];
+          fp[a][i] = fma(k, uu[b][j], fp[a][i]);
+          fp[b][j] = fma(k, uu[a][i], fp[b][j]);
+        }
+#pragma unroll
+  for (int q = 0; q < 6; ++q) *reinterpret_cast<double2 *>(out + 2 * q) = make_double2(fp[(2 * q) / 3][(2 * q) % 3], fp[(2 * q + 1) / 3][(2 * q + 1) % 3]);
+}
+__device__ __forceinline__ void bt_force(const double (&acc)[78], int a0, const double *ulo, const double *uhi, double *out) {
+  double ub[4][3], ut[4][3], fb[2][3], ft[4][3];
+  load_u4(ulo, ub);
+  load_u4(uhi, ut);
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) fb[a][i] = 0.0;
+#pragma unroll
+  for (int b = 0; b < 4; ++b)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) ft[b][j] = 0.0;
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    double ua[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) ua[d] = a0 ? ub[2 + a][d] : ub[a][d];
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const double k = acc[(a * 4 + b) * 9 + i * 3 + j];
+          fb[a][i] = fma(k, ut[b][j], fb[a][i]);
+          ft[b][j] = fma(k, ua[i], ft[b][j]);
+        }
+  }
+#pragma unroll
+  for (int q = 0; q < 3; ++q) *reinterpret_cast<double2 *>(out + 2 * q) = make_double2(fb[(2 * q) / 3][(2 * q) % 3], fb[(2 * q + 1) / 3][(2 * q + 1) % 3]);
+#pragma unroll
+  for (int q = 0; q < 6; ++q) *reinterpret_cast<double2 *>(out + 6 + 2 * q) = make_double2(ft[(2 * q) / 3][(2 * q) % 3], ft[(2 * q + 1) / 3][(2 * q + 1) % 3]);
 }
 
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-  for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-  return v;
+// ---------------------------------------------------------------------------------- gather phase
+// one CSR value: the <= 4 cell contributions in ascending cell order (unused table entries hit the zero area);
+// OFF = byte offset of scalar row i inside the stored block (static, so it folds into the LDS immediate)
+template <int OFF>
+__device__ __forceinline__ double gather_val(const char *q0, const char *q1, const char *q2, const char *q3) {
+  const double c0 = *reinterpret_cast<const double *>(q0 + OFF);
+  const double c1 = *reinterpret_cast<const double *>(q1 + OFF);
+  const double c2 = *reinterpret_cast<const double *>(q2 + OFF);
+  const double c3 = *reinterpret_cast<const double *>(q3 + OFF);
+  return ((c0 + c1) + c2) + c3;
 }
+#define FEMX_Q4(eb, t) (eb) + ((t).x & 0xffffu), (eb) + ((t).x >> 16), (eb) + ((t).y & 0xffffu), (eb) + ((t).y >> 16)
 
 }  // namespace
 
 template <bool WITH_F>
 __global__ void __launch_bounds__(NT, 1)
-hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ) {
+hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int wu = __reduce_max_sync(0xffffffffu, w);   // warp index the compiler can keep in a uniform register
   Tile T;
   T.i0 = blockIdx.x * NX; T.j0 = blockIdx.y * NY;
   T.l0 = blockIdx.z * LZ; T.l1 = min(T.l0 + LZ, hx.NK) - 1;
@@ -343,10 +407,11 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
   // gather-phase lane constants
   const int gl = lane < 27 ? lane : 26;
   const int kk = gl / 3, jj = gl % 3;
-  const int uoff = ((kk / 3) * UX + (kk % 3)) * 3 + jj;   // halo'd node (px + dx + 1, py + dy + 1), component j
 
-  if (tid < 243) S.tab[tid / 27][tid % 27] = table_entry((tid / 27) / 3, (tid / 27) % 3, tid % 27);
-  if (tid < 9 * 5) S.tab[tid / 5][27 + tid % 5] = make_uint2(0xffffffffu, 0xffffffffu);
+  for (int t = tid; t < 5 * 32; t += NT) {   // rows i > 0 of the dz = -1 / +1 groups sit at +8 i / +24 i bytes
+    const int q = t / 32;
+    S.tab[q][t % 32] = table_entry(q < 2 ? 0 : q - 2, q == 0 ? 0 : (q == 1 ? 2 : 1), t % 32);
+  }
   if (WITH_F && tid < NP * 3) (&S.fcarry[0][0])[tid] = 0.0;
   fetch_nid(S, hx, T, T.l0 - 1, tid); fetch_nid(S, hx, T, T.l0, tid); fetch_nid(S, hx, T, T.l0 + 1, tid);
   fetch_esc(S, hx, T, T.l0 - 1, tid);
@@ -362,7 +427,7 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
     const int m = T.l0 - 1 + it;
     cp_async_wait_all();
     __syncthreads();              // layer data of m, m+1 is in; the previous gather has left the scratch
-    geometry(S, m, tid);
+    if (!(dbg & 1)) geometry(S, m, tid);
     __syncthreads();
     // prefetch for the next step: ids of m+3, node layer m+2, cell scale of m+1 (ring slots of step it-2)
     fetch_nid(S, hx, T, m + 3, tid);
@@ -379,7 +444,7 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
         for (int q = 0; q < 78; ++q) acc[q] = 0.0;
       }
       const bool need = finisher ? it > 0 : it + 1 < nsteps;   // first finish / last start feed no owned row
-      if (cell_on && need) {
+      if (cell_on && need && !(dbg & 2)) {
         const double *gf = g + (finisher ? 0 : 4);
         double v0[3][4], v1[3][4];
         load_face(gf, v0);
@@ -394,7 +459,7 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
     } else {
 #pragma unroll
       for (int q = 0; q < 78; ++q) acc[q] = 0.0;
-      if (cell_on) {
+      if (cell_on && !(dbg & 2)) {
         const int a0 = (type - 2) * 2;
         double va0[3][2], vb0[3][4], va1[3][2], vb1[3][4];
         load_bt(g, a0, va0, vb0);
@@ -420,10 +485,18 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
 #pragma unroll
           for (int q = 0; q < 45; ++q)
             *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out(acc, 2 * q), face_out(acc, 2 * q + 1));
+          if (WITH_F) face_force(acc, &S.ulay[m & 3][0][0] + ((es / EX) * UX + es % EX) * 3, sc + F_OFF);
         }
       } else {
 #pragma unroll
         for (int p = 0; p < 8; ++p) to_k_block(&acc[p * 9], rho);
+        if (type == 3) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<double2 *>(sc + ZERO_OFF + 2 * q) = make_double2(0.0, 0.0);
+        }
+        if (WITH_F)
+          bt_force(acc, (type - 2) * 2, &S.ulay[m & 3][0][0] + ((es / EX) * UX + es % EX) * 3,
+                   &S.ulay[(m + 1) & 3][0][0] + ((es / EX) * UX + es % EX) * 3, sc + F_OFF + 12 + (type - 2) * 18);
         double *dst = sc + BT_OFF + (type - 2) * 72;
 #pragma unroll
         for (int q = 0; q < 36; ++q) *reinterpret_cast<double2 *>(dst + 2 * q) = make_double2(acc[2 * q], acc[2 * q + 1]);
@@ -431,38 +504,50 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
     }
     __syncthreads();
     // ------------------------------------------------------------------ gather: rows of node layer m (dz = 0, +1) and m+1 (dz = -1)
-    {
-      uint2 tb[9];
-#pragma unroll
-      for (int q = 0; q < 9; ++q) tb[q] = S.tab[q][lane];
-      const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
-      for (int n = w; n < NP; n += NW) {
+    const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
+    if (!(dbg & 4)) {
+      const uint2 t0 = S.tab[0][lane], t2 = S.tab[1][lane], t10 = S.tab[2][lane], t11 = S.tab[3][lane], t12 = S.tab[4][lane];
+      for (int n = wu; n < NP; n += NW) {
         const int px = n % NX, py = n / NX;
-        const double *eb = &S.a.scr[(py * EX + px) * SS];
+        const char *eb = reinterpret_cast<const char *>(&S.a.scr[(py * EX + px) * SS]);
         const HexRowMeta *rlo = &S.rowmeta[m & 3][n], *rhi = &S.rowmeta[(m + 1) & 3][n];
         const bool act_lo = lay_lo && rlo->nb > 0, act_hi = lay_hi && rhi->nb > 0;
-        const double *ulo = &S.ulay[m & 3][0][0] + (py * UX + px) * 3 + uoff;
-        const double *uhi = &S.ulay[(m + 1) & 3][0][0] + (py * UX + px) * 3 + uoff;
-        double f_lo[3], f_hi[3];
         // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
-        f_lo[0] = gather_pass<0, 1, WITH_F>(eb, tb[1], rlo, act_lo, kk, jj, vals, ulo) + gather_pass<0, 2, WITH_F>(eb, tb[2], rlo, act_lo, kk, jj, vals, uhi);
-        f_lo[1] = gather_pass<1, 1, WITH_F>(eb, tb[4], rlo, act_lo, kk, jj, vals, ulo) + gather_pass<1, 2, WITH_F>(eb, tb[5], rlo, act_lo, kk, jj, vals, uhi);
-        f_lo[2] = gather_pass<2, 1, WITH_F>(eb, tb[7], rlo, act_lo, kk, jj, vals, ulo) + gather_pass<2, 2, WITH_F>(eb, tb[8], rlo, act_lo, kk, jj, vals, uhi);
-        f_hi[0] = gather_pass<0, 0, WITH_F>(eb, tb[0], rhi, act_hi, kk, jj, vals, ulo);
-        f_hi[1] = gather_pass<1, 0, WITH_F>(eb, tb[3], rhi, act_hi, kk, jj, vals, ulo);
-        f_hi[2] = gather_pass<2, 0, WITH_F>(eb, tb[6], rhi, act_hi, kk, jj, vals, ulo);
-        if (WITH_F) {
+        const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
+        const bool on0 = act_hi && lane < 27 && k0 != 255, on1 = act_lo && lane < 27 && k1 != 255, on2 = act_lo && lane < 27 && k2 != 255;
+        double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
+        const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
+        double v[9];
+        v[0] = gather_val<0>(FEMX_Q4(eb, t0)); v[3] = gather_val<8>(FEMX_Q4(eb, t0)); v[6] = gather_val<16>(FEMX_Q4(eb, t0));
+        v[2] = gather_val<0>(FEMX_Q4(eb, t2)); v[5] = gather_val<24>(FEMX_Q4(eb, t2)); v[8] = gather_val<48>(FEMX_Q4(eb, t2));
+        v[1] = gather_val<0>(FEMX_Q4(eb, t10)); v[4] = gather_val<0>(FEMX_Q4(eb, t11)); v[7] = gather_val<0>(FEMX_Q4(eb, t12));
 #pragma unroll
-          for (int i = 0; i < 3; ++i) { f_lo[i] = warp_sum(f_lo[i]); f_hi[i] = warp_sum(f_hi[i]); }
-          if (lane < 3) {
-            const double flo = lane == 0 ? f_lo[0] : (lane == 1 ? f_lo[1] : f_lo[2]);
-            const double fhi = lane == 0 ? f_hi[0] : (lane == 1 ? f_hi[1] : f_hi[2]);
-            // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
-            if (act_lo) fint[(long long)rlo->grow + lane] = S.fcarry[n][lane] + flo;
-            S.fcarry[n][lane] = act_hi ? fhi : 0.0;
-          }
+        for (int i = 0; i < 3; ++i) {
+          if (on0) p0[i * rs_hi] = v[i * 3 + 0];
+          if (on1) p1[i * rs_lo] = v[i * 3 + 1];
+          if (on2) p2[i * rs_lo] = v[i * 3 + 2];
         }
       }
+    }
+    if (WITH_F && tid < NP * 3) {
+      // f_r = sum_c K_rc u_c from the cells' partials: 4 cells x (face + bottom part) for the lower node plus the
+      // dz = -1 part carried from the previous step; 4 cells x 2 threads of top parts go into the carry of the upper node
+      const int n = tid / 3, i = tid % 3, px = n % NX, py = n / NX;
+      double lo = S.fcarry[n][i], hi = 0.0;
+#pragma unroll
+      for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+        for (int ox = 0; ox < 2; ++ox) {
+          const int fa = face_index(1 - ox, 1 - oy);
+          const double *fp = &S.a.scr[((py + oy) * EX + px + ox) * SS + F_OFF];
+          lo += fp[fa * 3 + i];
+          lo += fp[12 + (fa >> 1) * 18 + (fa & 1) * 3 + i];
+          hi += fp[12 + 6 + fa * 3 + i];
+          hi += fp[12 + 18 + 6 + fa * 3 + i];
+        }
+      const HexRowMeta *rlo = &S.rowmeta[m & 3][n], *rhi = &S.rowmeta[(m + 1) & 3][n];
+      if (lay_lo && rlo->nb > 0) fint[(long long)rlo->grow + i] = lo;
+      S.fcarry[n][i] = (lay_hi && rhi->nb > 0) ? hi : 0.0;
     }
   }
 }
@@ -489,10 +574,10 @@ int launch_hex_sym(femx_ctx *c, const double *d_u, double *d_vals, double *d_fin
   const size_t smem = sizeof(Smem);
   if (d_u) {
     cudaFuncSetAttribute(hex_sym_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_sym_kernel<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ);
+    hex_sym_kernel<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   } else {
     cudaFuncSetAttribute(hex_sym_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_sym_kernel<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ);
+    hex_sym_kernel<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   }
   return 1;
 }
