@@ -44,6 +44,7 @@ struct Smem {
   double xlay[4][UY * XP];
   double ulay[4][UL][3];
   double esc[4][EL];
+  double2 carry[39][EL];   // top-face pair sums of the previous cell layer (raw G'), [pair of values][cell]
   double fcarry[NP][3];
   HexRowMeta rowmeta[4][NP];
   uint2 tab[5][32];        // gather table: {dz=-1, dz=+1, dz=0 rows i=0..2}[lane] -> four 16-bit byte offsets into the scratch
@@ -437,9 +438,12 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
     // ------------------------------------------------------------------ FMA phase
     const bool cell_on = S.esc[m & 3][es] != 0.0;
     const double *g = &S.a.geo[es * GS];
-    const bool finisher = type == (it & 1);        // face role: finisher adds the bottom face of layer m to the carried top face of m-1
+    const bool finisher = type == 0;               // face roles: type 0 adds the bottom face of layer m to the parked top face of m-1
     if (type < 2) {
-      if (!finisher) {
+      if (finisher && it > 0) {
+#pragma unroll
+        for (int q = 0; q < 39; ++q) { const double2 c = S.carry[q][es]; acc[2 * q] = c.x; acc[2 * q + 1] = c.y; }
+      } else {
 #pragma unroll
         for (int q = 0; q < 78; ++q) acc[q] = 0.0;
       }
@@ -486,6 +490,9 @@ hex_sym_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
           for (int q = 0; q < 45; ++q)
             *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out(acc, 2 * q), face_out(acc, 2 * q + 1));
           if (WITH_F) face_force(acc, &S.ulay[m & 3][0][0] + ((es / EX) * UX + es % EX) * 3, sc + F_OFF);
+        } else {   // park the raw top-face sums for the next layer's finisher (after the barrier: the finishers have loaded theirs)
+#pragma unroll
+          for (int q = 0; q < 39; ++q) S.carry[q][es] = make_double2(acc[2 * q], acc[2 * q + 1]);
         }
       } else {
 #pragma unroll
