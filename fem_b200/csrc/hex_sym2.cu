@@ -1,0 +1,568 @@
+// hex_sym2.cu -- assembly variant 5: the symmetric pair-block kernel of hex_sym.cu on 16 warps.
+//
+// Same tile program, scratch layout and gather table as variant 4; what changes is the split of a cell's 36 pair
+// blocks: EIGHT threads per cell (39 / 36 accumulators, <= 128 registers) instead of four, so the CTA runs 16 warps
+// (4 per scheduler) and the latency-bound phases (geometry, G' -> K, gather) overlap much better, and f_r = K_rc u_c
+// is formed in the gather (lane products, shared-memory transposed reduction) instead of from per-cell partials.
+//
+// (header of variant 4 follows)
+// hex_sym.cu -- assembly variant 4: symmetric pair-block fused hex8 K (+ f_int) kernel.
+//
+// Variants 2/3 give every node row its own threads, which recompute K_cr = K_rc^T on both sides and
+// re-read every scaled gradient ~10 times from shared memory (2.4 FMA per loaded double: the LSU
+// wavefront pipe, not the FP64 pipe, bounds them).  Here the unit of FP64 work is the ELEMENT:
+//   * four threads per element accumulate, over the 8 integration points, the 36 unique node-pair
+//     blocks G'_ab = sum_ip g~_a g~_b^T (a <= b) in registers -- 10 pairs of the bottom/top face
+//     (78 accumulators: off-diagonal 3x3, diagonal symmetric 6) and 2 x 8 bottom x top pairs
+//     (72 accumulators) -- 5 FMA per loaded double, every operand an LDS.128;
+//   * face pairs are summed over the two elements below/above the face in registers (the two face
+//     warps alternate "start"/"finish" from layer to layer), turned into K_ab = rho G' + G'^T + tr I
+//     and parked in a per-element shared-memory scratch (234 doubles);
+//   * a gather pass, lane <-> consecutive CSR value, sums the <= 4 element contributions of every
+//     value of a node row in fixed (ascending cell) order through a 243-entry offset table, takes the
+//     transposed entry for c < r, forms f_r += K_rc u_c on the way and stores coalesced 216-byte runs.
+// One CTA (256 threads, 1 per SM) owns 7 x 7 node positions, i.e. the 8 x 8 cells touching them, and
+// marches through the node layers of a z-chunk.  No atomics, fixed summation order, each CSR value
+// stored exactly once.  Same arithmetic as FormElKE (src/m_local.F90:21-67) in the (lambda, mu)
+// block form of elem_math.cuh.
+#include "elem_math.cuh"
+#include "launch.h"
+
+namespace femx {
+
+namespace {
+
+constexpr int NX = 7, NY = 7, NP = NX * NY;   // owned node positions of a tile
+constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // cells per layer (all cells touching the tile)
+constexpr int UX = NX + 2, UY = NY + 2, UL = UX * UY;   // node positions per layer incl. halo
+constexpr int NT = 8 * EL;                    // 512 threads: 8 per cell
+constexpr int NW = NT / 32;
+constexpr int GS = 194;                       // doubles per cell in the gradient buffer (8 ip x 24 + 2; 16-byte stride odd)
+constexpr int SS = 242;                       // doubles per cell of scratch: 10 face + 16 bottom x top blocks, 8 zeros (16-byte stride odd)
+constexpr int BT_OFF = 90;
+constexpr int ZERO_OFF = 234;                 // scr[cell][ZERO_OFF..+7] = 0: target of the unused gather-table entries
+constexpr int RB = 36;                        // row pitch of the per-warp f reduction buffer
+constexpr int XP = 40;                        // doubles per row of the coordinate layer (27 used; 40 = 8 mod 16 keeps two cell rows on distinct banks)
+static_assert(EL == 64 && NT == 512, "thread mapping assumes 64 cells per layer");
+
+struct Smem {
+  union {
+    double geo[EL * GS];   // scaled gradients [cell][ip][i][node]
+    double scr[EL * SS];   // K blocks [cell][block][i][j] (written after the FMA phase has left geo)
+  } a;
+  double xlay[3][UY * XP];
+  double ulay[4][UL][3];
+  double esc[4][EL];
+  double2 carry[2][20][EL];   // top-face pair sums of the previous cell layer (raw G') of the two face threads
+  double red[NW][6][RB];      // per-warp transposed reduction of the six f sums of a node pair
+  double fcarry[NP][3];
+  HexRowMeta rowmeta[4][NP];
+  uint2 tab[5][32];        // gather table: {dz=-1, dz=+1, dz=0 rows i=0..2}[lane] -> four 16-bit byte offsets into the scratch
+  int nid[8][UL];
+};
+
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__host__ __device__ constexpr int face_index(int lx, int ly) { return ly ? (lx ? 2 : 3) : (lx ? 1 : 0); }
+__host__ __device__ constexpr int pair_q(int a, int b) { return a * 4 - a * (a - 1) / 2 + (b - a); }   // a <= b, 0..9
+
+__host__ __device__ constexpr int sym_s(int i, int j) { return i == 0 ? j : (i == 1 ? j + 2 : 5); }     // i <= j, 0..5
+
+struct Tile {
+  int i0, j0, l0, l1;
+};
+
+__device__ __forceinline__ long long cell_of(const DevHex &hx, const Tile &T, int t, int lay, bool &ok) {
+  const int ni = T.i0 - 1 + t % UX, nj = T.j0 - 1 + t / UX;
+  ok = lay >= 0 && lay < hx.NK && ni >= 0 && nj >= 0 && ni < hx.NI && nj < hx.NJ;
+  return ((long long)lay * hx.NJ + nj) * hx.NI + ni;
+}
+
+template <bool WITH_F>
+__device__ __forceinline__ void fetch_layer(Smem &S, const DevHex &hx, const Tile &T, const double *u, int lay, int tid) {
+  const int buf = lay & 3;
+  for (int t = tid; t < UL; t += NT) {
+    bool ok;
+    const long long c = cell_of(hx, T, t, lay, ok);
+    double *xb = &S.xlay[(lay + 3) % 3][(t / UX) * XP + (t % UX) * 3];
+    if (ok) {
+#pragma unroll
+      for (int d = 0; d < 3; ++d) cp_async8(xb + d, hx.pos_x + c * 3 + d);
+    } else {
+      xb[0] = 0.0; xb[1] = 0.0; xb[2] = 0.0;
+    }
+    if (WITH_F) {
+      double *ub = S.ulay[buf][t];
+      const int r = S.nid[lay & 7][t];
+      if (r >= 0) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) cp_async8(ub + d, u + (long long)r * 3 + d);
+      } else {
+        ub[0] = 0.0; ub[1] = 0.0; ub[2] = 0.0;
+      }
+    }
+    const int ux = t % UX, uy = t / UX;
+    if (ux >= 1 && ux <= NX && uy >= 1 && uy <= NY) {
+      HexRowMeta *rm = &S.rowmeta[buf][(uy - 1) * NX + (ux - 1)];
+      if (ok) {
+        const double *src = reinterpret_cast<const double *>(hx.pos_meta + c);
+#pragma unroll
+        for (int d = 0; d < 6; ++d) cp_async8(reinterpret_cast<double *>(rm) + d, src + d);
+      } else {
+        rm->nb = 0;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void fetch_nid(Smem &S, const DevHex &hx, const Tile &T, int lay, int tid) {
+  for (int t = tid; t < UL; t += NT) {
+    bool ok;
+    const long long c = cell_of(hx, T, t, lay, ok);
+    if (ok) cp_async4(&S.nid[lay & 7][t], hx.node_at + c);
+    else S.nid[lay & 7][t] = -1;
+  }
+}
+
+__device__ __forceinline__ void fetch_esc(Smem &S, const DevHex &hx, const Tile &T, int lay, int tid) {
+  for (int t = tid; t < EL; t += NT) {
+    const int ei = T.i0 - 1 + t % EX, ej = T.j0 - 1 + t / EX;
+    if (lay >= 0 && lay < hx.NK - 1 && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
+      cp_async8(&S.esc[lay & 3][t], hx.cellmu + ((long long)lay * hx.NJ + ej) * hx.NI + ei);
+    else
+      S.esc[lay & 3][t] = 0.0;
+  }
+}
+
+// gather table entry of lane l (value (kk, j) of a 27-value run) for scalar row i and group g = dz + 1
+__device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
+  unsigned o[4] = {ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8};   // byte offsets from the node's base cell
+  if (l < 27) {
+    const int kk = l / 3, j = l % 3, dy = kk / 3 - 1, dx = kk % 3 - 1;
+    int n = 0;
+    for (int oy = 0; oy < 2; ++oy)
+      for (int ox = 0; ox < 2; ++ox) {
+        const int lx = 1 - ox, ly = 1 - oy, cx = lx + dx, cy = ly + dy;   // row / column node inside cell (px+ox, py+oy)
+        if (cx < 0 || cx > 1 || cy < 0 || cy > 1) continue;
+        const int fa = face_index(lx, ly), fb = face_index(cx, cy);
+        int off;
+        if (g == 1) off = fa <= fb ? pair_q(fa, fb) * 9 + i * 3 + j : pair_q(fb, fa) * 9 + j * 3 + i;
+        else if (g == 2) off = BT_OFF + (fa * 4 + fb) * 9 + i * 3 + j;     // row node on the bottom face
+        else off = BT_OFF + (fb * 4 + fa) * 9 + j * 3 + i;                 // row node on the top face: transposed block
+        o[n++] = (unsigned)((oy * EX + ox) * SS + off) * 8u;
+      }
+  }
+  return make_uint2(o[0] | (o[1] << 16), o[2] | (o[3] << 16));
+}
+
+// scaled physical gradients g~_b(ip) = adj(J)^T grad N_b * sqrt(mu w / detJ) of cell layer m (FormdNdetJ,
+// src/m_local.F90:175-189, with the closed-form adjugate instead of dgetrf/dgetri)
+__device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
+  const double *xlo = &S.xlay[(m + 3) % 3][0], *xhi = &S.xlay[(m + 4) % 3][0];
+  const int es = tid & (EL - 1);
+  const double smu = S.esc[m & 3][es];
+  if (smu == 0.0) return;
+  const int ex = es % EX, ey = es / EX;
+  {
+    const int ip = tid >> 6;
+    // integration point ip sits beside node ip (SamPtsHex, src/m_elems.F90:500-507)
+    const bool ppx = (ip == 1) | (ip == 2) | (ip == 5) | (ip == 6), ppy = (ip == 2) | (ip == 3) | (ip == 6) | (ip == 7);
+    const double e = ppx ? FEMX_G : -FEMX_G, n = ppy ? FEMX_G : -FEMX_G, s = ip >= 4 ? FEMX_G : -FEMX_G;
+    const double fx[2] = {1.0 - e, 1.0 + e}, fy[2] = {1.0 - n, 1.0 + n}, fz[2] = {1.0 - s, 1.0 + s};
+    double J[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) J[i][j] = 0.0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+      const int bx = (b == 1 || b == 2 || b == 5 || b == 6) ? 1 : 0, by = ((b & 3) >= 2) ? 1 : 0, bz = b >> 2;
+      const double *xs = (bz ? xhi : xlo) + (ey + by) * XP + (ex + bx) * 3;
+      const double X0 = xs[0], X1 = xs[1], X2 = xs[2];
+      // ShapeFuncdHex, src/m_elems.F90:574-579
+      const double d0 = (bx ? 0.125 : -0.125) * fy[by] * fz[bz];
+      const double d1 = (by ? 0.125 : -0.125) * fx[bx] * fz[bz];
+      const double d2 = (bz ? 0.125 : -0.125) * fx[bx] * fy[by];
+      J[0][0] = fma(d0, X0, J[0][0]); J[0][1] = fma(d0, X1, J[0][1]); J[0][2] = fma(d0, X2, J[0][2]);
+      J[1][0] = fma(d1, X0, J[1][0]); J[1][1] = fma(d1, X1, J[1][1]); J[1][2] = fma(d1, X2, J[1][2]);
+      J[2][0] = fma(d2, X0, J[2][0]); J[2][1] = fma(d2, X1, J[2][1]); J[2][2] = fma(d2, X2, J[2][2]);
+    }
+    double adj[3][3];   // inverse * det
+    adj[0][0] = J[1][1] * J[2][2] - J[1][2] * J[2][1];
+    adj[0][1] = J[0][2] * J[2][1] - J[0][1] * J[2][2];
+    adj[0][2] = J[0][1] * J[1][2] - J[0][2] * J[1][1];
+    adj[1][0] = J[1][2] * J[2][0] - J[1][0] * J[2][2];
+    adj[1][1] = J[0][0] * J[2][2] - J[0][2] * J[2][0];
+    adj[1][2] = J[0][2] * J[1][0] - J[0][0] * J[1][2];
+    adj[2][0] = J[1][0] * J[2][1] - J[1][1] * J[2][0];
+    adj[2][1] = J[0][1] * J[2][0] - J[0][0] * J[2][1];
+    adj[2][2] = J[0][0] * J[1][1] - J[0][1] * J[1][0];
+    const double det = J[0][0] * adj[0][0] + J[0][1] * adj[1][0] + J[0][2] * adj[2][0];
+    const double sc = smu * rsqrt(det);   // hex weights are 1 (src/m_elems.F90:508)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) adj[i][j] *= sc;
+    double *g = &S.a.geo[es * GS + ip * 24];
+#pragma unroll
+    for (int b = 0; b < 8; b += 2) {
+      double v[2][3];
+#pragma unroll
+      for (int qq = 0; qq < 2; ++qq) {
+        const int bb = b + qq;
+        const int bx = (bb == 1 || bb == 2 || bb == 5 || bb == 6) ? 1 : 0, by = ((bb & 3) >= 2) ? 1 : 0, bz = bb >> 2;
+        const double d0 = (bx ? 0.125 : -0.125) * fy[by] * fz[bz];
+        const double d1 = (by ? 0.125 : -0.125) * fx[bx] * fz[bz];
+        const double d2 = (bz ? 0.125 : -0.125) * fx[bx] * fy[by];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[qq][i] = adj[i][0] * d0 + adj[i][1] * d1 + adj[i][2] * d2;
+      }
+#pragma unroll
+      for (int i = 0; i < 3; ++i) *reinterpret_cast<double2 *>(g + i * 8 + b) = make_double2(v[0][i], v[1][i]);
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------------------------- FMA phase
+// Face thread X owns pairs (0,1) (0,2) (0,3) and the diagonals of nodes 0, 1 of a face (27 + 12 accumulators);
+// face thread Y owns (1,2) (1,3) (2,3) and the diagonals of nodes 2, 3.  A bottom x top thread owns 2 x 2 blocks.
+__device__ __forceinline__ void load_face_x(const double *gp, double (&v)[3][4]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double2 a = *reinterpret_cast<const double2 *>(gp + i * 8);
+    const double2 b = *reinterpret_cast<const double2 *>(gp + i * 8 + 2);
+    v[i][0] = a.x; v[i][1] = a.y; v[i][2] = b.x; v[i][3] = b.y;
+  }
+}
+__device__ __forceinline__ void load_face_y(const double *gp, double (&v)[3][3]) {   // nodes 1, 2, 3
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    v[i][0] = gp[i * 8 + 1];
+    const double2 b = *reinterpret_cast<const double2 *>(gp + i * 8 + 2);
+    v[i][1] = b.x; v[i][2] = b.y;
+  }
+}
+__device__ __forceinline__ void fma_face_x(const double (&v)[3][4], double (&acc)[40]) {
+#pragma unroll
+  for (int b = 1; b < 4; ++b)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) acc[(b - 1) * 9 + i * 3 + j] = fma(v[i][0], v[j][b], acc[(b - 1) * 9 + i * 3 + j]);
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = i; j < 3; ++j) acc[27 + a * 6 + sym_s(i, j)] = fma(v[i][a], v[j][a], acc[27 + a * 6 + sym_s(i, j)]);
+}
+__device__ __forceinline__ void fma_face_y(const double (&v)[3][3], double (&acc)[40]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      acc[i * 3 + j] = fma(v[i][0], v[j][1], acc[i * 3 + j]);            // (1,2)
+      acc[9 + i * 3 + j] = fma(v[i][0], v[j][2], acc[9 + i * 3 + j]);    // (1,3)
+      acc[18 + i * 3 + j] = fma(v[i][1], v[j][2], acc[18 + i * 3 + j]);  // (2,3)
+    }
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = i; j < 3; ++j) acc[27 + a * 6 + sym_s(i, j)] = fma(v[i][1 + a], v[j][1 + a], acc[27 + a * 6 + sym_s(i, j)]);
+}
+__device__ __forceinline__ void load_bt(const double *gp, int a0, int b0, double (&va)[3][2], double (&vb)[3][2]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double2 a = *reinterpret_cast<const double2 *>(gp + i * 8 + a0);
+    const double2 b = *reinterpret_cast<const double2 *>(gp + i * 8 + 4 + b0);
+    va[i][0] = a.x; va[i][1] = a.y; vb[i][0] = b.x; vb[i][1] = b.y;
+  }
+}
+__device__ __forceinline__ void fma_bt(const double (&va)[3][2], const double (&vb)[3][2], double (&acc)[40]) {
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 2; ++b)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) acc[(a * 2 + b) * 9 + i * 3 + j] = fma(va[i][a], vb[j][b], acc[(a * 2 + b) * 9 + i * 3 + j]);
+}
+// G' -> K in place: K = rho G' + G'^T + tr(G') I  (elem_math.cuh block form of B_a^T D B_b)
+__device__ __forceinline__ void to_k_block(double *g, double rho) {
+  const double tr = g[0] + g[4] + g[8];
+  double k9[9];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) k9[i * 3 + j] = fma(rho, g[i * 3 + j], g[j * 3 + i]) + (i == j ? tr : 0.0);
+#pragma unroll
+  for (int q = 0; q < 9; ++q) g[q] = k9[q];
+}
+__device__ __forceinline__ void to_k_sym(double *g, double rho1) {   // symmetric G' (6 entries), rho1 = rho + 1
+  const double tr = g[0] + g[3] + g[5];
+#pragma unroll
+  for (int s = 0; s < 6; ++s) g[s] *= rho1;
+  g[0] += tr; g[3] += tr; g[5] += tr;
+}
+// value at flat offset `off` of a face's scratch area (blocks in pair_q order): X holds 0..44, Y holds 45..89
+__device__ __forceinline__ double face_out_x(const double (&acc)[40], int off) {
+  const int q = off / 9, r = off % 9, i = r / 3, j = r % 3;
+  if (q == 0) return acc[27 + sym_s(i < j ? i : j, i < j ? j : i)];
+  if (q == 4) return acc[33 + sym_s(i < j ? i : j, i < j ? j : i)];
+  return acc[(q - 1) * 9 + r];
+}
+__device__ __forceinline__ double face_out_y(const double (&acc)[40], int off) {
+  const int q = off / 9, r = off % 9, i = r / 3, j = r % 3;
+  if (q == 7) return acc[27 + sym_s(i < j ? i : j, i < j ? j : i)];
+  if (q == 9) return acc[33 + sym_s(i < j ? i : j, i < j ? j : i)];
+  return acc[(q == 5 ? 0 : (q == 6 ? 9 : 18)) + r];
+}
+
+// ---------------------------------------------------------------------------------- gather phase
+// one CSR value: the <= 4 cell contributions in ascending cell order (unused table entries hit the zero area);
+// OFF = byte offset of scalar row i inside the stored block (static, so it folds into the LDS immediate)
+template <int OFF>
+__device__ __forceinline__ double gather_val(const char *q0, const char *q1, const char *q2, const char *q3) {
+  const double c0 = *reinterpret_cast<const double *>(q0 + OFF);
+  const double c1 = *reinterpret_cast<const double *>(q1 + OFF);
+  const double c2 = *reinterpret_cast<const double *>(q2 + OFF);
+  const double c3 = *reinterpret_cast<const double *>(q3 + OFF);
+  return ((c0 + c1) + c2) + c3;
+}
+#define FEMX_Q4(eb, t) (eb) + ((t).x & 0xffffu), (eb) + ((t).x >> 16), (eb) + ((t).y & 0xffffu), (eb) + ((t).y >> 16)
+
+}  // namespace
+
+template <bool WITH_F>
+__global__ void __launch_bounds__(NT, 1)
+hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Smem &S = *reinterpret_cast<Smem *>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int wu = __reduce_max_sync(0xffffffffu, w);   // warp index the compiler can keep in a uniform register
+  Tile T;
+  T.i0 = blockIdx.x * NX; T.j0 = blockIdx.y * NY;
+  T.l0 = blockIdx.z * LZ; T.l1 = min(T.l0 + LZ, hx.NK) - 1;
+  const int nsteps = T.l1 - T.l0 + 2;   // cell layers l0-1 .. l1
+  const double rho = hx.rho;
+
+  // FMA-phase role (two warps each): 0/1 = bottom-face threads X/Y (finish the face started one layer below),
+  // 2/3 = top-face threads X/Y (start the next face), 4..7 = 2 x 2 bottom x top blocks
+  const int type = wu >> 1;
+  const int es = (w & 1) * 32 + lane;
+  const bool top = type >= 2, isy = (type & 1) != 0;
+  // gather-phase lane constants
+  const int gl = lane < 27 ? lane : 26;
+  const int kk = gl / 3, jj = gl % 3;
+  const int uoff = ((kk / 3) * UX + (kk % 3)) * 3 + jj;   // halo'd node (px + dx + 1, py + dy + 1), component j
+
+  for (int t = tid; t < 5 * 32; t += NT) {   // rows i > 0 of the dz = -1 / +1 groups sit at +8 i / +24 i bytes
+    const int q = t / 32;
+    S.tab[q][t % 32] = table_entry(q < 2 ? 0 : q - 2, q == 0 ? 0 : (q == 1 ? 2 : 1), t % 32);
+  }
+  if (WITH_F && tid < NP * 3) (&S.fcarry[0][0])[tid] = 0.0;
+  fetch_nid(S, hx, T, T.l0 - 1, tid); fetch_nid(S, hx, T, T.l0, tid); fetch_nid(S, hx, T, T.l0 + 1, tid);
+  fetch_esc(S, hx, T, T.l0 - 1, tid);
+  cp_async_wait_all();
+  __syncthreads();
+  fetch_layer<WITH_F>(S, hx, T, u, T.l0 - 1, tid); fetch_layer<WITH_F>(S, hx, T, u, T.l0, tid);
+
+  for (int it = 0; it < nsteps; ++it) {
+    const int m = T.l0 - 1 + it;
+    cp_async_wait_all();
+    __syncthreads();              // layer data of m, m+1 is in; the previous gather has left the scratch
+    if (!(dbg & 1)) geometry(S, m, tid);
+    __syncthreads();
+    // prefetch for the next step: ids of m+3, node layer m+2, cell scale of m+1
+    fetch_nid(S, hx, T, m + 3, tid);
+    fetch_layer<WITH_F>(S, hx, T, u, m + 2, tid);
+    fetch_esc(S, hx, T, m + 1, tid);
+
+    // ------------------------------------------------------------------ FMA phase
+    const bool cell_on = S.esc[m & 3][es] != 0.0;
+    const double *g = &S.a.geo[es * GS];
+    double acc[40];
+    if (type < 4) {
+      if (!top && it > 0) {
+#pragma unroll
+        for (int q = 0; q < 20; ++q) { const double2 c = S.carry[isy][q][es]; acc[2 * q] = c.x; acc[2 * q + 1] = c.y; }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 40; ++q) acc[q] = 0.0;
+      }
+      const bool need = top ? it + 1 < nsteps : it > 0;   // first finish / last start feed no owned row
+      if (cell_on && need && !(dbg & 2)) {
+        const double *gf = g + (top ? 4 : 0);
+        if (isy) {
+#pragma unroll 2
+          for (int ip = 0; ip < 8; ++ip) {
+            double v[3][3];
+            load_face_y(gf + ip * 24, v);
+            fma_face_y(v, acc);
+          }
+        } else {
+#pragma unroll 2
+          for (int ip = 0; ip < 8; ++ip) {
+            double v[3][4];
+            load_face_x(gf + ip * 24, v);
+            fma_face_x(v, acc);
+          }
+        }
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 40; ++q) acc[q] = 0.0;
+      if (cell_on && !(dbg & 2)) {
+        const int a0 = ((type - 4) >> 1) * 2, b0 = ((type - 4) & 1) * 2;
+#pragma unroll 2
+        for (int ip = 0; ip < 8; ++ip) {
+          double va[3][2], vb[3][2];
+          load_bt(g + ip * 24, a0, b0, va, vb);
+          fma_bt(va, vb, acc);
+        }
+      }
+    }
+    __syncthreads();              // everybody has left the gradient buffer
+    // ------------------------------------------------------------------ G' -> K, park in the scratch
+    {
+      double *sc = &S.a.scr[es * SS];
+      if (type < 4) {
+        if (!top) {
+#pragma unroll
+          for (int p = 0; p < 3; ++p) to_k_block(&acc[p * 9], rho);
+          to_k_sym(&acc[27], rho + 1.0);
+          to_k_sym(&acc[33], rho + 1.0);
+          if (isy) {
+            sc[45] = face_out_y(acc, 45);
+#pragma unroll
+            for (int q = 23; q < 45; ++q)
+              *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out_y(acc, 2 * q), face_out_y(acc, 2 * q + 1));
+          } else {
+#pragma unroll
+            for (int q = 0; q < 22; ++q)
+              *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out_x(acc, 2 * q), face_out_x(acc, 2 * q + 1));
+            sc[44] = face_out_x(acc, 44);
+          }
+        } else {   // park the raw top-face sums for the next layer's finisher (after the barrier: the finishers have loaded theirs)
+#pragma unroll
+          for (int q = 0; q < 20; ++q) S.carry[isy][q][es] = make_double2(acc[2 * q], acc[2 * q + 1]);
+        }
+      } else {
+        const int a0 = ((type - 4) >> 1) * 2, b0 = ((type - 4) & 1) * 2;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) to_k_block(&acc[p * 9], rho);
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          double *dst = sc + BT_OFF + ((a0 + a) * 4 + b0) * 9;
+#pragma unroll
+          for (int q = 0; q < 9; ++q) *reinterpret_cast<double2 *>(dst + 2 * q) = make_double2(acc[a * 18 + 2 * q], acc[a * 18 + 2 * q + 1]);
+        }
+        if (type == 7) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<double2 *>(sc + ZERO_OFF + 2 * q) = make_double2(0.0, 0.0);
+        }
+      }
+    }
+    __syncthreads();
+    // ------------------------------------------------------------------ gather: rows of node layer m (dz = 0, +1) and m+1 (dz = -1)
+    const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
+    if (!(dbg & 4)) {
+      const uint2 t0 = S.tab[0][lane], t2 = S.tab[1][lane], t10 = S.tab[2][lane], t11 = S.tab[3][lane], t12 = S.tab[4][lane];
+      double *rb = &S.red[wu][0][0];
+      for (int n = wu; n < NP; n += NW) {
+        const int px = n % NX, py = n / NX;
+        const char *eb = reinterpret_cast<const char *>(&S.a.scr[(py * EX + px) * SS]);
+        const HexRowMeta *rlo = &S.rowmeta[m & 3][n], *rhi = &S.rowmeta[(m + 1) & 3][n];
+        const bool act_lo = lay_lo && rlo->nb > 0, act_hi = lay_hi && rhi->nb > 0;
+        // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
+        const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
+        const bool on0 = act_hi && lane < 27 && k0 != 255, on1 = act_lo && lane < 27 && k1 != 255, on2 = act_lo && lane < 27 && k2 != 255;
+        double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
+        const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
+        double v[9];
+        v[0] = gather_val<0>(FEMX_Q4(eb, t0)); v[3] = gather_val<8>(FEMX_Q4(eb, t0)); v[6] = gather_val<16>(FEMX_Q4(eb, t0));
+        v[2] = gather_val<0>(FEMX_Q4(eb, t2)); v[5] = gather_val<24>(FEMX_Q4(eb, t2)); v[8] = gather_val<48>(FEMX_Q4(eb, t2));
+        v[1] = gather_val<0>(FEMX_Q4(eb, t10)); v[4] = gather_val<0>(FEMX_Q4(eb, t11)); v[7] = gather_val<0>(FEMX_Q4(eb, t12));
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          if (on0) p0[i * rs_hi] = v[i * 3 + 0];
+          if (on1) p1[i * rs_lo] = v[i * 3 + 1];
+          if (on2) p2[i * rs_lo] = v[i * 3 + 2];
+        }
+        if (WITH_F) {
+          // f_r = sum_c K_rc u_c: lane products, transposed through shared memory, summed in fixed order
+          const double ulo = (&S.ulay[m & 3][0][0])[(py * UX + px) * 3 + uoff];
+          const double uhi = (&S.ulay[(m + 1) & 3][0][0])[(py * UX + px) * 3 + uoff];
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            rb[i * RB + lane] = fma(v[i * 3 + 1], ulo, v[i * 3 + 2] * uhi);   // lower node: dz = 0, +1 parts
+            rb[(3 + i) * RB + lane] = v[i * 3 + 0] * ulo;                     // upper node: dz = -1 part
+          }
+          __syncwarp();
+          const int val = lane >> 2, seg = lane & 3;
+          double s = 0.0, c = 0.0;
+          if (lane < 24) {
+            const double *r = rb + val * RB + seg;
+            s = r[0];
+#pragma unroll
+            for (int q = 1; q < 8; ++q) s += r[4 * q];
+            s += __shfl_xor_sync(0x00ffffffu, s, 1);
+            s += __shfl_xor_sync(0x00ffffffu, s, 2);
+            c = S.fcarry[n][val % 3];
+          }
+          __syncwarp();
+          if (lane < 24 && seg == 0) {
+            // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
+            if (val < 3) { if (act_lo) fint[(long long)rlo->grow + val] = c + s; }
+            else S.fcarry[n][val - 3] = act_hi ? s : 0.0;
+          }
+        }
+      }
+    }
+  }
+}
+
+int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+  const DevHex &hx = c->dhex;
+  const int tiles = ((hx.NI + NX - 1) / NX) * ((hx.NJ + NY - 1) / NY);
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+  // z-chunk length: fewest (waves x steps per chunk); every chunk pays one extra cell layer plus the prologue
+  int LZ = c->opts.reserved[1] > 0 ? c->opts.reserved[1] : 0;
+  if (LZ <= 0) {
+    double best = 1e300;
+    for (int nch = 1; nch <= hx.NK; ++nch) {
+      const int lz = (hx.NK + nch - 1) / nch, chunks = (hx.NK + lz - 1) / lz;
+      const long long ctas = (long long)tiles * chunks;
+      const double waves = (double)((ctas + nsm - 1) / nsm);
+      const double cost = waves * (lz + 2.0);
+      if (cost < best) { best = cost; LZ = lz; }
+    }
+  }
+  if (LZ > hx.NK) LZ = hx.NK;
+  dim3 grid((hx.NI + NX - 1) / NX, (hx.NJ + NY - 1) / NY, (hx.NK + LZ - 1) / LZ);
+  const size_t smem = sizeof(Smem);
+  static_assert(sizeof(Smem) <= 232448, "shared memory of variant 5 exceeds the 227 KB a CTA may opt into");
+  if (d_u) {
+    cudaFuncSetAttribute(hex_sym2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    hex_sym2_kernel<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+  } else {
+    cudaFuncSetAttribute(hex_sym2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    hex_sym2_kernel<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+  }
+  return 1;
+}
+
+}  // namespace femx

@@ -292,13 +292,13 @@ def test_fused_hex_variant_vs_oracle_and_twopass(orc):
                 assert close(v3, va_o, TOL_MAT), (name, "ws", lz)
                 assert close(f3int, f_o, TOL_MAT), (name, "ws", lz)
                 assert np.array_equal(f3.assemble_K(), v3), (name, "ws", lz)
-        for lz in (0, 25, 3):                                # symmetric pair-block kernel (variant 4)
-            with api.Femx(assembly_variant=4, lz=lz) as f4:
+        for var, lz in ((4, 0), (4, 25), (4, 3), (5, 0), (5, 25), (5, 3)):   # symmetric pair-block kernels (variants 4, 5)
+            with api.Femx(assembly_variant=var, lz=lz) as f4:
                 f4.set_mesh(m).build_plan()
                 v4, f4int = f4.assemble_K_fint(u)
-                assert close(v4, va_o, TOL_MAT), (name, "sym", lz)
-                assert close(f4int, f_o, TOL_MAT), (name, "sym", lz)
-                assert np.array_equal(f4.assemble_K(), v4), (name, "sym", lz)
+                assert close(v4, va_o, TOL_MAT), (name, "sym", var, lz)
+                assert close(f4int, f_o, TOL_MAT), (name, "sym", var, lz)
+                assert np.array_equal(f4.assemble_K(), v4), (name, "sym", var, lz)
         with api.Femx(assembly_variant=1) as f1:
             v1 = f1.set_mesh(m).build_plan().assemble_K()
         assert close(v1, va_o, TOL_MAT), name
