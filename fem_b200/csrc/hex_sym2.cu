@@ -32,32 +32,33 @@ namespace femx {
 
 namespace {
 
-constexpr int NX = 7, NY = 7, NP = NX * NY;   // owned node positions of a tile
-constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // cells per layer (all cells touching the tile)
+constexpr int NX = 8, NY = 6, NP = NX * NY;   // owned node positions of a tile: 48 = 3 per warp in the gather
+constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // 63 cells per layer (all cells touching the tile)
+constexpr int ELP = 64;                       // padded cell count (thread mapping: 8 threads per cell slot)
 constexpr int UX = NX + 2, UY = NY + 2, UL = UX * UY;   // node positions per layer incl. halo
-constexpr int NT = 8 * EL;                    // 512 threads: 8 per cell
+constexpr int NT = 8 * ELP;                   // 512 threads: 8 per cell
 constexpr int NW = NT / 32;
 constexpr int GS = 194;                       // doubles per cell in the gradient buffer (8 ip x 24 + 2; 16-byte stride odd)
-constexpr int SS = 242;                       // doubles per cell of scratch: 10 face + 16 bottom x top blocks, 8 zeros (16-byte stride odd)
-constexpr int BT_OFF = 90;
-constexpr int ZERO_OFF = 234;                 // scr[cell][ZERO_OFF..+7] = 0: target of the unused gather-table entries
-constexpr int RB = 36;                        // row pitch of the per-warp f reduction buffer
+constexpr int SS = 297;                       // doubles per cell of scratch (odd: cell-strided 8-byte stores hit 16 distinct banks)
+// Scratch of a cell = two 4 x 4 node matrices of 3x3 blocks (face pairs incl. transposes; bottom x top pairs), each stored
+// as rows [node a][i] of 12 doubles [node b][j], nodes in row-major (ly, lx) order, node pitch 37, row pitch 12.  Found by
+// exhaustive search: with these pitches every gather load (27 / 15 / 3 lanes) is within one wavefront of conflict-free.
+constexpr int FACE_OFF = 0, BT_OFF = 148, SA = 37, SI = 12;
 constexpr int XP = 40;                        // doubles per row of the coordinate layer (27 used; 40 = 8 mod 16 keeps two cell rows on distinct banks)
-static_assert(EL == 64 && NT == 512, "thread mapping assumes 64 cells per layer");
+static_assert(EL <= ELP && NT == 512 && NP % (NT / 32) == 0, "thread mapping assumes <= 64 cells and a node count divisible by the warps");
 
 struct Smem {
   union {
-    double geo[EL * GS];   // scaled gradients [cell][ip][i][node]
-    double scr[EL * SS];   // K blocks [cell][block][i][j] (written after the FMA phase has left geo)
+    double geo[ELP * GS];   // scaled gradients [cell][ip][i][node]
+    double scr[ELP * SS];   // K blocks [cell][block][i][j] (written after the FMA phase has left geo)
   } a;
   double xlay[3][UY * XP];
   double ulay[4][UL][3];
-  double esc[4][EL];
-  double2 carry[2][20][EL];   // top-face pair sums of the previous cell layer (raw G') of the two face threads
-  double red[NW][6][RB];      // per-warp transposed reduction of the six f sums of a node pair
+  double esc[4][ELP];
+  double2 carry[2][20][ELP];   // top-face pair sums of the previous cell layer (raw G') of the two face threads
   double fcarry[NP][3];
   HexRowMeta rowmeta[4][NP];
-  uint2 tab[5][32];        // gather table: {dz=-1, dz=+1, dz=0 rows i=0..2}[lane] -> four 16-bit byte offsets into the scratch
+  uint2 tab[3][32];        // gather table: [dz + 1][lane] -> four 16-bit byte offsets (row i = 0) into the scratch
   int nid[8][UL];
 };
 
@@ -133,18 +134,20 @@ __device__ __forceinline__ void fetch_nid(Smem &S, const DevHex &hx, const Tile 
 }
 
 __device__ __forceinline__ void fetch_esc(Smem &S, const DevHex &hx, const Tile &T, int lay, int tid) {
-  for (int t = tid; t < EL; t += NT) {
+  for (int t = tid; t < ELP; t += NT) {
     const int ei = T.i0 - 1 + t % EX, ej = T.j0 - 1 + t / EX;
-    if (lay >= 0 && lay < hx.NK - 1 && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
+    if (t < EL && lay >= 0 && lay < hx.NK - 1 && ei >= 0 && ej >= 0 && ei < hx.NI && ej < hx.NJ)
       cp_async8(&S.esc[lay & 3][t], hx.cellmu + ((long long)lay * hx.NJ + ej) * hx.NI + ei);
     else
       S.esc[lay & 3][t] = 0.0;
   }
 }
 
-// gather table entry of lane l (value (kk, j) of a 27-value run) for scalar row i and group g = dz + 1
-__device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
-  unsigned o[4] = {ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8, ZERO_OFF * 8};   // byte offsets from the node's base cell
+__host__ __device__ constexpr int rm_index(int lx, int ly) { return ly * 2 + lx; }   // row-major node index inside a face
+// gather table entry of lane l (value (kk, j) of a 27-value run) for group g = dz + 1, scalar row i = 0; row i sits
+// +8 i bytes further for dz = -1 (transposed block) and +8 SI i bytes for dz = 0, +1
+__device__ __forceinline__ uint2 table_entry(int g, int l) {
+  unsigned o[4] = {0, 0, 0, 0};
   if (l < 27) {
     const int kk = l / 3, j = l % 3, dy = kk / 3 - 1, dx = kk % 3 - 1;
     int n = 0;
@@ -152,11 +155,11 @@ __device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
       for (int ox = 0; ox < 2; ++ox) {
         const int lx = 1 - ox, ly = 1 - oy, cx = lx + dx, cy = ly + dy;   // row / column node inside cell (px+ox, py+oy)
         if (cx < 0 || cx > 1 || cy < 0 || cy > 1) continue;
-        const int fa = face_index(lx, ly), fb = face_index(cx, cy);
+        const int fa = rm_index(lx, ly), fb = rm_index(cx, cy);
         int off;
-        if (g == 1) off = fa <= fb ? pair_q(fa, fb) * 9 + i * 3 + j : pair_q(fb, fa) * 9 + j * 3 + i;
-        else if (g == 2) off = BT_OFF + (fa * 4 + fb) * 9 + i * 3 + j;     // row node on the bottom face
-        else off = BT_OFF + (fb * 4 + fa) * 9 + j * 3 + i;                 // row node on the top face: transposed block
+        if (g == 1) off = FACE_OFF + fa * SA + fb * 3 + j;
+        else if (g == 2) off = BT_OFF + fa * SA + fb * 3 + j;      // row node on the bottom face
+        else off = BT_OFF + fb * SA + j * SI + fa * 3;             // row node on the top face: transposed block
         o[n++] = (unsigned)((oy * EX + ox) * SS + off) * 8u;
       }
   }
@@ -167,7 +170,7 @@ __device__ __forceinline__ uint2 table_entry(int i, int g, int l) {
 // src/m_local.F90:175-189, with the closed-form adjugate instead of dgetrf/dgetri)
 __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
   const double *xlo = &S.xlay[(m + 3) % 3][0], *xhi = &S.xlay[(m + 4) % 3][0];
-  const int es = tid & (EL - 1);
+  const int es = tid & (ELP - 1);
   const double smu = S.esc[m & 3][es];
   if (smu == 0.0) return;
   const int ex = es % EX, ey = es / EX;
@@ -316,32 +319,43 @@ __device__ __forceinline__ void to_k_sym(double *g, double rho1) {   // symmetri
   for (int s = 0; s < 6; ++s) g[s] *= rho1;
   g[0] += tr; g[3] += tr; g[5] += tr;
 }
-// value at flat offset `off` of a face's scratch area (blocks in pair_q order): X holds 0..44, Y holds 45..89
-__device__ __forceinline__ double face_out_x(const double (&acc)[40], int off) {
-  const int q = off / 9, r = off % 9, i = r / 3, j = r % 3;
-  if (q == 0) return acc[27 + sym_s(i < j ? i : j, i < j ? j : i)];
-  if (q == 4) return acc[33 + sym_s(i < j ? i : j, i < j ? j : i)];
-  return acc[(q - 1) * 9 + r];
+// block K_ab of face nodes (row-major indices ra, rb) and its transpose into the 4 x 4 node matrix at m
+__device__ __forceinline__ void put_pair(double *m, int ra, int rb, const double *k) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      m[ra * SA + i * SI + rb * 3 + j] = k[i * 3 + j];
+      m[rb * SA + j * SI + ra * 3 + i] = k[i * 3 + j];
+    }
 }
-__device__ __forceinline__ double face_out_y(const double (&acc)[40], int off) {
-  const int q = off / 9, r = off % 9, i = r / 3, j = r % 3;
-  if (q == 7) return acc[27 + sym_s(i < j ? i : j, i < j ? j : i)];
-  if (q == 9) return acc[33 + sym_s(i < j ? i : j, i < j ? j : i)];
-  return acc[(q == 5 ? 0 : (q == 6 ? 9 : 18)) + r];
+__device__ __forceinline__ void put_diag(double *m, int ra, const double *k6) {   // symmetric block, 6 stored entries
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) m[ra * SA + i * SI + ra * 3 + j] = k6[sym_s(i < j ? i : j, i < j ? j : i)];
 }
 
 // ---------------------------------------------------------------------------------- gather phase
-// one CSR value: the <= 4 cell contributions in ascending cell order (unused table entries hit the zero area);
-// OFF = byte offset of scalar row i inside the stored block (static, so it folds into the LDS immediate)
+// one CSR value: the <= 4 cell contributions in ascending cell order.  Loads of contributions a lane does not have are
+// predicated off (no shared-memory wavefront for them); OFF = byte offset of scalar row i inside the stored block.
 template <int OFF>
-__device__ __forceinline__ double gather_val(const char *q0, const char *q1, const char *q2, const char *q3) {
-  const double c0 = *reinterpret_cast<const double *>(q0 + OFF);
-  const double c1 = *reinterpret_cast<const double *>(q1 + OFF);
-  const double c2 = *reinterpret_cast<const double *>(q2 + OFF);
-  const double c3 = *reinterpret_cast<const double *>(q3 + OFF);
+__device__ __forceinline__ double lds_pred(unsigned addr, int on) {
+  double v;
+  asm volatile("{\n .reg .pred p;\n setp.ne.s32 p, %2, 0;\n mov.f64 %0, 0d0000000000000000;\n @p ld.shared.f64 %0, [%1+%3];\n}"
+               : "=d"(v) : "r"(addr), "r"(on), "n"(OFF) : "memory");
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ double gather_val(unsigned eb, const uint2 t, int on0, int on1, int on2) {
+  const double c0 = lds_pred<OFF>(eb + (t.x & 0xffffu), on0);
+  const double c1 = lds_pred<OFF>(eb + (t.x >> 16), on1);
+  const double c2 = lds_pred<OFF>(eb + (t.y & 0xffffu), on2);
+  const double c3 = lds_pred<OFF>(eb + (t.y >> 16), on2);
   return ((c0 + c1) + c2) + c3;
 }
-#define FEMX_Q4(eb, t) (eb) + ((t).x & 0xffffu), (eb) + ((t).x >> 16), (eb) + ((t).y & 0xffffu), (eb) + ((t).y >> 16)
+
+__device__ __forceinline__ bool v_dummy(const double *p) { return p == nullptr; }   // diagnostic: never true
 
 }  // namespace
 
@@ -367,11 +381,10 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   const int gl = lane < 27 ? lane : 26;
   const int kk = gl / 3, jj = gl % 3;
   const int uoff = ((kk / 3) * UX + (kk % 3)) * 3 + jj;   // halo'd node (px + dx + 1, py + dy + 1), component j
+  // cells contributing to this lane's value: 4 around the node itself, 2 along an edge neighbour, 1 for a diagonal one
+  const int c_on0 = lane < 27, c_on1 = lane < 27 && (kk & 1 || kk == 4), c_on2 = lane < 27 && kk == 4;
 
-  for (int t = tid; t < 5 * 32; t += NT) {   // rows i > 0 of the dz = -1 / +1 groups sit at +8 i / +24 i bytes
-    const int q = t / 32;
-    S.tab[q][t % 32] = table_entry(q < 2 ? 0 : q - 2, q == 0 ? 0 : (q == 1 ? 2 : 1), t % 32);
-  }
+  for (int t = tid; t < 3 * 32; t += NT) S.tab[t / 32][t % 32] = table_entry(t / 32, t % 32);
   if (WITH_F && tid < NP * 3) (&S.fcarry[0][0])[tid] = 0.0;
   fetch_nid(S, hx, T, T.l0 - 1, tid); fetch_nid(S, hx, T, T.l0, tid); fetch_nid(S, hx, T, T.l0 + 1, tid);
   fetch_esc(S, hx, T, T.l0 - 1, tid);
@@ -444,16 +457,12 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
           for (int p = 0; p < 3; ++p) to_k_block(&acc[p * 9], rho);
           to_k_sym(&acc[27], rho + 1.0);
           to_k_sym(&acc[33], rho + 1.0);
-          if (isy) {
-            sc[45] = face_out_y(acc, 45);
-#pragma unroll
-            for (int q = 23; q < 45; ++q)
-              *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out_y(acc, 2 * q), face_out_y(acc, 2 * q + 1));
-          } else {
-#pragma unroll
-            for (int q = 0; q < 22; ++q)
-              *reinterpret_cast<double2 *>(sc + 2 * q) = make_double2(face_out_x(acc, 2 * q), face_out_x(acc, 2 * q + 1));
-            sc[44] = face_out_x(acc, 44);
+          if (isy) {   // CCW nodes 1, 2, 3 = row-major 1, 3, 2
+            put_pair(sc + FACE_OFF, 1, 3, &acc[0]); put_pair(sc + FACE_OFF, 1, 2, &acc[9]); put_pair(sc + FACE_OFF, 3, 2, &acc[18]);
+            put_diag(sc + FACE_OFF, 3, &acc[27]); put_diag(sc + FACE_OFF, 2, &acc[33]);
+          } else {     // CCW nodes 0, 1 = row-major 0, 1
+            put_pair(sc + FACE_OFF, 0, 1, &acc[0]); put_pair(sc + FACE_OFF, 0, 3, &acc[9]); put_pair(sc + FACE_OFF, 0, 2, &acc[18]);
+            put_diag(sc + FACE_OFF, 0, &acc[27]); put_diag(sc + FACE_OFF, 1, &acc[33]);
           }
         } else {   // park the raw top-face sums for the next layer's finisher (after the barrier: the finishers have loaded theirs)
 #pragma unroll
@@ -464,69 +473,71 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 #pragma unroll
         for (int p = 0; p < 4; ++p) to_k_block(&acc[p * 9], rho);
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
-          double *dst = sc + BT_OFF + ((a0 + a) * 4 + b0) * 9;
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-          for (int q = 0; q < 9; ++q) *reinterpret_cast<double2 *>(dst + 2 * q) = make_double2(acc[a * 18 + 2 * q], acc[a * 18 + 2 * q + 1]);
-        }
-        if (type == 7) {
+          for (int b = 0; b < 2; ++b) {
+            const int ra = (a0 + a) ^ ((a0 + a) >> 1), rb = (b0 + b) ^ ((b0 + b) >> 1);   // CCW -> row-major node index
+            double *dst = sc + BT_OFF + ra * SA + rb * 3;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) *reinterpret_cast<double2 *>(sc + ZERO_OFF + 2 * q) = make_double2(0.0, 0.0);
-        }
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+              for (int j = 0; j < 3; ++j) dst[i * SI + j] = acc[(a * 2 + b) * 9 + i * 3 + j];
+          }
       }
     }
     __syncthreads();
     // ------------------------------------------------------------------ gather: rows of node layer m (dz = 0, +1) and m+1 (dz = -1)
     const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
     if (!(dbg & 4)) {
-      const uint2 t0 = S.tab[0][lane], t2 = S.tab[1][lane], t10 = S.tab[2][lane], t11 = S.tab[3][lane], t12 = S.tab[4][lane];
-      double *rb = &S.red[wu][0][0];
+      const uint2 t0 = S.tab[0][lane], t1 = S.tab[1][lane], t2 = S.tab[2][lane];
+      const bool upper = (lane & 16) != 0;
+#pragma unroll
       for (int n = wu; n < NP; n += NW) {
         const int px = n % NX, py = n / NX;
-        const char *eb = reinterpret_cast<const char *>(&S.a.scr[(py * EX + px) * SS]);
+        const unsigned eb = (unsigned)__cvta_generic_to_shared(&S.a.scr[(py * EX + px) * SS]);
         const HexRowMeta *rlo = &S.rowmeta[m & 3][n], *rhi = &S.rowmeta[(m + 1) & 3][n];
         const bool act_lo = lay_lo && rlo->nb > 0, act_hi = lay_hi && rhi->nb > 0;
         // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
         const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
-        const bool on0 = act_hi && lane < 27 && k0 != 255, on1 = act_lo && lane < 27 && k1 != 255, on2 = act_lo && lane < 27 && k2 != 255;
+        const bool st = !(dbg & 8) || v_dummy(vals);
+        const bool on0 = st && act_hi && lane < 27 && k0 != 255, on1 = st && act_lo && lane < 27 && k1 != 255, on2 = st && act_lo && lane < 27 && k2 != 255;
         double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
         const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
         double v[9];
-        v[0] = gather_val<0>(FEMX_Q4(eb, t0)); v[3] = gather_val<8>(FEMX_Q4(eb, t0)); v[6] = gather_val<16>(FEMX_Q4(eb, t0));
-        v[2] = gather_val<0>(FEMX_Q4(eb, t2)); v[5] = gather_val<24>(FEMX_Q4(eb, t2)); v[8] = gather_val<48>(FEMX_Q4(eb, t2));
-        v[1] = gather_val<0>(FEMX_Q4(eb, t10)); v[4] = gather_val<0>(FEMX_Q4(eb, t11)); v[7] = gather_val<0>(FEMX_Q4(eb, t12));
+        v[0] = gather_val<0>(eb, t0, c_on0, c_on1, c_on2); v[3] = gather_val<8>(eb, t0, c_on0, c_on1, c_on2); v[6] = gather_val<16>(eb, t0, c_on0, c_on1, c_on2);
+        v[2] = gather_val<0>(eb, t2, c_on0, c_on1, c_on2); v[5] = gather_val<8 * SI>(eb, t2, c_on0, c_on1, c_on2); v[8] = gather_val<16 * SI>(eb, t2, c_on0, c_on1, c_on2);
+        v[1] = gather_val<0>(eb, t1, c_on0, c_on1, c_on2); v[4] = gather_val<8 * SI>(eb, t1, c_on0, c_on1, c_on2); v[7] = gather_val<16 * SI>(eb, t1, c_on0, c_on1, c_on2);
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           if (on0) p0[i * rs_hi] = v[i * 3 + 0];
           if (on1) p1[i * rs_lo] = v[i * 3 + 1];
           if (on2) p2[i * rs_lo] = v[i * 3 + 2];
         }
-        if (WITH_F) {
-          // f_r = sum_c K_rc u_c: lane products, transposed through shared memory, summed in fixed order
+        if (WITH_F && !(dbg & 16)) {
+          // f_r = sum_c K_rc u_c: lane products, butterfly-summed (fixed order); lanes 0-15 end up with the three
+          // sums of the lower node, lanes 16-31 with those of the upper node
           const double ulo = (&S.ulay[m & 3][0][0])[(py * UX + px) * 3 + uoff];
           const double uhi = (&S.ulay[(m + 1) & 3][0][0])[(py * UX + px) * 3 + uoff];
+          double keep[3];
 #pragma unroll
           for (int i = 0; i < 3; ++i) {
-            rb[i * RB + lane] = fma(v[i * 3 + 1], ulo, v[i * 3 + 2] * uhi);   // lower node: dz = 0, +1 parts
-            rb[(3 + i) * RB + lane] = v[i * 3 + 0] * ulo;                     // upper node: dz = -1 part
+            const double flo = fma(v[i * 3 + 1], ulo, v[i * 3 + 2] * uhi), fhi = v[i * 3 + 0] * ulo;
+            keep[i] = (upper ? fhi : flo) + __shfl_xor_sync(0xffffffffu, upper ? flo : fhi, 16);
           }
-          __syncwarp();
-          const int val = lane >> 2, seg = lane & 3;
-          double s = 0.0, c = 0.0;
-          if (lane < 24) {
-            const double *r = rb + val * RB + seg;
-            s = r[0];
 #pragma unroll
-            for (int q = 1; q < 8; ++q) s += r[4 * q];
-            s += __shfl_xor_sync(0x00ffffffu, s, 1);
-            s += __shfl_xor_sync(0x00ffffffu, s, 2);
-            c = S.fcarry[n][val % 3];
+          for (int d = 8; d >= 1; d >>= 1)
+#pragma unroll
+            for (int i = 0; i < 3; ++i) keep[i] += __shfl_xor_sync(0xffffffffu, keep[i], d);
+          const int li = lane & 15;
+          if (li < 3) {
+            const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
+            // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
+            if (!upper) { if (act_lo) fint[(long long)rlo->grow + li] = S.fcarry[n][li] + mine; }
           }
           __syncwarp();
-          if (lane < 24 && seg == 0) {
-            // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
-            if (val < 3) { if (act_lo) fint[(long long)rlo->grow + val] = c + s; }
-            else S.fcarry[n][val - 3] = act_hi ? s : 0.0;
+          if (li < 3 && upper) {
+            const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
+            S.fcarry[n][li] = act_hi ? mine : 0.0;
           }
         }
       }
