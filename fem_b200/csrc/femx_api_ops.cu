@@ -56,7 +56,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
-    const int av = c->opts.assembly_variant;
+    const int av = c->opts.assembly_variant == 0 ? 5 : c->opts.assembly_variant;   // auto = the 16-warp symmetric kernel
     c->launches += av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint) : av == 4 ? launch_hex_sym(c, d_u, d_vals, d_fint)
                    : (av == 3 ? launch_hex_ws(c, d_u, d_vals, d_fint) : launch_hex_fused(c, d_u, d_vals, d_fint));
   } else {

@@ -61,11 +61,12 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh, 1 = two-pass
- * (element kernel -> packed Ke scratch -> ordered gather), 2 = fused tile kernel */
+/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, else 1),
+ * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
+ * 3 = its warp-specialised form, 4 / 5 = symmetric pair-block kernel on 8 / 16 warps */
 typedef struct {
   int quirks;            /* FEMX_Q_* bits                                   */
-  int assembly_variant;  /* 0 auto, 1 two-pass, 2 fused                     */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 2..5 fused hex8 kernels     */
   int reserved[6];
 } femx_opts;
 
