@@ -48,17 +48,25 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (u_local && (rc = stage_in(c, u_local, nloc, where, &c->d_u, &d_u))) return rc;
   if ((rc = stage_out(c, vals, c->nnz, where, &c->d_vals, &d_vals))) return rc;
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
-  const bool fused = c->hex.ok && c->opts.assembly_variant != 1;
-  if (!fused) {
+  // auto (0): the 16-warp symmetric tile kernel for a logical hex8 grid, else the fused rows kernel, else two-pass
+  const int av0 = c->opts.assembly_variant;
+  const bool fused = c->hex.ok && av0 != 1 && av0 != 9;
+  const bool rows = !fused && av0 != 1 && rows_fused_ok(c);
+  if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
+  if (!fused && !rows) {
     if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
     if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
   }
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
-    const int av = c->opts.assembly_variant == 0 ? 5 : c->opts.assembly_variant;   // auto = the 16-warp symmetric kernel
-    c->launches += av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint) : av == 4 ? launch_hex_sym(c, d_u, d_vals, d_fint)
+    const int av = av0 == 0 ? 5 : av0;
+    c->launches += av == 8 ? launch_hex_sym5(c, d_u, d_vals, d_fint) : av == 7 ? launch_hex_sym4(c, d_u, d_vals, d_fint)
+                   : av == 6 ? launch_hex_sym3(c, d_u, d_vals, d_fint) : av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint)
+                   : av == 4 ? launch_hex_sym(c, d_u, d_vals, d_fint)
                    : (av == 3 ? launch_hex_ws(c, d_u, d_vals, d_fint) : launch_hex_fused(c, d_u, d_vals, d_fint));
+  } else if (rows) {
+    c->launches += launch_rows_fused(c, d_u, d_vals, d_fint);
   } else {
     c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
     c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);

@@ -40,6 +40,12 @@ struct Plan {
   std::vector<int64_t> ke_off;     // [nels+1] offsets (doubles) of packed Ke scratch: nen^2*pd^2
   std::vector<int64_t> fe_off;     // [nels+1] offsets of per-element vectors: nen*pd
   int64_t nblk = 0;
+  // row gather lists for the fused rows kernel (variant 9): for node r and block k of its row, the contributing
+  // (incident element index, local node b) pairs in ascending element order
+  std::vector<int64_t> rbe_ptr;    // [nlnds+1] first entry of node r in rb_ent
+  std::vector<uint16_t> rb_off;    // node r: nb+1 node-local offsets at [bptr[r] + r ...]
+  std::vector<uint8_t> rb_ent;     // (incident index << 3) | b
+  int max_inc = 0;                 // largest number of elements around a node
   // cohesive overlay: blocks / nodes touched by nonlinear elements, contributions ascending
   std::vector<int32_t> coh_elems;        // local element ids with enlmat != 0
   std::vector<int64_t> cblk_id;          // touched block ids (r-major order)
@@ -104,6 +110,9 @@ struct DevMesh {
   int32_t *bcol = nullptr, *bdiag = nullptr, *n2e_elem = nullptr;
   uint8_t *n2e_a = nullptr;
   uint16_t *bpos = nullptr;
+  int64_t *rbe_ptr = nullptr;
+  uint16_t *rb_off = nullptr;
+  uint8_t *rb_ent = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 

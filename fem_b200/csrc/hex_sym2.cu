@@ -25,6 +25,8 @@
 // marches through the node layers of a z-chunk.  No atomics, fixed summation order, each CSR value
 // stored exactly once.  Same arithmetic as FormElKE (src/m_local.F90:21-67) in the (lambda, mu)
 // block form of elem_math.cuh.
+#include <cstdio>
+
 #include "elem_math.cuh"
 #include "launch.h"
 
@@ -32,11 +34,24 @@ namespace femx {
 
 namespace {
 
-constexpr int NX = 8, NY = 6, NP = NX * NY;   // owned node positions of a tile: 48 = 3 per warp in the gather
+// Tile configuration (hex_sym3.cu includes this file with a half-size tile and two CTAs per SM = variant 6)
+#ifndef FEMX_SYM_NX
+#define FEMX_SYM_NX 8
+#define FEMX_SYM_NY 6
+#define FEMX_SYM_ELP 64
+#define FEMX_SYM_CTAS 1
+#define FEMX_SYM_TPC 8
+#define FEMX_SYM_KERNEL hex_sym2_kernel
+#define FEMX_SYM_LAUNCH launch_hex_sym2
+#endif
+constexpr int NX = FEMX_SYM_NX, NY = FEMX_SYM_NY, NP = NX * NY;   // owned node positions of a tile (8 x 6: 3 per warp in the gather)
 constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // 63 cells per layer (all cells touching the tile)
-constexpr int ELP = 64;                       // padded cell count (thread mapping: 8 threads per cell slot)
+constexpr int ELP = FEMX_SYM_ELP;             // padded cell count (thread mapping: 8 threads per cell slot)
+constexpr int WPT = ELP / 32;                 // warps per FMA-phase role
+constexpr int CTAS = FEMX_SYM_CTAS;           // resident CTAs per SM
 constexpr int UX = NX + 2, UY = NY + 2, UL = UX * UY;   // node positions per layer incl. halo
-constexpr int NT = 8 * ELP;                   // 512 threads: 8 per cell
+constexpr int TPC = FEMX_SYM_TPC;              // threads per cell in the FMA phase: 8 (39 / 36 accumulators) or 4 (78 / 72)
+constexpr int NT = TPC * ELP;
 constexpr int NW = NT / 32;
 constexpr int GS = 194;                       // doubles per cell in the gradient buffer (8 ip x 24 + 2; 16-byte stride odd)
 constexpr int SS = 297;                       // doubles per cell of scratch (odd: cell-strided 8-byte stores hit 16 distinct banks)
@@ -45,7 +60,7 @@ constexpr int SS = 297;                       // doubles per cell of scratch (od
 // exhaustive search: with these pitches every gather load (27 / 15 / 3 lanes) is within one wavefront of conflict-free.
 constexpr int FACE_OFF = 0, BT_OFF = 148, SA = 37, SI = 12;
 constexpr int XP = 40;                        // doubles per row of the coordinate layer (27 used; 40 = 8 mod 16 keeps two cell rows on distinct banks)
-static_assert(EL <= ELP && NT == 512 && NP % (NT / 32) == 0, "thread mapping assumes <= 64 cells and a node count divisible by the warps");
+static_assert(EL <= ELP && (ELP == 32 || ELP == 64), "thread mapping assumes 32 or 64 cell slots");
 
 struct Smem {
   union {
@@ -55,7 +70,7 @@ struct Smem {
   double xlay[3][UY * XP];
   double ulay[4][UL][3];
   double esc[4][ELP];
-  double2 carry[2][20][ELP];   // top-face pair sums of the previous cell layer (raw G') of the two face threads
+  double2 carry[TPC == 8 ? 2 : 1][TPC == 8 ? 20 : 39][ELP];   // top-face pair sums of the previous cell layer (raw G') of the two face threads
   double fcarry[NP][3];
   HexRowMeta rowmeta[4][NP];
   uint2 tab[3][32];        // gather table: [dz + 1][lane] -> four 16-bit byte offsets (row i = 0) into the scratch
@@ -174,8 +189,9 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
   const double smu = S.esc[m & 3][es];
   if (smu == 0.0) return;
   const int ex = es % EX, ey = es / EX;
-  {
-    const int ip = tid >> 6;
+#pragma unroll
+  for (int q = 0; q < 8 / TPC; ++q) {
+    const int ip = tid / ELP + TPC * q;
     // integration point ip sits beside node ip (SamPtsHex, src/m_elems.F90:500-507)
     const bool ppx = (ip == 1) | (ip == 2) | (ip == 5) | (ip == 6), ppy = (ip == 2) | (ip == 3) | (ip == 6) | (ip == 7);
     const double e = ppx ? FEMX_G : -FEMX_G, n = ppy ? FEMX_G : -FEMX_G, s = ip >= 4 ? FEMX_G : -FEMX_G;
@@ -336,6 +352,47 @@ __device__ __forceinline__ void put_diag(double *m, int ra, const double *k6) { 
     for (int j = 0; j < 3; ++j) m[ra * SA + i * SI + ra * 3 + j] = k6[sym_s(i < j ? i : j, i < j ? j : i)];
 }
 
+#if FEMX_SYM_TPC == 4
+// four threads per cell: one thread owns all 10 pairs of a face (78 accumulators), one 2 x 4 bottom x top blocks (72)
+__host__ __device__ constexpr int offdiag_p(int a, int b) { return a == 0 ? b - 1 : (a == 1 ? b + 1 : 5); }   // a < b, 0..5
+__device__ __forceinline__ void fma_face4(const double (&v)[3][4], double (&acc)[78]) {
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = a + 1; b < 4; ++b)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) acc[offdiag_p(a, b) * 9 + i * 3 + j] = fma(v[i][a], v[j][b], acc[offdiag_p(a, b) * 9 + i * 3 + j]);
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = i; j < 3; ++j) acc[54 + a * 6 + sym_s(i, j)] = fma(v[i][a], v[j][a], acc[54 + a * 6 + sym_s(i, j)]);
+}
+__device__ __forceinline__ void load_bt4(const double *gp, int a0, double (&va)[3][2], double (&vb)[3][4]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double2 a = *reinterpret_cast<const double2 *>(gp + i * 8 + a0);
+    const double2 b = *reinterpret_cast<const double2 *>(gp + i * 8 + 4);
+    const double2 c = *reinterpret_cast<const double2 *>(gp + i * 8 + 6);
+    va[i][0] = a.x; va[i][1] = a.y;
+    vb[i][0] = b.x; vb[i][1] = b.y; vb[i][2] = c.x; vb[i][3] = c.y;
+  }
+}
+__device__ __forceinline__ void fma_bt4(const double (&va)[3][2], const double (&vb)[3][4], double (&acc)[78]) {
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) acc[(a * 4 + b) * 9 + i * 3 + j] = fma(va[i][a], vb[j][b], acc[(a * 4 + b) * 9 + i * 3 + j]);
+}
+#endif
+
 // ---------------------------------------------------------------------------------- gather phase
 // one CSR value: the <= 4 cell contributions in ascending cell order.  Loads of contributions a lane does not have are
 // predicated off (no shared-memory wavefront for them); OFF = byte offset of scalar row i inside the stored block.
@@ -360,8 +417,8 @@ __device__ __forceinline__ bool v_dummy(const double *p) { return p == nullptr; 
 }  // namespace
 
 template <bool WITH_F>
-__global__ void __launch_bounds__(NT, 1)
-hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg) {
+__global__ void __launch_bounds__(NT, CTAS)
+FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -374,9 +431,11 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 
   // FMA-phase role (two warps each): 0/1 = bottom-face threads X/Y (finish the face started one layer below),
   // 2/3 = top-face threads X/Y (start the next face), 4..7 = 2 x 2 bottom x top blocks
-  const int type = wu >> 1;
-  const int es = (w & 1) * 32 + lane;
+  const int type = wu / WPT;
+  const int es = (w % WPT) * 32 + lane;
+#if FEMX_SYM_TPC == 8
   const bool top = type >= 2, isy = (type & 1) != 0;
+#endif
   // gather-phase lane constants
   const int gl = lane < 27 ? lane : 26;
   const int kk = gl / 3, jj = gl % 3;
@@ -384,6 +443,10 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   // cells contributing to this lane's value: 4 around the node itself, 2 along an edge neighbour, 1 for a diagonal one
   const int c_on0 = lane < 27, c_on1 = lane < 27 && (kk & 1 || kk == 4), c_on2 = lane < 27 && kk == 4;
 
+  if (CTAS > 1 && (dbg >> 8) > 0) {   // diagnostic: start the second resident CTA of an SM (dbg >> 8) x 256 clocks late
+    const int lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if ((lin / 148) & 1) { const long long t0 = clock64(); while (clock64() - t0 < (long long)(dbg >> 8) * 256) { } }
+  }
   for (int t = tid; t < 3 * 32; t += NT) S.tab[t / 32][t % 32] = table_entry(t / 32, t % 32);
   if (WITH_F && tid < NP * 3) (&S.fcarry[0][0])[tid] = 0.0;
   fetch_nid(S, hx, T, T.l0 - 1, tid); fetch_nid(S, hx, T, T.l0, tid); fetch_nid(S, hx, T, T.l0 + 1, tid);
@@ -406,6 +469,7 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
     // ------------------------------------------------------------------ FMA phase
     const bool cell_on = S.esc[m & 3][es] != 0.0;
     const double *g = &S.a.geo[es * GS];
+#if FEMX_SYM_TPC == 8
     double acc[40];
     if (type < 4) {
       if (!top && it > 0) {
@@ -485,6 +549,73 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
           }
       }
     }
+#else
+    double acc[78];
+    if (type < 2) {
+      const bool topf = type == 1;
+      if (!topf && it > 0) {
+#pragma unroll
+        for (int q = 0; q < 39; ++q) { const double2 c = S.carry[0][q][es]; acc[2 * q] = c.x; acc[2 * q + 1] = c.y; }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 78; ++q) acc[q] = 0.0;
+      }
+      const bool need = topf ? it + 1 < nsteps : it > 0;   // first finish / last start feed no owned row
+      if (cell_on && need && !(dbg & 2)) {
+        const double *gf = g + (topf ? 4 : 0);
+#pragma unroll 2
+        for (int ip = 0; ip < 8; ++ip) {
+          double v[3][4];
+          load_face_x(gf + ip * 24, v);
+          fma_face4(v, acc);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 78; ++q) acc[q] = 0.0;
+      if (cell_on && !(dbg & 2)) {
+        const int a0 = (type - 2) * 2;
+#pragma unroll 2
+        for (int ip = 0; ip < 8; ++ip) {
+          double va[3][2], vb[3][4];
+          load_bt4(g + ip * 24, a0, va, vb);
+          fma_bt4(va, vb, acc);
+        }
+      }
+    }
+    __syncthreads();              // everybody has left the gradient buffer
+    // ------------------------------------------------------------------ G' -> K, park in the scratch
+    {
+      double *sc = &S.a.scr[es * SS];
+      if (type == 0) {   // CCW face nodes 0, 1, 2, 3 = row-major 0, 1, 3, 2
+#pragma unroll
+        for (int p = 0; p < 6; ++p) to_k_block(&acc[p * 9], rho);
+#pragma unroll
+        for (int a = 0; a < 4; ++a) to_k_sym(&acc[54 + a * 6], rho + 1.0);
+        put_pair(sc + FACE_OFF, 0, 1, &acc[0]); put_pair(sc + FACE_OFF, 0, 3, &acc[9]); put_pair(sc + FACE_OFF, 0, 2, &acc[18]);
+        put_pair(sc + FACE_OFF, 1, 3, &acc[27]); put_pair(sc + FACE_OFF, 1, 2, &acc[36]); put_pair(sc + FACE_OFF, 3, 2, &acc[45]);
+        put_diag(sc + FACE_OFF, 0, &acc[54]); put_diag(sc + FACE_OFF, 1, &acc[60]); put_diag(sc + FACE_OFF, 3, &acc[66]); put_diag(sc + FACE_OFF, 2, &acc[72]);
+      } else if (type == 1) {   // park the raw top-face sums for the next layer's finisher (after the barrier: the finishers have loaded theirs)
+#pragma unroll
+        for (int q = 0; q < 39; ++q) S.carry[0][q][es] = make_double2(acc[2 * q], acc[2 * q + 1]);
+      } else {
+        const int a0 = (type - 2) * 2;
+#pragma unroll
+        for (int p = 0; p < 8; ++p) to_k_block(&acc[p * 9], rho);
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const int ra = (a0 + a) ^ ((a0 + a) >> 1), rb = b ^ (b >> 1);   // CCW -> row-major node index
+            double *dst = sc + BT_OFF + ra * SA + rb * 3;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+              for (int j = 0; j < 3; ++j) dst[i * SI + j] = acc[(a * 4 + b) * 9 + i * 3 + j];
+          }
+      }
+    }
+#endif
     __syncthreads();
     // ------------------------------------------------------------------ gather: rows of node layer m (dz = 0, +1) and m+1 (dz = -1)
     const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
@@ -545,7 +676,7 @@ hex_sym2_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   }
 }
 
-int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
   const DevHex &hx = c->dhex;
   const int tiles = ((hx.NI + NX - 1) / NX) * ((hx.NJ + NY - 1) / NY);
   int nsm = 148;
@@ -557,7 +688,7 @@ int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
     for (int nch = 1; nch <= hx.NK; ++nch) {
       const int lz = (hx.NK + nch - 1) / nch, chunks = (hx.NK + lz - 1) / lz;
       const long long ctas = (long long)tiles * chunks;
-      const double waves = (double)((ctas + nsm - 1) / nsm);
+      const double waves = (double)((ctas + nsm * CTAS - 1) / (nsm * CTAS));
       const double cost = waves * (lz + 2.0);
       if (cost < best) { best = cost; LZ = lz; }
     }
@@ -565,13 +696,22 @@ int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
   if (LZ > hx.NK) LZ = hx.NK;
   dim3 grid((hx.NI + NX - 1) / NX, (hx.NJ + NY - 1) / NY, (hx.NK + LZ - 1) / LZ);
   const size_t smem = sizeof(Smem);
-  static_assert(sizeof(Smem) <= 232448, "shared memory of variant 5 exceeds the 227 KB a CTA may opt into");
+  static_assert(sizeof(Smem) <= (CTAS == 1 ? 232448 : 115712), "shared memory exceeds what the resident CTAs of an SM may opt into");
+  if (c->opts.reserved[2] & 32) {
+    int nb = -1;
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, FEMX_SYM_KERNEL<true>, NT, smem);
+    fprintf(stderr, "femx: sym kernel smem %zu B, %d resident CTAs per SM, grid %d x %d x %d, LZ %d\n", smem, nb, grid.x, grid.y, grid.z, LZ);
+  }
   if (d_u) {
-    cudaFuncSetAttribute(hex_sym2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_sym2_kernel<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    FEMX_SYM_KERNEL<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   } else {
-    cudaFuncSetAttribute(hex_sym2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hex_sym2_kernel<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    FEMX_SYM_KERNEL<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   }
   return 1;
 }

@@ -27,5 +27,10 @@ int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_f
 int launch_hex_ws(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+int launch_hex_sym3(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+int launch_hex_sym4(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+int launch_hex_sym5(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+bool rows_fused_ok(const femx_ctx *c);
+int launch_rows_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 
 }  // namespace femx

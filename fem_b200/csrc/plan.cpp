@@ -106,6 +106,40 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
       }
     }
   });
+  // row gather lists (fused rows kernel): invert bpos per node
+  {
+    P->rbe_ptr.assign(nlnds + 1, 0);
+    P->max_inc = 0;
+    for (int r = 0; r < nlnds; ++r) {
+      int64_t n = 0;
+      for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p) { const int e = P->n2e_elem[p]; n += eptr[e + 1] - eptr[e]; }
+      P->rbe_ptr[r + 1] = P->rbe_ptr[r] + n;
+      P->max_inc = std::max(P->max_inc, (int)(P->n2e_ptr[r + 1] - P->n2e_ptr[r]));
+    }
+    P->rb_off.assign((size_t)P->nblk + nlnds, 0);
+    P->rb_ent.assign((size_t)P->rbe_ptr[nlnds], 0);
+    if (P->max_inc <= 32)
+      parallel_for(nlnds, [&](int64_t lo, int64_t hi) {
+        std::vector<int32_t> cntk;
+        for (int64_t r = lo; r < hi; ++r) {
+          const int nb = (int)(P->bptr[r + 1] - P->bptr[r]);
+          cntk.assign(nb + 1, 0);
+          for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p) {
+            const int e = P->n2e_elem[p], a = P->n2e_a[p], nen = eptr[e + 1] - eptr[e];
+            for (int b = 0; b < nen; ++b) ++cntk[P->bpos[P->eb_ptr[e] + a * nen + b] + 1];
+          }
+          for (int k = 0; k < nb; ++k) cntk[k + 1] += cntk[k];
+          uint16_t *off = &P->rb_off[P->bptr[r] + r];
+          for (int k = 0; k <= nb; ++k) off[k] = (uint16_t)cntk[k];
+          uint8_t *ent = &P->rb_ent[P->rbe_ptr[r]];
+          int idx = 0;
+          for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p, ++idx) {   // ascending element order
+            const int e = P->n2e_elem[p], a = P->n2e_a[p], nen = eptr[e + 1] - eptr[e];
+            for (int b = 0; b < nen; ++b) ent[cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++] = (uint8_t)((idx << 3) | b);
+          }
+        }
+      });
+  }
   // cohesive overlay (elements with nlMat != 0, src/m_global.F90:130-150, :188-206)
   P->coh_elems.clear();
   for (int e = 0; e < nels; ++e)

@@ -1,0 +1,169 @@
+// rows_fused.cu -- assembly variant 9: fused gather-ordered assembly for ANY element mix (tri3, quad4, tet4, hex8,
+// cohesive), the general-mesh counterpart of the hex8 tile kernels.
+//
+// The two-pass path (kernels.cu) writes every element matrix to HBM and reads it back (tet4: 1.15 kB each way for
+// 215 B of compulsory traffic).  Here the element row blocks never leave the SM:
+//   phase A  a group of G lanes (G = power of two >= the largest number of elements around a node) owns one node
+//            row; lane i computes row-block a_i of Ke of the i-th incident element (ke_row_blocks, FormElKE
+//            src/m_local.F90:21-67) and its share f = K_a. u_e of the internal force into its shared-memory slot;
+//   phase B  the same lanes walk the node's CSR values in storage order (lane <-> consecutive value, coalesced
+//            stores) and sum, per value, the contributing (element, local node b) entries listed by the plan in
+//            ascending element order -- MatSetValues(ADD_VALUES) semantics (src/main.F90:157-171) without atomics,
+//            each value written exactly once.
+// Plan data read per node: the incidence list and one byte per (element, b) contribution.
+#include "elem_math.cuh"
+#include "launch.h"
+
+namespace femx {
+
+namespace {
+
+constexpr int kWarps = 8;
+
+template <int T>
+__device__ __forceinline__ void row_of(const DevMesh &dm, int e, int a, const double *__restrict__ u, double *out, int foff) {
+  constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, D2 = DIM * DIM;
+  if constexpr (T == FEMX_COH) {
+    // E = nu = 0 -> D = 0 (src/m_global.F90:250-252): explicit zero blocks that still enter the pattern
+#pragma unroll
+    for (int q = 0; q < NEN * D2; ++q) out[q] = 0.0;
+#pragma unroll
+    for (int i = 0; i < DIM; ++i) out[foff + i] = 0.0;
+  } else {
+    const int32_t *cn = dm.conn0 + dm.eptr[e];
+    double X[NEN][DIM];
+    int nd[NEN];
+#pragma unroll
+    for (int b = 0; b < NEN; ++b) {
+      nd[b] = cn[b];
+#pragma unroll
+      for (int d = 0; d < DIM; ++d) X[b][d] = dm.coords[(int64_t)nd[b] * DIM + d];
+    }
+    const int m = dm.emat[e] - 1;
+    const double lam = dm.lam_mu[2 * m], mu = dm.lam_mu[2 * m + 1];
+    double acc[NEN][D2];
+    ke_row_blocks<T>(X, a, lam, mu, acc);
+#pragma unroll
+    for (int b = 0; b < NEN; ++b)
+#pragma unroll
+      for (int q = 0; q < D2; ++q) out[b * D2 + q] = acc[b][q];
+    if (u) {
+      double f[DIM];
+#pragma unroll
+      for (int i = 0; i < DIM; ++i) f[i] = 0.0;
+#pragma unroll
+      for (int b = 0; b < NEN; ++b)
+#pragma unroll
+        for (int j = 0; j < DIM; ++j) {
+          const double ub = u[(int64_t)nd[b] * DIM + j];
+#pragma unroll
+          for (int i = 0; i < DIM; ++i) f[i] += acc[b][i * DIM + j] * ub;
+        }
+#pragma unroll
+      for (int i = 0; i < DIM; ++i) out[foff + i] = f[i];
+    }
+  }
+}
+
+template <int PD, int G, bool HEX>   // HEX: the mesh holds hex8 elements (keeps their 72 accumulators out of tet-only builds)
+__global__ void __launch_bounds__(kWarps * 32)
+fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int slot, int foff) {
+  extern __shared__ double sm_rows[];
+  constexpr int D2 = PD * PD, NPW = 32 / G;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int gl = lane % G, gi = lane / G;
+  double *mine = sm_rows + ((size_t)w * 32 + lane) * slot;
+  const double *grp = sm_rows + ((size_t)w * 32 + gi * G) * slot;
+  const int64_t ngroups = ((int64_t)dm.nlnds + NPW - 1) / NPW;
+  for (int64_t wg = (int64_t)blockIdx.x * kWarps + w; wg < ngroups; wg += (int64_t)gridDim.x * kWarps) {
+    const int64_t r = wg * NPW + gi;
+    const bool node_on = r < dm.nlnds;
+    int64_t p0 = 0;
+    int ninc = 0;
+    if (node_on) { p0 = dm.n2e_ptr[r]; ninc = (int)(dm.n2e_ptr[r + 1] - p0); }
+    // ---- phase A: one incident element per lane
+    if (gl < ninc) {
+      const int e = dm.n2e_elem[p0 + gl], a = dm.n2e_a[p0 + gl];
+      const int t = dm.etype[e];
+      if constexpr (PD == 2) {
+        if (t == FEMX_QUA) row_of<FEMX_QUA>(dm, e, a, u, mine, foff);
+        else if (t == FEMX_TRI) row_of<FEMX_TRI>(dm, e, a, u, mine, foff);
+        else row_of<FEMX_COH>(dm, e, a, u, mine, foff);
+      } else {
+        if (!HEX || t == FEMX_TET) row_of<FEMX_TET>(dm, e, a, u, mine, foff);
+        else if constexpr (HEX) row_of<FEMX_HEX>(dm, e, a, u, mine, foff);
+      }
+    }
+    __syncwarp();
+    // ---- phase B: the node's CSR values in storage order
+    if (node_on) {
+      const int64_t b0 = dm.bptr[r];
+      const int nb = (int)(dm.bptr[r + 1] - b0);
+      const int rowlen = PD * nb, nv = PD * rowlen;
+      const uint16_t *off = dm.rb_off + b0 + r;
+      const uint8_t *ent = dm.rb_ent + dm.rbe_ptr[r];
+      double *vrow = vals + D2 * b0;
+      for (int v = gl; v < nv; v += G) {
+        const int i = v / rowlen, rem = v - i * rowlen, k = rem / PD, j = rem - k * PD;
+        const int c1 = off[k + 1];
+        double s = 0.0;
+        for (int c = off[k]; c < c1; ++c) {
+          const int en = ent[c];
+          s += grp[(en >> 3) * slot + (en & 7) * D2 + i * PD + j];
+        }
+        vrow[v] = s;
+      }
+      if (fint && gl < PD) {
+        double s = 0.0;
+        for (int q = 0; q < ninc; ++q) s += grp[q * slot + foff + gl];
+        fint[(int64_t)PD * (dm.nl2g[r] - 1) + gl] = s;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+template <int PD, int G, bool HEX>
+int launch_g(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int slot, int foff) {
+  const size_t smem = (size_t)kWarps * 32 * slot * sizeof(double);
+  cudaFuncSetAttribute(fused_rows_kernel<PD, G, HEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  int nsm = 148, per_sm = 1;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_rows_kernel<PD, G, HEX>, kWarps * 32, smem);
+  if (per_sm < 1) per_sm = 1;
+  const int64_t ngroups = ((int64_t)c->nlnds + 32 / G - 1) / (32 / G);
+  int64_t grid = (ngroups + kWarps - 1) / kWarps;
+  const int64_t cap = (int64_t)nsm * per_sm * 4;   // a few CTAs per resident slot, grid-stride over the rest
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  fused_rows_kernel<PD, G, HEX><<<(unsigned)grid, kWarps * 32, smem, c->stream>>>(c->dm, d_u, d_vals, d_fint, slot, foff);
+  return 1;
+}
+
+template <int PD, bool HEX>
+int launch_pd(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int g, int slot, int foff) {
+  switch (g) {
+    case 4: return launch_g<PD, 4, HEX>(c, d_u, d_vals, d_fint, slot, foff);
+    case 8: return launch_g<PD, 8, HEX>(c, d_u, d_vals, d_fint, slot, foff);
+    case 16: return launch_g<PD, 16, HEX>(c, d_u, d_vals, d_fint, slot, foff);
+    default: return launch_g<PD, 32, HEX>(c, d_u, d_vals, d_fint, slot, foff);
+  }
+}
+
+}  // namespace
+
+bool rows_fused_ok(const femx_ctx *c) { return c->plan.max_inc >= 1 && c->plan.max_inc <= 32; }
+
+int launch_rows_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+  int g = 4;
+  while (g < c->plan.max_inc) g *= 2;
+  int maxnen = 3;
+  for (const auto &b : c->buckets) maxnen = maxnen > type_nen(b.type) ? maxnen : type_nen(b.type);
+  const int pd = c->pdim, foff = maxnen * pd * pd;
+  int slot = foff + pd;
+  if (slot % 2 == 0) ++slot;   // odd pitch: the lane-strided 8-byte stores of phase A hit distinct banks
+  if (pd == 2) return launch_pd<2, false>(c, d_u, d_vals, d_fint, g, slot, foff);
+  return maxnen == 8 ? launch_pd<3, true>(c, d_u, d_vals, d_fint, g, slot, foff) : launch_pd<3, false>(c, d_u, d_vals, d_fint, g, slot, foff);
+}
+
+}  // namespace femx

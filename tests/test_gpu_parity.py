@@ -127,6 +127,27 @@ def test_pattern_values_fint_vs_oracle(fx, orc, golden):
         assert np.array_equal(kb[pen], vb_o[pen]) and close(kb[~pen], vb_o[~pen], TOL_MAT, np.abs(va_o).max()), name
 
 
+def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
+    """Variant 9 (fused rows kernel: element row blocks stay in shared memory) against variant 1 (two-pass through
+    the packed Ke scratch) and the oracle, on every element mix incl. cohesive zeros and an unstructured hex mesh."""
+    cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("tet_jitter", mg.jitter(mg.tet_cube(5)))]
+    for name, m in cases:
+        u = mg.displacement_field(m)
+        om = orc.Mesh(m)
+        _, _, va_o = orc.assemble_K(om).export(om.ndof)
+        f_o = orc.fint(om, u.reshape(-1))
+        res = {}
+        for var in (9, 1):
+            with api.Femx(assembly_variant=var) as f:
+                f.set_mesh(m).build_plan()
+                vals, fint = f.assemble_K_fint(u)
+                assert close(vals, va_o, TOL_MAT), (name, var)
+                assert close(fint, f_o, TOL_MAT), (name, var)
+                assert np.array_equal(f.assemble_K(), vals), (name, var)
+                res[var] = vals
+        assert np.array_equal(res[9], res[1]), name      # same per-entry summation order: identical bits
+
+
 def test_golden_matview_through_cuda(golden):
     """examples/tmp.txt: the Jacobian of cohesive_test_2.inp, now from the CUDA path."""
     g = golden["jacobian_matview_cohesive_test_2"]
@@ -292,7 +313,7 @@ def test_fused_hex_variant_vs_oracle_and_twopass(orc):
                 assert close(v3, va_o, TOL_MAT), (name, "ws", lz)
                 assert close(f3int, f_o, TOL_MAT), (name, "ws", lz)
                 assert np.array_equal(f3.assemble_K(), v3), (name, "ws", lz)
-        for var, lz in ((4, 0), (4, 25), (4, 3), (5, 0), (5, 25), (5, 3)):   # symmetric pair-block kernels (variants 4, 5)
+        for var, lz in ((4, 0), (4, 25), (4, 3), (5, 0), (5, 25), (5, 3), (6, 0), (6, 25), (6, 3), (7, 0), (7, 25), (7, 3), (8, 0), (8, 3)):   # symmetric pair-block kernels
             with api.Femx(assembly_variant=var, lz=lz) as f4:
                 f4.set_mesh(m).build_plan()
                 v4, f4int = f4.assemble_K_fint(u)
