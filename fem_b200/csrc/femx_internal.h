@@ -44,7 +44,8 @@ struct Plan {
   // (incident element index, local node b) pairs in ascending element order
   std::vector<int64_t> rbe_ptr;    // [nlnds+1] first entry of node r in rb_ent
   std::vector<uint16_t> rb_off;    // node r: nb+1 node-local offsets at [bptr[r] + r ...]
-  std::vector<uint8_t> rb_ent;     // (incident index << 3) | b
+  std::vector<uint16_t> rb_ent;    // shared-memory offset (doubles) of the contributing block: incident index * rb_slot + b * pd^2
+  int rb_slot = 0, rb_foff = 0;    // slot pitch per incident element (odd) and offset of its f share inside the slot
   int max_inc = 0;                 // largest number of elements around a node
   // cohesive overlay: blocks / nodes touched by nonlinear elements, contributions ascending
   std::vector<int32_t> coh_elems;        // local element ids with enlmat != 0
@@ -112,7 +113,7 @@ struct DevMesh {
   uint16_t *bpos = nullptr;
   int64_t *rbe_ptr = nullptr;
   uint16_t *rb_off = nullptr;
-  uint8_t *rb_ent = nullptr;
+  uint16_t *rb_ent = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 

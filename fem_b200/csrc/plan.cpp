@@ -116,6 +116,13 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
       P->rbe_ptr[r + 1] = P->rbe_ptr[r] + n;
       P->max_inc = std::max(P->max_inc, (int)(P->n2e_ptr[r + 1] - P->n2e_ptr[r]));
     }
+    int maxnen = 3;
+    for (int e = 0; e < nels; ++e) maxnen = std::max(maxnen, eptr[e + 1] - eptr[e]);
+    const int d2 = pdim * pdim;
+    P->rb_foff = maxnen * d2;
+    P->rb_slot = P->rb_foff + pdim;
+    if (P->rb_slot % 2 == 0) ++P->rb_slot;   // odd pitch: lane-strided 8-byte stores hit distinct banks
+    const int slot = P->rb_slot;
     P->rb_off.assign((size_t)P->nblk + nlnds, 0);
     P->rb_ent.assign((size_t)P->rbe_ptr[nlnds], 0);
     if (P->max_inc <= 32)
@@ -131,11 +138,11 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
           for (int k = 0; k < nb; ++k) cntk[k + 1] += cntk[k];
           uint16_t *off = &P->rb_off[P->bptr[r] + r];
           for (int k = 0; k <= nb; ++k) off[k] = (uint16_t)cntk[k];
-          uint8_t *ent = &P->rb_ent[P->rbe_ptr[r]];
+          uint16_t *ent = &P->rb_ent[P->rbe_ptr[r]];
           int idx = 0;
           for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p, ++idx) {   // ascending element order
             const int e = P->n2e_elem[p], a = P->n2e_a[p], nen = eptr[e + 1] - eptr[e];
-            for (int b = 0; b < nen; ++b) ent[cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++] = (uint8_t)((idx << 3) | b);
+            for (int b = 0; b < nen; ++b) ent[cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++] = (uint16_t)(idx * slot + b * d2);
           }
         }
       });

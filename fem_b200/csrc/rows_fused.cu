@@ -70,53 +70,103 @@ __global__ void __launch_bounds__(kWarps * 32)
 fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int slot, int foff) {
   extern __shared__ double sm_rows[];
   constexpr int D2 = PD * PD, NPW = 32 / G;
+  constexpr int PARTS = G / D2;                  // lanes per diagonal-block value when the group is wide enough to split it
+  constexpr bool SPLIT = PARTS >= 2;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int gl = lane % G, gi = lane / G;
   double *mine = sm_rows + ((size_t)w * 32 + lane) * slot;
   const double *grp = sm_rows + ((size_t)w * 32 + gi * G) * slot;
   const int64_t ngroups = ((int64_t)dm.nlnds + NPW - 1) / NPW;
-  for (int64_t wg = (int64_t)blockIdx.x * kWarps + w; wg < ngroups; wg += (int64_t)gridDim.x * kWarps) {
+  const int64_t stride = (int64_t)gridDim.x * kWarps;
+  // incidence of the first node group; the next one is fetched while the current one is being processed
+  int64_t wg = (int64_t)blockIdx.x * kWarps + w;
+  int ninc = 0, e = 0, a = 0;
+  {
+    const int64_t r = wg * NPW + gi;
+    if (wg < ngroups && r < dm.nlnds) {
+      const int64_t p0 = dm.n2e_ptr[r];
+      ninc = (int)(dm.n2e_ptr[r + 1] - p0);
+      if (gl < ninc) { e = dm.n2e_elem[p0 + gl]; a = dm.n2e_a[p0 + gl]; }
+    }
+  }
+  for (; wg < ngroups; wg += stride) {
     const int64_t r = wg * NPW + gi;
     const bool node_on = r < dm.nlnds;
-    int64_t p0 = 0;
-    int ninc = 0;
-    if (node_on) { p0 = dm.n2e_ptr[r]; ninc = (int)(dm.n2e_ptr[r + 1] - p0); }
+    const int ninc_cur = ninc, e_cur = e, a_cur = a;
+    {   // prefetch
+      const int64_t rn = (wg + stride) * NPW + gi;
+      ninc = 0;
+      if (wg + stride < ngroups && rn < dm.nlnds) {
+        const int64_t p0 = dm.n2e_ptr[rn];
+        ninc = (int)(dm.n2e_ptr[rn + 1] - p0);
+        if (gl < ninc) { e = dm.n2e_elem[p0 + gl]; a = dm.n2e_a[p0 + gl]; }
+      }
+    }
     // ---- phase A: one incident element per lane
-    if (gl < ninc) {
-      const int e = dm.n2e_elem[p0 + gl], a = dm.n2e_a[p0 + gl];
-      const int t = dm.etype[e];
+    if (gl < ninc_cur) {
+      const int t = dm.etype[e_cur];
       if constexpr (PD == 2) {
-        if (t == FEMX_QUA) row_of<FEMX_QUA>(dm, e, a, u, mine, foff);
-        else if (t == FEMX_TRI) row_of<FEMX_TRI>(dm, e, a, u, mine, foff);
-        else row_of<FEMX_COH>(dm, e, a, u, mine, foff);
+        if (t == FEMX_QUA) row_of<FEMX_QUA>(dm, e_cur, a_cur, u, mine, foff);
+        else if (t == FEMX_TRI) row_of<FEMX_TRI>(dm, e_cur, a_cur, u, mine, foff);
+        else row_of<FEMX_COH>(dm, e_cur, a_cur, u, mine, foff);
       } else {
-        if (!HEX || t == FEMX_TET) row_of<FEMX_TET>(dm, e, a, u, mine, foff);
-        else if constexpr (HEX) row_of<FEMX_HEX>(dm, e, a, u, mine, foff);
+        if (!HEX || t == FEMX_TET) row_of<FEMX_TET>(dm, e_cur, a_cur, u, mine, foff);
+        else if constexpr (HEX) row_of<FEMX_HEX>(dm, e_cur, a_cur, u, mine, foff);
       }
     }
     __syncwarp();
     // ---- phase B: the node's CSR values in storage order
+    const unsigned on_mask = __ballot_sync(0xffffffffu, node_on);
     if (node_on) {
       const int64_t b0 = dm.bptr[r];
       const int nb = (int)(dm.bptr[r + 1] - b0);
       const int rowlen = PD * nb, nv = PD * rowlen;
       const uint16_t *off = dm.rb_off + b0 + r;
-      const uint8_t *ent = dm.rb_ent + dm.rbe_ptr[r];
+      const uint16_t *ent = dm.rb_ent + dm.rbe_ptr[r];
       double *vrow = vals + D2 * b0;
+      const int kd = SPLIT ? dm.bdiag[r] : -1;   // the diagonal block has one contribution per incident element: split it
       for (int v = gl; v < nv; v += G) {
-        const int i = v / rowlen, rem = v - i * rowlen, k = rem / PD, j = rem - k * PD;
+        const int i = (v >= rowlen) + (PD == 3 && v >= 2 * rowlen), rem = v - i * rowlen, k = rem / PD, j = rem - k * PD;
+        if (k == kd) continue;
+        const double *src = grp + i * PD + j;
+        int c = off[k];
         const int c1 = off[k + 1];
         double s = 0.0;
-        for (int c = off[k]; c < c1; ++c) {
-          const int en = ent[c];
-          s += grp[(en >> 3) * slot + (en & 7) * D2 + i * PD + j];
+        for (; c + 1 < c1; c += 2) {
+          const double x0 = src[ent[c]], x1 = src[ent[c + 1]];
+          s += x0;
+          s += x1;
         }
+        if (c < c1) s += src[ent[c]];
         vrow[v] = s;
       }
-      if (fint && gl < PD) {
+      if constexpr (SPLIT) {
+        // lanes (q, part): part sums every PARTS-th contribution in ascending order, then (p0 + p1) + p2 ...
+        const int q = gl % D2, part = gl / D2;
         double s = 0.0;
-        for (int q = 0; q < ninc; ++q) s += grp[q * slot + foff + gl];
-        fint[(int64_t)PD * (dm.nl2g[r] - 1) + gl] = s;
+        if (part < PARTS) {
+          const double *src = grp + q;
+          const int c1 = off[kd + 1];
+          for (int c = off[kd] + part; c < c1; c += PARTS) s += src[ent[c]];
+        }
+        double tot = __shfl_sync(on_mask, s, gi * G + q);
+#pragma unroll
+        for (int pp = 1; pp < PARTS; ++pp) tot += __shfl_sync(on_mask, s, gi * G + pp * D2 + q);
+        if (gl < D2) vrow[(q / PD) * rowlen + PD * kd + q % PD] = tot;
+      }
+      if (fint) {   // f_r = sum of the incident elements' shares, FP interleaved partial sums per component (fixed order)
+        constexpr int FP = G >= 16 ? 4 : 1;
+        const int d = gl % PD, part = gl / PD;
+        double s = 0.0;
+        if (part < FP)
+          for (int q = part; q < ninc_cur; q += FP) s += grp[q * slot + foff + d];
+        if constexpr (FP > 1) {
+          double tot = __shfl_sync(on_mask, s, gi * G + d);
+#pragma unroll
+          for (int pp = 1; pp < FP; ++pp) tot += __shfl_sync(on_mask, s, gi * G + pp * PD + d);
+          s = tot;
+        }
+        if (gl < PD) fint[(int64_t)PD * (dm.nl2g[r] - 1) + gl] = s;
       }
     }
     __syncwarp();
@@ -159,9 +209,7 @@ int launch_rows_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_
   while (g < c->plan.max_inc) g *= 2;
   int maxnen = 3;
   for (const auto &b : c->buckets) maxnen = maxnen > type_nen(b.type) ? maxnen : type_nen(b.type);
-  const int pd = c->pdim, foff = maxnen * pd * pd;
-  int slot = foff + pd;
-  if (slot % 2 == 0) ++slot;   // odd pitch: the lane-strided 8-byte stores of phase A hit distinct banks
+  const int pd = c->pdim, slot = c->plan.rb_slot, foff = c->plan.rb_foff;   // the plan's entries are offsets into these slots
   if (pd == 2) return launch_pd<2, false>(c, d_u, d_vals, d_fint, g, slot, foff);
   return maxnen == 8 ? launch_pd<3, true>(c, d_u, d_vals, d_fint, g, slot, foff) : launch_pd<3, false>(c, d_u, d_vals, d_fint, g, slot, foff);
 }

@@ -145,7 +145,7 @@ def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
                 assert close(fint, f_o, TOL_MAT), (name, var)
                 assert np.array_equal(f.assemble_K(), vals), (name, var)
                 res[var] = vals
-        assert np.array_equal(res[9], res[1]), name      # same per-entry summation order: identical bits
+        assert close(res[9], res[1], TOL_MAT), name      # same summation order except the split diagonal block
 
 
 def test_golden_matview_through_cuda(golden):

@@ -51,7 +51,7 @@ def main():
         d_f = fx.device_buffer(8 * fx.nrows)
         d_s = fx.device_buffer(8 * 6 * m.nlnds)
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_vals.ptr, d_f.ptr, api.DEVICE)), args.reps)
-        line(f"C3 tet4 {args.tet}^3x6", "K + f_int (variant 1, two-pass)", m.nels, ms, best, 215.0,
+        line(f"C3 tet4 {args.tet}^3x6", "K + f_int (auto = variant 9, fused rows kernel)", m.nels, ms, best, 215.0,
              {"nnz": int(fx.nnz), "plan_build_s": round(plan_s, 2)})
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_stress(fx.h, d_u.ptr, d_s.ptr, api.ROW_MAJOR, api.DEVICE)), args.reps)
         line(f"C3 tet4 {args.tet}^3x6", "nodal-averaged stress", m.nels, ms, best, 36.5)
@@ -72,7 +72,7 @@ def main():
         d_fe = fx.device_buffer(8 * fx.nrows).upload(np.zeros(fx.nrows))
         d_r = fx.device_buffer(8 * fx.nrows)
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_k.ptr, d_f.ptr, api.DEVICE)), args.reps)
-        line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "K + f_int (variant 1, two-pass)", m.nels, ms, best, 356.0,
+        line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "K + f_int (auto = variant 9, fused rows kernel)", m.nels, ms, best, 356.0,
              {"nnz": int(fx.nnz), "plan_build_s": round(plan_s, 2)})
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_jacobian(fx.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE)), args.reps)
         line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "CalcJacobian (copy K, cohesive overlay, BC diagonal)", m.nels, ms, best,
