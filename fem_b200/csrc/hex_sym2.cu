@@ -1,30 +1,26 @@
-// hex_sym2.cu -- assembly variant 5: the symmetric pair-block kernel of hex_sym.cu on 16 warps.
+// hex_sym2.cu -- assembly variants 5..8: symmetric pair-block fused hex8 K (+ f_int) tile kernel.
 //
-// Same tile program, scratch layout and gather table as variant 4; what changes is the split of a cell's 36 pair
-// blocks: EIGHT threads per cell (39 / 36 accumulators, <= 128 registers) instead of four, so the CTA runs 16 warps
-// (4 per scheduler) and the latency-bound phases (geometry, G' -> K, gather) overlap much better, and f_r = K_rc u_c
-// is formed in the gather (lane products, shared-memory transposed reduction) instead of from per-cell partials.
-//
-// (header of variant 4 follows)
-// hex_sym.cu -- assembly variant 4: symmetric pair-block fused hex8 K (+ f_int) kernel.
-//
-// Variants 2/3 give every node row its own threads, which recompute K_cr = K_rc^T on both sides and
-// re-read every scaled gradient ~10 times from shared memory (2.4 FMA per loaded double: the LSU
-// wavefront pipe, not the FP64 pipe, bounds them).  Here the unit of FP64 work is the ELEMENT:
-//   * four threads per element accumulate, over the 8 integration points, the 36 unique node-pair
-//     blocks G'_ab = sum_ip g~_a g~_b^T (a <= b) in registers -- 10 pairs of the bottom/top face
-//     (78 accumulators: off-diagonal 3x3, diagonal symmetric 6) and 2 x 8 bottom x top pairs
-//     (72 accumulators) -- 5 FMA per loaded double, every operand an LDS.128;
-//   * face pairs are summed over the two elements below/above the face in registers (the two face
-//     warps alternate "start"/"finish" from layer to layer), turned into K_ab = rho G' + G'^T + tr I
-//     and parked in a per-element shared-memory scratch (234 doubles);
-//   * a gather pass, lane <-> consecutive CSR value, sums the <= 4 element contributions of every
-//     value of a node row in fixed (ascending cell) order through a 243-entry offset table, takes the
-//     transposed entry for c < r, forms f_r += K_rc u_c on the way and stores coalesced 216-byte runs.
-// One CTA (256 threads, 1 per SM) owns 7 x 7 node positions, i.e. the 8 x 8 cells touching them, and
-// marches through the node layers of a z-chunk.  No atomics, fixed summation order, each CSR value
-// stored exactly once.  Same arithmetic as FormElKE (src/m_local.F90:21-67) in the (lambda, mu)
-// block form of elem_math.cuh.
+// Variants 2/3 (hex_fused.cu, hex_ws.cu) give every node row its own threads, which recompute K_cr = K_rc^T on both
+// sides and re-read every scaled gradient ~10 times from shared memory (2.4 FMA per loaded double: the LSU wavefront
+// pipe, not the FP64 pipe, bounds them).  Here the unit of FP64 work is the ELEMENT (cell):
+//   * FMA phase: TPC threads per cell accumulate over the 8 integration points the 36 unique node-pair blocks
+//     G'_ab = sum_ip g~_a g~_b^T (a <= b) in registers.  TPC = 8 (variants 5, 6): two threads per face (3 off-diagonal
+//     3x3 blocks + 2 symmetric diagonal blocks = 39 accumulators), four threads with 2 x 2 of the bottom x top blocks
+//     (36); 128 registers, 16 warps.  TPC = 4 (variants 7, 8): one thread per face (78), two threads with 2 x 4
+//     bottom x top blocks (72); 255 registers.  Every operand is an LDS.128 from 32 distinct cells (conflict-free);
+//   * the top-face threads park their raw sums in shared memory (`carry`), the bottom-face threads of the next
+//     layer start from them, so face pairs reach the scratch already summed over the two cells sharing the face;
+//   * G' -> K = rho G' + G'^T + tr(G') I in registers, parked in a per-cell scratch: two 4 x 4 node matrices of
+//     3x3 blocks (face pairs incl. transposes; bottom x top pairs), rows [node][i] of 12 doubles [node][j];
+//   * gather phase, lane <-> consecutive CSR value: per node the nine 27-value runs (3 scalar rows x dz in
+//     {-1, 0, +1}) are the sums of the <= 4 cell contributions in ascending cell order, addressed through a
+//     3-entry-per-lane offset table (row i is a static LDS immediate, unused contributions are predicated off,
+//     dz = -1 reads the transposed block), stored as coalesced 216-byte runs; f_r = sum_c K_rc u_c from the same
+//     registers (lane products, fixed-order butterfly; the dz = -1 part is carried one layer).
+// One CTA owns NX x NY node positions = the (NX+1) x (NY+1) cells touching them and marches through the node layers
+// of a z-chunk (cp.async ring one layer ahead); the gradient buffer and the scratch alias.  No atomics, fixed
+// summation order, each CSR value stored exactly once.  Same arithmetic as FormElKE (src/m_local.F90:21-67) in the
+// (lambda, mu) block form of elem_math.cuh.  hex_sym3/4/5.cu include this file with other tile macros.
 #include <cstdio>
 
 #include "elem_math.cuh"
@@ -191,7 +187,7 @@ __device__ __forceinline__ void geometry(Smem &S, int m, int tid) {
   const int ex = es % EX, ey = es / EX;
 #pragma unroll
   for (int q = 0; q < 8 / TPC; ++q) {
-    const int ip = tid / ELP + TPC * q;
+    const int ip = (tid >> (ELP == 64 ? 6 : 5)) + TPC * q;
     // integration point ip sits beside node ip (SamPtsHex, src/m_elems.F90:500-507)
     const bool ppx = (ip == 1) | (ip == 2) | (ip == 5) | (ip == 6), ppy = (ip == 2) | (ip == 3) | (ip == 6) | (ip == 7);
     const double e = ppx ? FEMX_G : -FEMX_G, n = ppy ? FEMX_G : -FEMX_G, s = ip >= 4 ? FEMX_G : -FEMX_G;
@@ -431,8 +427,8 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 
   // FMA-phase role (two warps each): 0/1 = bottom-face threads X/Y (finish the face started one layer below),
   // 2/3 = top-face threads X/Y (start the next face), 4..7 = 2 x 2 bottom x top blocks
-  const int type = wu / WPT;
-  const int es = (w % WPT) * 32 + lane;
+  const int type = wu >> (WPT - 1);
+  const int es = (w & (WPT - 1)) * 32 + lane;
 #if FEMX_SYM_TPC == 8
   const bool top = type >= 2, isy = (type & 1) != 0;
 #endif

@@ -25,7 +25,6 @@ int launch_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b,
                       int64_t nout, double *out);
 int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_ws(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_sym(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym3(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym4(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);

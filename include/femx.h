@@ -63,10 +63,11 @@ enum {
 
 /* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, else 1),
  * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
- * 3 = its warp-specialised form, 4 / 5 = symmetric pair-block kernel on 8 / 16 warps */
+ * 3 = its warp-specialised form, 5 = symmetric pair-block kernel on 16 warps (6, 7, 8: its measured tile / thread
+ * variants, 4 = alias of 8), 9 = fused rows kernel for any element mix */
 typedef struct {
   int quirks;            /* FEMX_Q_* bits                                   */
-  int assembly_variant;  /* 0 auto, 1 two-pass, 2..5 fused hex8 kernels     */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8 hex8 tile kernels, 9 fused rows */
   int reserved[6];
 } femx_opts;
 
