@@ -121,6 +121,9 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--exchange", choices=("peer", "peer-fused", "nccl"), default="peer",
+                    help="N > 1: interface rows pushed into the owner's arena over NVLink by femx's own kernel behind the assembly "
+                         "kernel (peer), stored there by the assembly kernel itself (peer-fused), or sent with NCCL after it")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--n", type=int, default=100, help="hex8 cube edge per GPU")
@@ -149,7 +152,8 @@ def main():
 
     from fem_b200 import api
     m, u = build_workload(args.n, world, rank)
-    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz, dbg=args.dbg)
+    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz, dbg=args.dbg,
+                  peer_in_kernel=args.exchange == "peer-fused")
     t0 = time.time()
     fx.set_mesh(m).build_plan()
     plan_s = time.time() - t0
@@ -162,7 +166,7 @@ def main():
         # interface rows go to their PETSc owners over NCCL every step (fem_b200/parallel.py)
         import ctypes as C
         from fem_b200 import parallel as par
-        da = par.DistributedAssembly(fx, dist, torch.device("cuda", local_rank), with_merge=False)
+        da = par.DistributedAssembly(fx, dist, torch.device("cuda", local_rank), with_merge=False, peer=args.exchange != "nccl")
         vals_ptr = C.c_void_p(da.vals_local.data_ptr())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     else:
@@ -172,7 +176,7 @@ def main():
     def step_device():
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, vals_ptr, d_f.ptr, api.DEVICE))
         ms = fx.last_kernel_ms
-        if da is not None:
+        if da is not None and not da.peer:   # peer mode: the kernel stored the interface rows into the owners' arenas
             ev0.record()
             da.exchange()
             ev1.record()
@@ -252,8 +256,11 @@ def main():
                 "config": {"workload": f"hex8 cube {args.n}^3 per GPU, jittered, K + f_int (BASELINE configs[1])",
                            "elements_per_gpu": m.nels, "dof_per_gpu": int(m.pdim * m.nlnds), "nnz_per_gpu": int(nnz),
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
-                           "parallelism": (f"z-slab element partition x{world}, PETSc row split, NCCL all_to_all of interface rows "
-                                           f"({int(da.ep.recv_counts.sum()) * 8} B received on rank 0 per step)") if world > 1 else "1 GPU",
+                           "parallelism": (f"z-slab element partition x{world}, PETSc row split, interface rows "
+                                           + ((("stored by the assembly kernel" if args.exchange == "peer-fused" else "pushed by femx's peer kernel")
+                                               + " into the owner's arena over NVLink + device-side step barrier")
+                                              if da.peer else "sent with NCCL all_to_all after the kernel")
+                                           + f" ({int(da.ep.recv_counts.sum()) * 8} B received on rank 0 per step)") if world > 1 else "1 GPU",
                            "variant": args.variant, "tile": args.tile, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
                 "gpu_launches": int(launches),
                 "clocks": sampler.summary(),
@@ -272,6 +279,8 @@ def main():
                                     "sample": f"hex8 cube {args.cpu_n}^3 ({ne} elements) in {sec:.2f} s, oracle/ CPU "
                                               "restatement of src/main.F90:157-166; reference (Fortran+PETSc) not buildable here"}
         print(json.dumps(line))
+    if da is not None:
+        da.close()
     fx.close()
     if world > 1:
         dist.destroy_process_group()

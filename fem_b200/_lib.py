@@ -54,6 +54,10 @@ SIGNATURES = {
     "femx_stress": (C.c_int, [V, V, V, C.c_int, C.c_int]),
     "femx_set_ownership": (C.c_int, [V, C.c_int, C.c_int, C.c_int64, C.c_int64]),
     "femx_gather_sum": (C.c_int, [V, V, C.c_int64, V, V, V, C.c_int64, V]),
+    "femx_peer_arena_create": (C.c_int, [V, C.c_int64, C.c_int64, V]),
+    "femx_peer_connect": (C.c_int, [V, C.c_int, C.c_int, V, V, V, V, V, V, V]),
+    "femx_peer_recv": (C.c_int, [V, V, V]),
+    "femx_peer_disconnect": (C.c_int, [V]),
     "femx_nccl_unique_id": (C.c_int, [C.c_char_p]),
     "femx_comm_init": (C.c_int, [V, C.c_char_p]),
     "femx_launch_count": (C.c_int64, [V]),

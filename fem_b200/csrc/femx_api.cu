@@ -42,6 +42,8 @@ int femx_destroy(femx_ctx *c) {
   if (!c) return FEMX_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  femx_peer_disconnect(c);
+  if (c->peer.arena) cudaFree(c->peer.arena);
   for (void *p : c->allocs) cudaFree(p);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);

@@ -53,6 +53,11 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   const bool fused = c->hex.ok && av0 != 1 && av0 != 9;
   const bool rows = !fused && av0 != 1 && rows_fused_ok(c);
   if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
+  const bool peer = c->peer.connected;
+  // peer exchange: reserved[3] = 1 lets the assembly kernel store interface rows at their owner itself (variants 0, 5, 9);
+  // default is the push kernel behind the unchanged assembly kernel
+  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5) : rows);
+  c->peer.in_kernel = peer_fused;
   if (!fused && !rows) {
     if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
     if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
@@ -71,10 +76,17 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
     c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
     c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);
   }
+  if (peer) c->launches += launch_peer_finish(c, peer_fused, d_vals, d_fint);   // step barrier: the peers' stores into this rank's arena are complete
   if ((rc = end_timing(c))) return rc;
   if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
   if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;
-  return finish_call(c, true);
+  if ((rc = finish_call(c, true))) return rc;
+  if (peer) {
+    int e = 0;
+    CK(cudaMemcpy(&e, c->peer.d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (e) { c->err = "peer exchange: rank " + std::to_string(e - 1) + " did not reach the step barrier"; return FEMX_ERR_CUDA; }
+  }
+  return FEMX_OK;
 }
 
 }  // namespace

@@ -86,6 +86,39 @@ struct DevHex {
   HexRowMeta *pos_meta = nullptr;   // [NK][NJ][NI]
   double *cellmu = nullptr;         // [NK][NJ][NI] sqrt(mu) of the element in that cell, 0 = no element
 };
+// peer-memory exchange (peer.cu): kernel parameter that tells the assembly kernels where the values of rows another
+// rank owns go.  Local value offsets [vb[q], vb[q+1]) (rows ascend with the owner) belong to rank q; vdst[q] is the
+// address, in q's receive arena mapped over NVLink, at which offset vb[q] lands (nullptr: keep in the local array).
+// fb / fdst: the same for the internal-force entries, numbered pdim * local node + i.
+constexpr int kMaxPeers = 8;
+struct PeerTab {
+  int n = 0, rank = 0;
+  long long vb[kMaxPeers + 1] = {};
+  long long fb[kMaxPeers + 1] = {};
+  double *vdst[kMaxPeers] = {};
+  double *fdst[kMaxPeers] = {};
+};
+// fast path: the value range [lo, hi) / force entry o stays in the local arrays (97 % of the rows)
+__device__ __forceinline__ bool peer_local(const PeerTab &pt, long long lo, long long hi) {
+  return lo >= pt.vb[pt.rank] && hi <= pt.vb[pt.rank + 1];
+}
+__device__ __forceinline__ bool peer_local_f(const PeerTab &pt, long long o) { return o >= pt.fb[pt.rank] && o < pt.fb[pt.rank + 1]; }
+// address of local value offset `off` (first value of one matrix row); a row never straddles owners
+__device__ __forceinline__ double *peer_row(const PeerTab &pt, double *vals, long long off) {
+  double *p = vals + off;
+#pragma unroll 1
+  for (int q = 0; q < pt.n; ++q)
+    if (pt.vdst[q] && off >= pt.vb[q] && off < pt.vb[q + 1]) p = pt.vdst[q] + (off - pt.vb[q]);
+  return p;
+}
+__device__ __forceinline__ double *peer_f(const PeerTab &pt, double *local, long long o) {
+  double *p = local;
+#pragma unroll 1
+  for (int q = 0; q < pt.n; ++q)
+    if (pt.fdst[q] && o >= pt.fb[q] && o < pt.fb[q + 1]) p = pt.fdst[q] + (o - pt.fb[q]);
+  return p;
+}
+
 int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,
                    HexPlan *H, std::string *why);
 
@@ -159,4 +192,18 @@ struct femx_ctx {
   int32_t *d_cnode_id = nullptr, *d_cnode_ptr = nullptr, *d_cnode_src = nullptr;
   double *d_coh_ke = nullptr, *d_coh_fe = nullptr;
   std::vector<void *> allocs;  // everything cudaMalloc'ed by the ctx
+  // peer-memory exchange (peer.cu)
+  struct Peer {
+    int nranks = 0, rank = 0;
+    char *arena = nullptr;                 // [flags 1 KB | buffer 0: vals, f | buffer 1: vals, f]
+    int64_t nv = 0, nf = 0;                // receive capacity (doubles) per buffer
+    char *remote[femx::kMaxPeers] = {};    // peers' arenas mapped with cudaIpcOpenMemHandle
+    int64_t rnv[femx::kMaxPeers] = {}, rnf[femx::kMaxPeers] = {};   // peers' capacities (their buffer layout)
+    int64_t vb[femx::kMaxPeers + 1] = {}, fb[femx::kMaxPeers + 1] = {};
+    int64_t vdst[femx::kMaxPeers] = {}, fdst[femx::kMaxPeers] = {};  // offsets (doubles) inside the peer's vals / f receive area
+    unsigned long long step = 0;           // assemblies done; buffer parity = step & 1
+    int *d_err = nullptr;
+    bool connected = false;
+    bool in_kernel = false;                // this assembly's kernel stores the interface rows itself (PEER instantiation)
+  } peer;
 };

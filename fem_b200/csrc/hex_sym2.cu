@@ -412,9 +412,10 @@ __device__ __forceinline__ bool v_dummy(const double *p) { return p == nullptr; 
 
 }  // namespace
 
-template <bool WITH_F>
+template <bool WITH_F, bool PEER>   // PEER: rows another rank owns are stored into that rank's receive arena (peer.cu)
 __global__ void __launch_bounds__(NT, CTAS)
-FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg) {
+FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg,
+                const PeerTab pt) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -630,15 +631,25 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
         const bool on0 = st && act_hi && lane < 27 && k0 != 255, on1 = st && act_lo && lane < 27 && k1 != 255, on2 = st && act_lo && lane < 27 && k2 != 255;
         double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
         const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
+        bool remote = false;     // PEER: one of the two nodes' rows lives on another rank (3 % of the nodes)
+        if constexpr (PEER)
+          remote = (act_hi && !peer_local(pt, rhi->base, rhi->base + 3 * rs_hi)) || (act_lo && !peer_local(pt, rlo->base, rlo->base + 3 * rs_lo));
         double v[9];
         v[0] = gather_val<0>(eb, t0, c_on0, c_on1, c_on2); v[3] = gather_val<8>(eb, t0, c_on0, c_on1, c_on2); v[6] = gather_val<16>(eb, t0, c_on0, c_on1, c_on2);
         v[2] = gather_val<0>(eb, t2, c_on0, c_on1, c_on2); v[5] = gather_val<8 * SI>(eb, t2, c_on0, c_on1, c_on2); v[8] = gather_val<16 * SI>(eb, t2, c_on0, c_on1, c_on2);
         v[1] = gather_val<0>(eb, t1, c_on0, c_on1, c_on2); v[4] = gather_val<8 * SI>(eb, t1, c_on0, c_on1, c_on2); v[7] = gather_val<16 * SI>(eb, t1, c_on0, c_on1, c_on2);
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-          if (on0) p0[i * rs_hi] = v[i * 3 + 0];
-          if (on1) p1[i * rs_lo] = v[i * 3 + 1];
-          if (on2) p2[i * rs_lo] = v[i * 3 + 2];
+          if (PEER && remote) {   // row starts looked up at their owner
+            double *a = peer_row(pt, vals, rhi->base + i * rs_hi), *b = peer_row(pt, vals, rlo->base + i * rs_lo);
+            if (on0) a[3 * k0 + jj] = v[i * 3 + 0];
+            if (on1) b[3 * k1 + jj] = v[i * 3 + 1];
+            if (on2) b[3 * k2 + jj] = v[i * 3 + 2];
+          } else {
+            if (on0) p0[i * rs_hi] = v[i * 3 + 0];
+            if (on1) p1[i * rs_lo] = v[i * 3 + 1];
+            if (on2) p2[i * rs_lo] = v[i * 3 + 2];
+          }
         }
         if (WITH_F && !(dbg & 16)) {
           // f_r = sum_c K_rc u_c: lane products, butterfly-summed (fixed order); lanes 0-15 end up with the three
@@ -659,7 +670,14 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
           if (li < 3) {
             const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
             // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
-            if (!upper) { if (act_lo) fint[(long long)rlo->grow + li] = S.fcarry[n][li] + mine; }
+            if (!upper && act_lo) {
+              double *fp = fint + ((long long)rlo->grow + li);
+              if constexpr (PEER) {
+                const long long o = 3ll * S.nid[m & 7][(py + 1) * UX + px + 1] + li;
+                if (!peer_local_f(pt, o)) fp = peer_f(pt, fp, o);
+              }
+              *fp = S.fcarry[n][li] + mine;
+            }
           }
           __syncwarp();
           if (li < 3 && upper) {
@@ -695,20 +713,25 @@ int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
   static_assert(sizeof(Smem) <= (CTAS == 1 ? 232448 : 115712), "shared memory exceeds what the resident CTAs of an SM may opt into");
   if (c->opts.reserved[2] & 32) {
     int nb = -1;
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, FEMX_SYM_KERNEL<true>, NT, smem);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, FEMX_SYM_KERNEL<true, false>, NT, smem);
     fprintf(stderr, "femx: sym kernel smem %zu B, %d resident CTAs per SM, grid %d x %d x %d, LZ %d\n", smem, nb, grid.x, grid.y, grid.z, LZ);
   }
-  if (d_u) {
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    FEMX_SYM_KERNEL<true><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
-  } else {
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    FEMX_SYM_KERNEL<false><<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+  const PeerTab pt = c->peer.in_kernel ? peer_tab(c) : PeerTab{};
+  const int dbg = c->opts.reserved[2];
+  auto go = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, dbg, pt);
+  };
+#if FEMX_SYM_TPC == 8 && FEMX_SYM_CTAS == 1
+  if (pt.n > 0) {
+    if (d_u) go(FEMX_SYM_KERNEL<true, true>); else go(FEMX_SYM_KERNEL<false, true>);
+    return 1;
   }
+#endif
+  if (d_u) go(FEMX_SYM_KERNEL<true, false>); else go(FEMX_SYM_KERNEL<false, false>);
   return 1;
 }
 

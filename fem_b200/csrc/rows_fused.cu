@@ -65,9 +65,12 @@ __device__ __forceinline__ void row_of(const DevMesh &dm, int e, int a, const do
   }
 }
 
-template <int PD, int G, bool HEX>   // HEX: the mesh holds hex8 elements (keeps their 72 accumulators out of tet-only builds)
+// HEX: the mesh holds hex8 elements (keeps their 72 accumulators out of tet-only builds); PEER: rows another rank owns
+// are stored into that rank's receive arena (peer.cu)
+template <int PD, int G, bool HEX, bool PEER>
 __global__ void __launch_bounds__(kWarps * 32)
-fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int slot, int foff) {
+fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int slot, int foff,
+                  const PeerTab pt) {
   extern __shared__ double sm_rows[];
   constexpr int D2 = PD * PD, NPW = 32 / G;
   constexpr int PARTS = G / D2;                  // lanes per diagonal-block value when the group is wide enough to split it
@@ -124,6 +127,15 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
       const uint16_t *off = dm.rb_off + b0 + r;
       const uint16_t *ent = dm.rb_ent + dm.rbe_ptr[r];
       double *vrow = vals + D2 * b0;
+      double *prow[PD];   // PEER: first value of each of the node's PD rows, at its owner
+      if constexpr (PEER) {
+#pragma unroll
+        for (int i = 0; i < PD; ++i) prow[i] = vrow + (int64_t)i * rowlen;
+        if (!peer_local(pt, D2 * b0, D2 * b0 + nv)) {
+#pragma unroll
+          for (int i = 0; i < PD; ++i) prow[i] = peer_row(pt, vals, D2 * b0 + (int64_t)i * rowlen);
+        }
+      }
       const int kd = SPLIT ? dm.bdiag[r] : -1;   // the diagonal block has one contribution per incident element: split it
       for (int v = gl; v < nv; v += G) {
         const int i = (v >= rowlen) + (PD == 3 && v >= 2 * rowlen), rem = v - i * rowlen, k = rem / PD, j = rem - k * PD;
@@ -138,7 +150,8 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
           s += x1;
         }
         if (c < c1) s += src[ent[c]];
-        vrow[v] = s;
+        if constexpr (PEER) (i == 0 ? prow[0] : (i == 1 ? prow[1] : prow[PD - 1]))[rem] = s;
+        else vrow[v] = s;
       }
       if constexpr (SPLIT) {
         // lanes (q, part): part sums every PARTS-th contribution in ascending order, then (p0 + p1) + p2 ...
@@ -152,7 +165,10 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
         double tot = __shfl_sync(on_mask, s, gi * G + q);
 #pragma unroll
         for (int pp = 1; pp < PARTS; ++pp) tot += __shfl_sync(on_mask, s, gi * G + pp * D2 + q);
-        if (gl < D2) vrow[(q / PD) * rowlen + PD * kd + q % PD] = tot;
+        if (gl < D2) {
+          if constexpr (PEER) (q / PD == 0 ? prow[0] : (q / PD == 1 ? prow[1] : prow[PD - 1]))[PD * kd + q % PD] = tot;
+          else vrow[(q / PD) * rowlen + PD * kd + q % PD] = tot;
+        }
       }
       if (fint) {   // f_r = sum of the incident elements' shares, FP interleaved partial sums per component (fixed order)
         constexpr int FP = G >= 16 ? 4 : 1;
@@ -166,28 +182,41 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
           for (int pp = 1; pp < FP; ++pp) tot += __shfl_sync(on_mask, s, gi * G + pp * PD + d);
           s = tot;
         }
-        if (gl < PD) fint[(int64_t)PD * (dm.nl2g[r] - 1) + gl] = s;
+        if (gl < PD) {
+          double *fp = fint + ((int64_t)PD * (dm.nl2g[r] - 1) + gl);
+          if constexpr (PEER) {
+            if (!peer_local_f(pt, (int64_t)PD * r + gl)) fp = peer_f(pt, fp, (int64_t)PD * r + gl);
+          }
+          *fp = s;
+        }
       }
     }
     __syncwarp();
   }
 }
 
-template <int PD, int G, bool HEX>
-int launch_g(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int slot, int foff) {
+template <int PD, int G, bool HEX, bool PEER>
+int launch_gp(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int slot, int foff, const PeerTab &pt) {
   const size_t smem = (size_t)kWarps * 32 * slot * sizeof(double);
-  cudaFuncSetAttribute(fused_rows_kernel<PD, G, HEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaFuncSetAttribute(fused_rows_kernel<PD, G, HEX, PEER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   int nsm = 148, per_sm = 1;
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_rows_kernel<PD, G, HEX>, kWarps * 32, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_rows_kernel<PD, G, HEX, PEER>, kWarps * 32, smem);
   if (per_sm < 1) per_sm = 1;
   const int64_t ngroups = ((int64_t)c->nlnds + 32 / G - 1) / (32 / G);
   int64_t grid = (ngroups + kWarps - 1) / kWarps;
   const int64_t cap = (int64_t)nsm * per_sm * 4;   // a few CTAs per resident slot, grid-stride over the rest
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
-  fused_rows_kernel<PD, G, HEX><<<(unsigned)grid, kWarps * 32, smem, c->stream>>>(c->dm, d_u, d_vals, d_fint, slot, foff);
+  fused_rows_kernel<PD, G, HEX, PEER><<<(unsigned)grid, kWarps * 32, smem, c->stream>>>(c->dm, d_u, d_vals, d_fint, slot, foff, pt);
   return 1;
+}
+
+template <int PD, int G, bool HEX>
+int launch_g(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int slot, int foff) {
+  const PeerTab pt = c->peer.in_kernel ? peer_tab(c) : PeerTab{};
+  return pt.n > 0 ? launch_gp<PD, G, HEX, true>(c, d_u, d_vals, d_fint, slot, foff, pt)
+                  : launch_gp<PD, G, HEX, false>(c, d_u, d_vals, d_fint, slot, foff, pt);
 }
 
 template <int PD, bool HEX>

@@ -120,6 +120,48 @@ def exchange_lists(ep: ExchangePlan, dist, device="cpu"):
     return out[0], out[1]
 
 
+def peer_layout(ep: ExchangePlan, recv_rows: list, nl2g: np.ndarray, pdim: int, nrows: int, nnz: int):
+    """Index side of the peer-memory exchange (csrc/peer.cu): where each source rank's slice lands in this
+    rank's receive arena, and which local ranges go to which owner.  Returns a dict of int64 arrays:
+      recv_voff / recv_foff [P+1]  start of source s's values / force entries in the arena (source-rank order),
+      f_rows[s]                    global rows of the force entries source s sends (its local rows in my range,
+                                   ascending = the unique rows of its matrix list, every row has a diagonal),
+      val_bounds / f_bounds [P+1]  local value offsets / local dofs (pdim*node + i) by owner."""
+    P = ep.nranks
+    f_rows = [np.unique(np.asarray(r, np.int64)) for r in recv_rows]
+    recv_voff = np.concatenate([[0], np.cumsum([len(r) for r in recv_rows])]).astype(np.int64)
+    recv_foff = np.concatenate([[0], np.cumsum([len(r) for r in f_rows])]).astype(np.int64)
+    val_bounds = np.concatenate([ep.send_lo, [nnz]]).astype(np.int64)
+    assert np.array_equal(ep.send_hi, val_bounds[1:]), "local rows must ascend with their owner"
+    bounds = np.array([petsc_ownership(nrows, P, r)[0] for r in range(P)] + [nrows], dtype=np.int64)
+    gdof = (pdim * (np.asarray(nl2g, np.int64) - 1)[:, None] + np.arange(pdim)[None, :]).reshape(-1)
+    assert np.all(np.diff(gdof) > 0), "local nodes must ascend in global id"
+    f_bounds = np.searchsorted(gdof, bounds).astype(np.int64)
+    return dict(recv_voff=recv_voff, recv_foff=recv_foff, f_rows=f_rows, val_bounds=val_bounds, f_bounds=f_bounds)
+
+
+def exchange_offsets(lay: dict, dist, nranks: int, device="cpu"):
+    """Tell every source rank where its slices start in my arena; learn where mine start in theirs.
+    Returns (val_dst[P], f_dst[P], caps[P, 2]) with caps = every rank's arena capacities (values, force entries)."""
+    import torch
+    mine = torch.tensor(np.stack([lay["recv_voff"][:-1], lay["recv_foff"][:-1]], 1).reshape(-1), dtype=torch.int64, device=device)
+    theirs = torch.empty_like(mine)
+    dist.all_to_all_single(theirs, mine)
+    theirs = theirs.cpu().numpy().reshape(nranks, 2)
+    cap = torch.tensor([int(lay["recv_voff"][-1]), int(lay["recv_foff"][-1])], dtype=torch.int64, device=device)
+    caps = [torch.empty_like(cap) for _ in range(nranks)]
+    dist.all_gather(caps, cap)
+    caps = np.stack([c.cpu().numpy() for c in caps])
+    return theirs[:, 0].copy(), theirs[:, 1].copy(), caps
+
+
+class _DevArray:
+    """torch view of library-owned device memory (CUDA array interface)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f8", "data": (int(ptr), False), "version": 3, "strides": None}
+
+
 class DistributedAssembly:
     """Per-rank driver: femx context on the local mesh + the exchange plan.
 
@@ -127,7 +169,7 @@ class DistributedAssembly:
     femx writes into it through its raw device pointer.
     """
 
-    def __init__(self, fx, dist, device, with_merge=True):
+    def __init__(self, fx, dist, device, with_merge=True, peer=False):
         import torch
         self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
         rowptr, colidx = fx.pattern()
@@ -141,11 +183,78 @@ class DistributedAssembly:
         self.recv_splits = [int(x) for x in self.ep.recv_counts]
         self.n_own = self.ep.own_hi - self.ep.own_lo
         self._merge_dev = None
+        self.peer = False
+        if peer:                 # all ranks or none: a rank whose IPC mapping fails takes everybody back to NCCL
+            try:
+                self._connect_peers(rr)
+                good = 1
+            except Exception as e:   # noqa: BLE001
+                import sys
+                print(f"femx: peer-memory exchange unavailable on rank {rank} ({e}); using NCCL", file=sys.stderr, flush=True)
+                good = 0
+            t = torch.tensor([good], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            if not int(t.item()) and good:
+                self.fx._ck(self.fx.L.femx_peer_disconnect(self.fx.h))
+            self.peer = bool(int(t.item()))
+
+    def _connect_peers(self, recv_rows):
+        """Peer-memory mode: the assembly kernel stores interface rows into the owner's arena (csrc/peer.cu);
+        exchange() then only looks up where the last assembly's receive buffer is."""
+        import ctypes as C
+        torch, fx, dist, ep = self.torch, self.fx, self.dist, self.ep
+        P = ep.nranks
+        m = fx.mesh
+        self.lay = lay = peer_layout(ep, recv_rows, m.nl2g, m.pdim, fx.nrows, fx.nnz)
+        val_dst, f_dst, caps = exchange_offsets(lay, dist, P, self.device)
+        handle = (C.c_char * 64)()
+        fx._ck(fx.L.femx_peer_arena_create(fx.h, int(caps[ep.rank, 0]), int(caps[ep.rank, 1]), C.addressof(handle)))
+        mine = torch.frombuffer(bytearray(handle.raw), dtype=torch.uint8).to(self.device)
+        alls = [torch.empty_like(mine) for _ in range(P)]
+        dist.all_gather(alls, mine)
+        handles = b"".join(bytes(t.cpu().numpy().tobytes()) for t in alls)
+        i64 = lambda a: np.ascontiguousarray(a, np.int64)
+        args = [i64(caps[:, 0]), i64(caps[:, 1]), i64(lay["val_bounds"]), i64(val_dst), i64(lay["f_bounds"]), i64(f_dst)]
+        fx._ck(fx.L.femx_peer_connect(fx.h, P, ep.rank, handles, *[a.ctypes.data for a in args]))
+        self._peer_keep = args
+        self.n_recv_f = int(caps[ep.rank, 1])
+
+    def peer_received(self):
+        """(values, force entries) the last assembly received, as torch views of the arena."""
+        import ctypes as C
+        pv, pf = C.c_void_p(), C.c_void_p()
+        self.fx._ck(self.fx.L.femx_peer_recv(self.fx.h, C.byref(pv), C.byref(pf)))
+        n = int(self.ep.recv_counts.sum())
+        as_t = lambda p, k: (self.torch.as_tensor(_DevArray(p.value, k), device=self.device) if k > 0
+                             else self.torch.empty(0, dtype=self.torch.float64, device=self.device))
+        return as_t(pv, n), as_t(pf, self.n_recv_f)
+
+    def owned_fint(self, d_f):
+        """Internal force of the owned rows after a peer-mode assembly: this rank's partial plus the entries
+        each source rank stored into the arena, added in source-rank order (deterministic)."""
+        torch, ep = self.torch, self.ep
+        out = d_f[ep.row_start:ep.row_end].clone()
+        fr = self.peer_received()[1]
+        for s, rows in enumerate(self.lay["f_rows"]):
+            if len(rows):
+                o = int(self.lay["recv_foff"][s])
+                idx = torch.from_numpy(rows - ep.row_start).to(self.device)
+                out.index_add_(0, idx, fr[o:o + len(rows)])
+        return out
+
+    def close(self):
+        if self.peer:
+            self.fx._ck(self.fx.L.femx_peer_disconnect(self.fx.h))
+            self.dist.barrier()  # nobody frees an arena a peer still maps
+            self.peer = False
 
     def exchange(self):
         """Ship the interface-row values (contiguous slices of vals_local, no pack kernel);
         returns (own slice view, received values ordered by source rank)."""
         ep = self.ep
+        if self.peer:            # the kernel already delivered the slices; the step barrier ran inside the assemble call
+            self.recv = self.peer_received()[0]
+            return self.vals_local[ep.own_lo:ep.own_hi], self.recv
         ins = [self.vals_local[int(ep.send_lo[q]):int(ep.send_hi[q])] if q != ep.rank else self.vals_local[:0]
                for q in range(ep.nranks)]
         offs = np.concatenate([[0], np.cumsum(self.recv_splits)])

@@ -156,6 +156,28 @@ int femx_set_ownership(femx_ctx *ctx, int nranks, int rank, int64_t row_start, i
  * a = this rank's own values of its owned rows, b = the values received from the other ranks. */
 int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b, const int64_t *ptr,
                     const int64_t *idx, int64_t nout, double *out);
+/* Peer-memory interface exchange (one node, 2..8 ranks; replaces the stash traffic of MatAssemblyBegin/End,
+ * src/main.F90:167-168).  The rank-local CSR lists rows in ascending global order, so the values bound for rank q
+ * are the contiguous local value range [val_bounds[q], val_bounds[q+1]) and the internal-force entries (numbered
+ * pdim*local_node + i) the range [f_bounds[q], f_bounds[q+1]).  After femx_peer_connect the assembly kernels of
+ * femx_assemble_K / femx_assemble_K_fint (variants 0, 5, 9) store those ranges straight into
+ * rank q's receive arena over NVLink, at val_dst[q] / f_dst[q] doubles from the start of q's value / force receive
+ * area, and the call ends with a device-side step barrier among the ranks: at return the rank's own slice of `vals`
+ * (and the owned rows of `fint`) plus everything its peers sent are complete.  The non-owned ranges of the local
+ * `vals` / `fint` arrays are NOT written in this mode.  Assemblies are collective: every rank calls them the same
+ * number of times.  The arena is double-buffered on the call parity.
+ *   femx_peer_arena_create  allocates the arena for n_recv_vals + n_recv_f doubles (per buffer) and returns its
+ *                           cudaIpcMemHandle (64 bytes) for the caller to all-gather among the ranks;
+ *   femx_peer_connect       handles = nranks x 64 bytes, recv_vals / recv_f = every rank's arena capacities;
+ *   femx_peer_recv          device pointers to what the LAST assembly received (source-rank order, as laid out by
+ *                           the caller's val_dst / f_dst);
+ *   femx_peer_disconnect    unmaps the peers' arenas (call on every rank before any rank destroys its ctx). */
+int femx_peer_arena_create(femx_ctx *ctx, int64_t n_recv_vals, int64_t n_recv_f, char handle[64]);
+int femx_peer_connect(femx_ctx *ctx, int nranks, int rank, const char *handles, const int64_t *recv_vals,
+                      const int64_t *recv_f, const int64_t *val_bounds, const int64_t *val_dst,
+                      const int64_t *f_bounds, const int64_t *f_dst);
+int femx_peer_recv(femx_ctx *ctx, const double **vals_recv, const double **f_recv);
+int femx_peer_disconnect(femx_ctx *ctx);
 int femx_nccl_unique_id(char id[128]);
 int femx_comm_init(femx_ctx *ctx, const char id[128]);
 

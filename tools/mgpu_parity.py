@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """Multi-GPU parity check (run under torchrun, one rank per GPU):
     torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/mgpu_parity.py
-Every rank assembles its slab with the CUDA path, interface rows travel over NCCL, and the merged
-owned rows are compared with the CPU oracle's 1-rank global matrix (pattern bit-exact, values 1e-12)."""
+Every rank assembles its slab with the CUDA path; interface rows travel either inside the assembly kernel
+(peer-memory stores over NVLink, csrc/peer.cu) or over NCCL after it, and the merged owned rows are compared
+with the CPU oracle's 1-rank global matrix (pattern bit-exact, values 1e-12), twice per mode so that both
+receive buffers of the peer arena are exercised."""
 import os
 import sys
 
@@ -21,20 +23,32 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     dev = torch.device("cuda", lr)
     ok = True
-    for name, g in (("hex", mg.jitter(mg.hex_cube(12, clamp=False))), ("tet", mg.jitter(mg.tet_cube(6))),
-                    ("quad", mg.jitter(mg.quad_rect(40, 31)))):
-        loc = fm.localize(g, mg.slab_partition(g, world), rank)
-        fx = api.Femx(device=lr)
-        fx.set_mesh(loc).build_plan()
-        da = par.DistributedAssembly(fx, dist, dev)
+    import ctypes as C
+    cases = [(name, g, peer, rep) for name, g in (("hex", mg.jitter(mg.hex_cube(12, clamp=False))), ("tet", mg.jitter(mg.tet_cube(6))),
+                                                  ("quad", mg.jitter(mg.quad_rect(40, 31))))
+             for peer in (0, 1, 2) for rep in ((0, 1, 2) if peer else (0,))]   # 0 NCCL, 1 push kernel, 2 stores fused into the assembly kernel
+    fx = da = None
+    for name, g, peer, rep in cases:
+        if rep == 0:
+            if fx is not None:
+                da.close(); fx.close()
+            loc = fm.localize(g, mg.slab_partition(g, world), rank)
+            fx = api.Femx(device=lr, peer_in_kernel=peer == 2)
+            fx.set_mesh(loc).build_plan()
+            da = par.DistributedAssembly(fx, dist, dev, peer=peer > 0)
         u = mg.displacement_field(loc)
         d_u = torch.from_numpy(u.reshape(-1)).to(dev)
         d_f = torch.zeros(fx.nrows, dtype=torch.float64, device=dev)
-        import ctypes as C
+        da.vals_local.fill_(float("nan"))
+        torch.cuda.synchronize()
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, C.c_void_p(d_u.data_ptr()), C.c_void_p(da.vals_local.data_ptr()),
                                          C.c_void_p(d_f.data_ptr()), api.DEVICE))
         da.exchange()
         merged = da.merged().cpu().numpy()
+        if peer:                                   # owned rows: own partial + what the peers stored into the arena
+            own = da.owned_fint(d_f)
+            d_f.zero_()
+            d_f[da.ep.row_start:da.ep.row_end] = own
         dist.all_reduce(d_f)                       # residual: plain sum of the ranks' partial vectors
         og = orc.Mesh(g)
         rp, ci, va = orc.assemble_K(og).export(og.ndof)
@@ -46,10 +60,10 @@ def main():
         f_ref = orc.fint(og, mg.displacement_field(g).reshape(-1))
         f = d_f.cpu().numpy()
         good = good and np.all(np.abs(f - f_ref) <= 1e-12 * np.maximum(np.abs(f_ref), np.abs(f_ref).max()))
-        print(f"[rank {rank}] {name}: owned rows [{r0},{r1}) nnz {len(merged)} recv {int(da.ep.recv_counts.sum())} "
+        print(f"[rank {rank}] {name} {('nccl', 'peer-push', 'peer-fused')[peer]} #{rep}: owned rows [{r0},{r1}) nnz {len(merged)} recv {int(da.ep.recv_counts.sum())} "
               f"{'OK' if good else 'MISMATCH'}", flush=True)
         ok = ok and bool(good)
-        fx.close()
+    da.close(); fx.close()
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
