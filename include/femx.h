@@ -61,7 +61,7 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, else 1),
+/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, else 9, else 1),
  * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
  * 3 = its warp-specialised form, 5 = symmetric pair-block kernel on 16 warps (6, 7, 8: its measured tile / thread
  * variants, 4 = alias of 8), 9 = fused rows kernel for any element mix */
@@ -159,13 +159,14 @@ int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b,
 /* Peer-memory interface exchange (one node, 2..8 ranks; replaces the stash traffic of MatAssemblyBegin/End,
  * src/main.F90:167-168).  The rank-local CSR lists rows in ascending global order, so the values bound for rank q
  * are the contiguous local value range [val_bounds[q], val_bounds[q+1]) and the internal-force entries (numbered
- * pdim*local_node + i) the range [f_bounds[q], f_bounds[q+1]).  After femx_peer_connect the assembly kernels of
- * femx_assemble_K / femx_assemble_K_fint (variants 0, 5, 9) store those ranges straight into
- * rank q's receive arena over NVLink, at val_dst[q] / f_dst[q] doubles from the start of q's value / force receive
- * area, and the call ends with a device-side step barrier among the ranks: at return the rank's own slice of `vals`
- * (and the owned rows of `fint`) plus everything its peers sent are complete.  The non-owned ranges of the local
- * `vals` / `fint` arrays are NOT written in this mode.  Assemblies are collective: every rank calls them the same
- * number of times.  The arena is double-buffered on the call parity.
+ * pdim*local_node + i) the range [f_bounds[q], f_bounds[q+1]).  After femx_peer_connect, femx_assemble_K /
+ * femx_assemble_K_fint push those ranges into rank q's receive arena over NVLink (remote stores of a kernel behind
+ * the assembly kernel; with opts.reserved[3] = 1 and variants 0, 5, 9 the assembly kernel stores them there itself
+ * and the non-owned ranges of the local arrays are not written), at val_dst[q] / f_dst[q] doubles from the start of
+ * q's value / force receive area, and the call ends with a device-side step barrier among the ranks: at return the
+ * rank's own slice of `vals` (and the owned rows of `fint`) plus everything its peers sent are complete.
+ * Assemblies are collective: every rank calls them the same number of times.  The arena is double-buffered on the
+ * call parity.
  *   femx_peer_arena_create  allocates the arena for n_recv_vals + n_recv_f doubles (per buffer) and returns its
  *                           cudaIpcMemHandle (64 bytes) for the caller to all-gather among the ranks;
  *   femx_peer_connect       handles = nranks x 64 bytes, recv_vals / recv_f = every rank's arena capacities;

@@ -61,6 +61,45 @@ def _worker(rank, world, port, kind, out):
         assert np.all(np.abs(merged - ref) <= 1e-12 * np.maximum(np.abs(ref), np.abs(va_g).max()))
         # COO form: every (i, j) owned, duplicates only on interface rows
         assert len(ep.coo_i) == (ep.own_hi - ep.own_lo) + int(ep.recv_counts.sum())
+        # peer-memory layout (csrc/peer.cu): every sender's slice must land where the receiver's source-rank-ordered
+        # lists expect it, for the matrix values and for the internal force (wire format: local dof order)
+        lay = par.peer_layout(ep, rr, loc.nl2g, loc.pdim, om.ndof, len(vals))
+        val_dst, f_dst, caps = par.exchange_offsets(lay, dist, world)
+        assert caps[rank, 0] == ep.recv_counts.sum() and np.array_equal(np.diff(lay["recv_voff"]), ep.recv_counts)
+        u = mg.displacement_field(loc)
+        f_loc = orc.fint(om, u.reshape(-1))                      # global-length partial, this rank's elements only
+        gdof = (loc.pdim * (loc.nl2g.astype(np.int64) - 1)[:, None] + np.arange(loc.pdim)).reshape(-1)
+        arena_v, arena_f = np.full(int(caps[rank, 0]), np.nan), np.full(int(caps[rank, 1]), np.nan)
+        reqs, stash = [], []
+        for q in range(world):
+            if q == rank:
+                continue
+            vb, fb = lay["val_bounds"], lay["f_bounds"]
+            msg = np.concatenate([[val_dst[q], vb[q + 1] - vb[q], f_dst[q], fb[q + 1] - fb[q]], vals[vb[q]:vb[q + 1]],
+                                  f_loc[gdof[fb[q]:fb[q + 1]]]])
+            hdr = torch.tensor([len(msg)], dtype=torch.int64)
+            reqs.append(dist.isend(hdr, q)); reqs.append(dist.isend(torch.from_numpy(msg), q, tag=1))
+        for q in range(world):
+            if q == rank:
+                continue
+            hdr = torch.empty(1, dtype=torch.int64)
+            dist.recv(hdr, q)
+            buf = torch.empty(int(hdr.item()), dtype=torch.float64)
+            dist.recv(buf, q, tag=1)
+            b = buf.numpy()
+            vo, vn, fo, fn = (int(x) for x in b[:4])
+            arena_v[vo:vo + vn] = b[4:4 + vn]                    # the remote store of rank q's push kernel
+            arena_f[fo:fo + fn] = b[4 + vn:4 + vn + fn]
+        for r in reqs:
+            r.wait()
+        assert np.array_equal(arena_v, np.concatenate([o.numpy() for o in outs])), "arena = source-rank-ordered receive list"
+        f_own = f_loc[r0:r1].copy()
+        for s_, rows in enumerate(lay["f_rows"]):
+            o = int(lay["recv_foff"][s_])
+            np.add.at(f_own, rows - r0, arena_f[o:o + len(rows)])
+        ug = mg.displacement_field(g)
+        f_ref = orc.fint(og, ug.reshape(-1))[r0:r1]
+        assert np.all(np.abs(f_own - f_ref) <= 1e-12 * max(np.abs(f_ref).max(), 1e-300)), "owned internal force"
         out.put((rank, int(ep.recv_counts.sum()), len(merged)))
     finally:
         dist.destroy_process_group()
