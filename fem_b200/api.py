@@ -271,6 +271,22 @@ class Femx:
         self._ck(self.L.femx_residual_forces(self.h, _p(u), _p(f), float(dt), float(t_total), _p(r), HOST))
         return r
 
+    def set_loads(self, fnode=(), fval=(), telsd=(), tval=()):
+        """fnode/fval, telsd/tval as ReadDistForces / ReadDistTractions leave them (src/m_io.F90:330-372, :414-475)."""
+        pd = self.mesh.pdim
+        fn = np.ascontiguousarray(fnode, np.int32).reshape(-1)
+        fv = np.ascontiguousarray(fval, np.float64).reshape(len(fn), pd + 2) if len(fn) else np.zeros((0, pd + 2))
+        te = np.ascontiguousarray(telsd, np.int32).reshape(-1, 2)
+        tv = np.ascontiguousarray(tval, np.float64).reshape(len(te), pd + 2) if len(te) else np.zeros((0, pd + 2))
+        self._ck(self.L.femx_set_loads(self.h, len(fn), _ip(fn), _dp(fv), len(te), _ip(te), _dp(tv)))
+        return self
+
+    def FormRHS(self, t_init, dt, t_total) -> np.ndarray:
+        """FormRHS (src/m_global.F90:373-436): global-length Vec_F of this rank."""
+        f = np.empty(self.nrows)
+        self._ck(self.L.femx_form_rhs(self.h, float(t_init), float(dt), float(t_total), _p(f), HOST))
+        return f
+
     def stress(self, uu_local, layout=ROW_MAJOR) -> np.ndarray:
         """RecoverStress + RecoverNodalStress + average: stress_node [nlnds, cp]."""
         u = np.ascontiguousarray(uu_local, dtype=np.float64).reshape(-1)

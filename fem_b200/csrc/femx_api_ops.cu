@@ -230,7 +230,7 @@ static int residual_impl(femx_ctx *c, const double *jvals, const double *u_total
   CK(cudaMemcpyAsync(d_br, d_f, sizeof(double) * (size_t)nglob, cudaMemcpyDeviceToDevice, c->stream));  // VecCopy(Vec_F, R)
   c->launches += launch_cohesive_mesh(c, d_u, dt, c->d_coh_fe, nullptr);
   c->launches += launch_cohesive_force_gather(c, d_br);
-  c->launches += launch_bc_force(c, dt / t_total, d_br);  // EnforceBCForce :439-455
+  c->launches += launch_bc_force(c, dt, t_total, d_br);  // EnforceBCForce :439-455
   if (jvals) {
     if (c->nlnds != c->nnds) CK(cudaMemsetAsync(d_r, 0, sizeof(double) * (size_t)nglob, c->stream));
     c->launches += launch_spmv_sub(c, d_j, d_du, d_br, d_r);  // VecScale(-1); MatMultAdd :225-226
@@ -251,6 +251,76 @@ int femx_residual_forces(femx_ctx *c, const double *u_total_local, const double 
                          double *out, int where) {
   if (!c) return FEMX_ERR_ARG;
   return residual_impl(c, nullptr, u_total_local, nullptr, f_ext, dt, t_total, out, where);
+}
+
+// ---- loads: ReadDistForces / ReadDistTractions arrays (src/m_io.F90:330-372, :414-475) -> FormRHS
+int femx_set_loads(femx_ctx *c, int nfrcs, const int *fnode, const double *fval, int ntrcs, const int *telsd, const double *tval) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan, "femx_build_plan first");
+  ARG(nfrcs >= 0 && ntrcs >= 0 && (nfrcs == 0 || (fnode && fval)) && (ntrcs == 0 || (telsd && tval)), "bad load arrays");
+  CK(cudaSetDevice(c->device));
+  const int pd = c->pdim, w = pd + 2;
+  static const int tri[3][2] = {{0, 1}, {1, 2}, {2, 0}}, qua[4][2] = {{0, 1}, {1, 2}, {2, 3}, {3, 0}};
+  static const int tet[4][3] = {{0, 1, 3}, {1, 2, 3}, {0, 2, 3}, {0, 1, 2}};
+  static const int hex[6][4] = {{0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}, {0, 1, 2, 3}, {4, 5, 6, 7}};
+  // (dof, order) pairs in the reference's call order: all nodal forces, then all tractions (src/m_global.F90:399-428)
+  std::vector<std::pair<int64_t, int32_t>> ent;
+  for (int i = 0; i < nfrcs; ++i) {
+    ARG(fnode[i] >= 1 && fnode[i] <= c->nnds, "femx_set_loads: force node out of range");
+    for (int d = 0; d < pd; ++d) ent.push_back({(int64_t)pd * fnode[i] - pd + d, (i << 3) | d});
+  }
+  std::vector<int32_t> tel(2 * (size_t)ntrcs, 0);
+  for (int i = 0; i < ntrcs; ++i) {
+    const int el = telsd[2 * i], side = telsd[2 * i + 1];
+    tel[2 * i] = el - 1; tel[2 * i + 1] = side;
+    if (el == 0) continue;   // `if (el/=0)`, src/m_global.F90:427
+    ARG(el >= 1 && el <= c->nels, "femx_set_loads: traction element out of range");
+    const int t = c->etype[el - 1];
+    ARG(t != FEMX_COH, "femx_set_loads: traction on a cohesive element");
+    const int nsides = t == FEMX_TRI ? 3 : (t == FEMX_HEX ? 6 : 4), nps = t == FEMX_HEX ? 4 : (t == FEMX_TET ? 3 : 2);
+    ARG(side >= 1 && side <= nsides, "femx_set_loads: side out of range");
+    const int *j = t == FEMX_TRI ? tri[side - 1] : t == FEMX_QUA ? qua[side - 1] : t == FEMX_TET ? tet[side - 1] : hex[side - 1];
+    for (int q = 0; q < nps; ++q) {
+      const int g = c->nl2g[c->eind[c->eptr[el - 1] + j[q]] - 1];
+      for (int d = 0; d < pd; ++d) ent.push_back({(int64_t)pd * g - pd + d, (i << 3) | 4 | d});
+    }
+  }
+  std::stable_sort(ent.begin(), ent.end(), [](const auto &a, const auto &b) { return a.first < b.first; });
+  std::vector<int64_t> dof;
+  std::vector<int32_t> ptr, src;
+  for (size_t k = 0; k < ent.size(); ++k) {
+    if (k == 0 || ent[k].first != ent[k - 1].first) { dof.push_back(ent[k].first); ptr.push_back((int32_t)k); }
+    src.push_back(ent[k].second);
+  }
+  ptr.push_back((int32_t)ent.size());
+  auto &L = c->loads;
+  dev_release(c, L.dof); dev_release(c, L.ptr); dev_release(c, L.src); dev_release(c, L.fval); dev_release(c, L.tval); dev_release(c, L.tel);
+  L = femx::DevLoads{};
+  L.ntouched = (int)dof.size(); L.nfrcs = nfrcs; L.ntrcs = ntrcs;
+  int rc;
+  if ((rc = upload(c, &L.dof, dof)) || (rc = upload(c, &L.ptr, ptr)) || (rc = upload(c, &L.src, src))) return rc;
+  if ((rc = upload(c, &L.fval, std::vector<double>(fval, fval + (size_t)nfrcs * w)))) return rc;
+  if ((rc = upload(c, &L.tval, std::vector<double>(tval, tval + (size_t)ntrcs * w)))) return rc;
+  if ((rc = upload(c, &L.tel, tel))) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+
+int femx_form_rhs(femx_ctx *c, double t_init, double dt, double t_total, double *f, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && f, "femx_build_plan first / NULL argument");
+  CK(cudaSetDevice(c->device));
+  const int64_t nglob = (int64_t)c->pdim * c->nnds;
+  int rc;
+  double *d_f = nullptr;
+  if ((rc = stage_out(c, f, nglob, where, &c->d_vec[3], &d_f))) return rc;
+  if ((rc = begin_timing(c))) return rc;
+  CK(cudaMemsetAsync(d_f, 0, sizeof(double) * (size_t)nglob, c->stream));   // VecZeroEntries(Vec_F)
+  c->launches += launch_form_rhs(c, t_init, dt, d_f);
+  c->launches += launch_bc_force(c, dt, t_total, d_f);                      // EnforceBCForce
+  if ((rc = end_timing(c))) return rc;
+  if ((rc = copy_back(c, f, d_f, nglob, where))) return rc;
+  return finish_call(c, true);
 }
 
 int femx_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, const int64_t *ptr, const int64_t *idx,

@@ -150,6 +150,17 @@ struct DevMesh {
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 
+// loads of FormRHS (src/m_global.F90:373-436) gathered by destination dof, contributions in the reference's call order
+struct DevLoads {
+  int ntouched = 0, nfrcs = 0, ntrcs = 0;
+  int64_t *dof = nullptr;      // [ntouched] global dof
+  int32_t *ptr = nullptr;      // [ntouched+1]
+  int32_t *src = nullptr;      // (load index << 3) | (kind << 2) | component; kind 0 = nodal force, 1 = traction
+  double *fval = nullptr;      // [nfrcs][pdim+2]
+  double *tval = nullptr;      // [ntrcs][pdim+2]
+  int32_t *tel = nullptr;      // [ntrcs][2] 0-based local element, 1-based side
+};
+
 }  // namespace femx
 
 struct femx_ctx {
@@ -191,6 +202,7 @@ struct femx_ctx {
   int64_t *d_cblk_id = nullptr;
   int32_t *d_cnode_id = nullptr, *d_cnode_ptr = nullptr, *d_cnode_src = nullptr;
   double *d_coh_ke = nullptr, *d_coh_fe = nullptr;
+  femx::DevLoads loads;
   std::vector<void *> allocs;  // everything cudaMalloc'ed by the ctx
   // peer-memory exchange (peer.cu)
   struct Peer {

@@ -262,10 +262,76 @@ __global__ void apply_kbc_kernel(int n, const int64_t *__restrict__ diag, double
 }
 
 __global__ void bc_force_kernel(int n, const int64_t *__restrict__ dof, const double *__restrict__ val,
-                                double scale, double *__restrict__ out) {
+                                double dt, double t_total, double *__restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  // vvec = PENALTY_PARAM * bcval * dt / t, INSERT (src/m_global.F90:451)
-  if (i < n) out[dof[i]] = kPenalty * val[i] * scale;
+  // vvec = PENALTY_PARAM * bcval * dt / t, INSERT (src/m_global.F90:451), evaluated left to right
+  if (i < n) out[dof[i]] = __ddiv_rn(__dmul_rn(__dmul_rn(kPenalty, val[i]), dt), t_total);
+}
+
+// ---- FormRHS (src/m_global.F90:373-436).  Explicit _rn intrinsics: no FMA contraction, the sums round like the
+// reference's scalar code.
+// MatDet (src/m_utils.F90:60-66) of the matrices TriArea builds (:25-33): columns a, b, (1, 1, 1)
+__device__ __forceinline__ double det3_ones(double a1, double a2, double a3, double b1, double b2, double b3) {
+  const double t1 = __dmul_rn(a1, __dsub_rn(b2, b3)), t2 = __dmul_rn(b1, __dsub_rn(a2, a3));
+  const double t3 = __dsub_rn(__dmul_rn(a2, b3), __dmul_rn(b2, a3));
+  return __dadd_rn(__dsub_rn(t1, t2), t3);
+}
+__device__ __forceinline__ double tri_area(const double *p1, const double *p2, const double *p3) {
+  const double d1 = fabs(det3_ones(p1[0], p2[0], p3[0], p1[1], p2[1], p3[1]));
+  const double d2 = fabs(det3_ones(p1[1], p2[1], p3[1], p1[2], p2[2], p3[2]));
+  const double d3 = fabs(det3_ones(p1[2], p2[2], p3[2], p1[0], p2[0], p3[0]));
+  return __dmul_rn(0.5, __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(d1, d1), __dmul_rn(d2, d2)), __dmul_rn(d3, d3))));
+}
+// EdgeAreaNodes{Tri,Qua,Tet,Hex} (src/m_elems.F90:282-293, 366-378, 469-482, 583-599): length / area of a side
+__device__ double side_area(const DevMesh &dm, int e, int side, int *nps) {
+  const int t = dm.etype[e];
+  const int32_t *cn = dm.conn0 + dm.eptr[e];
+  if (t == FEMX_TRI || t == FEMX_QUA) {
+    const int nen = t == FEMX_TRI ? 3 : 4, a = side - 1, b = side % nen;
+    const double *x = dm.coords + 2 * (int64_t)cn[a], *y = dm.coords + 2 * (int64_t)cn[b];
+    const double dx = __dsub_rn(x[0], y[0]), dy = __dsub_rn(x[1], y[1]);
+    *nps = 2;
+    return __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+  }
+  if (t == FEMX_TET) {
+    const int j[4][3] = {{0, 1, 3}, {1, 2, 3}, {0, 2, 3}, {0, 1, 2}};
+    *nps = 3;
+    return tri_area(dm.coords + 3 * (int64_t)cn[j[side - 1][0]], dm.coords + 3 * (int64_t)cn[j[side - 1][1]],
+                    dm.coords + 3 * (int64_t)cn[j[side - 1][2]]);
+  }
+  const int j[6][4] = {{0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}, {0, 1, 2, 3}, {4, 5, 6, 7}};
+  const double *p0 = dm.coords + 3 * (int64_t)cn[j[side - 1][0]], *p1 = dm.coords + 3 * (int64_t)cn[j[side - 1][1]];
+  const double *p2 = dm.coords + 3 * (int64_t)cn[j[side - 1][2]], *p3 = dm.coords + 3 * (int64_t)cn[j[side - 1][3]];
+  *nps = 4;
+  return __dadd_rn(fabs(tri_area(p0, p1, p2)), fabs(tri_area(p0, p2, p3)));   // QuadArea, src/m_utils.F90:36-42
+}
+
+// one thread per loaded dof; contributions added in the reference's call order (nodal forces, then tractions)
+__global__ void form_rhs_kernel(DevMesh dm, DevLoads L, double t_init, double t_end, double dt, double *__restrict__ f) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L.ntouched) return;
+  const int pd = dm.pdim, w = pd + 2;
+  double s = 0.0;   // VecZeroEntries
+  for (int c = L.ptr[i]; c < L.ptr[i + 1]; ++c) {
+    const int code = L.src[c], comp = code & 3, idx = code >> 3;
+    if (!(code & 4)) {   // nodal force: fval * applied_interval / (t2 - t1), src/m_global.F90:399-409
+      const double *fv = L.fval + (int64_t)idx * w;
+      const double t1 = fv[pd], t2 = fv[pd + 1];
+      if (t_end < t1 || t_init > t2) continue;
+      const double interval = __dsub_rn(fmin(t2, t_end), fmax(t1, t_init));
+      s = __dadd_rn(s, __ddiv_rn(__dmul_rn(fv[comp], interval), __dsub_rn(t2, t1)));
+    } else {             // traction: tval * (applied_interval / (t2 - t1)), t1 and t2 divided by dt (:414-415), then * area / nps (:360)
+      const double *tv = L.tval + (int64_t)idx * w;
+      const double t1 = __ddiv_rn(tv[pd], dt), t2 = __ddiv_rn(tv[pd + 1], dt);
+      if (t_end < t1 || t_init > t2) continue;
+      const double interval = __dsub_rn(fmin(t2, t_end), fmax(t1, t_init));
+      int nps;
+      const double area = side_area(dm, L.tel[2 * idx], L.tel[2 * idx + 1], &nps);
+      const double v = __dmul_rn(tv[comp], __ddiv_rn(interval, __dsub_rn(t2, t1)));
+      s = __dadd_rn(s, __ddiv_rn(__dmul_rn(v, area), (double)nps));
+    }
+  }
+  f[L.dof[i]] = s;
 }
 
 // y[g] = sum_k J[row, k] * x[col] - sub[g] over the local node rows (one warp per node)
@@ -479,9 +545,15 @@ int launch_apply_kbc(femx_ctx *c, double *d_vals) {
   return 1;
 }
 
-int launch_bc_force(femx_ctx *c, double scale, double *d_out) {
+int launch_bc_force(femx_ctx *c, double dt, double t_total, double *d_out) {
   if (!c->nbc_dofs) return 0;
-  bc_force_kernel<<<nblocks(c->nbc_dofs, 128), 128, 0, c->stream>>>(c->nbc_dofs, c->d_bc_dof, c->d_bc_val, scale, d_out);
+  bc_force_kernel<<<nblocks(c->nbc_dofs, 128), 128, 0, c->stream>>>(c->nbc_dofs, c->d_bc_dof, c->d_bc_val, dt, t_total, d_out);
+  return 1;
+}
+
+int launch_form_rhs(femx_ctx *c, double t_init, double dt, double *d_f) {
+  if (!c->loads.ntouched) return 0;
+  form_rhs_kernel<<<nblocks(c->loads.ntouched, 128), 128, 0, c->stream>>>(c->dm, c->loads, t_init, t_init + dt, dt, d_f);
   return 1;
 }
 

@@ -14,7 +14,8 @@ int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const
 int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major);
 int launch_colidx(femx_ctx *c, int32_t *d_colidx);
 int launch_apply_kbc(femx_ctx *c, double *d_vals);
-int launch_bc_force(femx_ctx *c, double scale, double *d_out);
+int launch_bc_force(femx_ctx *c, double dt, double t_total, double *d_out);
+int launch_form_rhs(femx_ctx *c, double t_init, double dt, double *d_f);
 int launch_spmv_sub(femx_ctx *c, const double *d_vals, const double *d_x, const double *d_sub, double *d_y);
 int launch_cohesive_mesh(femx_ctx *c, const double *d_u, double dt, double *d_force, double *d_stiff);
 int launch_cohesive_unit(femx_ctx *c, int n, const double *d_x, const int32_t *d_nodes, const double *d_u,

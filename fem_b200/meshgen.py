@@ -180,6 +180,24 @@ def hex_block(nx: int, ny: int, nz: int, z0: int = 0, nz_total: int | None = Non
     return m
 
 
+def random_loads(m: Mesh, nfrcs=40, ntrcs=60, seed=7):
+    """Synthetic FormRHS input (src/m_global.F90:373-436): nodal forces on GLOBAL nodes this rank holds (repeats
+    included, so several contributions meet in one dof) and tractions on random sides of random non-cohesive LOCAL
+    elements, with ramp windows that start before, inside and after [t_init, t_init + dt]; one traction row with
+    element 0 (skipped by the reference, :427).  Returns fnode, fval, telsd, tval."""
+    rng = np.random.default_rng(seed)
+    pd = m.pdim
+    fnode = rng.choice(m.nl2g, size=nfrcs).astype(np.int32)
+    fval = np.c_[rng.uniform(-1e3, 1e3, (nfrcs, pd)), rng.uniform(0.0, 0.6, nfrcs), rng.uniform(0.7, 2.0, nfrcs)]
+    solid = np.flatnonzero(np.asarray(m.etype) != 5)
+    els = rng.choice(solid, size=ntrcs)
+    nsides = np.where(m.etype[els] == 1, 3, np.where(m.etype[els] == 4, 6, 4))
+    telsd = np.c_[els + 1, 1 + rng.integers(0, 1 << 30, ntrcs) % nsides].astype(np.int32)
+    telsd[ntrcs // 2, 0] = 0
+    tval = np.c_[rng.uniform(-50.0, 50.0, (ntrcs, pd)), rng.uniform(0.0, 0.6, ntrcs) * m.dt, rng.uniform(0.7, 2.0, ntrcs) * m.dt]
+    return fnode, fval, telsd, tval
+
+
 def slab_partition(m: Mesh, nparts: int) -> np.ndarray:
     """Element partition into `nparts` contiguous element ranges (slabs along the slowest
     axis for the structured generators).  Stand-in for METIS_PartMeshNodal

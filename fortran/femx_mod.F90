@@ -129,6 +129,45 @@ module femx
       type(c_ptr), value :: ctx, a, b, ptr, idx, out
       integer(c_int64_t), value :: na, nout
     end function
+    ! FormRHS (src/m_global.F90:373-436): fnode / fval / telsd / tval as ReadDistForces / ReadDistTractions leave them,
+    ! TRANSPOSED to row-major (the Fortran arrays are (count, pdim+2) column-major)
+    integer(c_int) function femx_set_loads(ctx, nfrcs, fnode, fval, ntrcs, telsd, tval) bind(C, name="femx_set_loads")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nfrcs, ntrcs
+      integer(c_int), intent(in) :: fnode(*), telsd(*)
+      real(c_double), intent(in) :: fval(*), tval(*)
+    end function
+    integer(c_int) function femx_form_rhs(ctx, t_init, dt, t_total, f, where) bind(C, name="femx_form_rhs")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx, f
+      real(c_double), value :: t_init, dt, t_total
+      integer(c_int), value :: where
+    end function
+    ! peer-memory interface exchange (include/femx.h): handles are 64-byte cudaIpcMemHandle blobs
+    integer(c_int) function femx_peer_arena_create(ctx, n_recv_vals, n_recv_f, handle) bind(C, name="femx_peer_arena_create")
+      import :: c_ptr, c_int, c_int64_t, c_char
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), value :: n_recv_vals, n_recv_f
+      character(kind=c_char), intent(out) :: handle(64)
+    end function
+    integer(c_int) function femx_peer_connect(ctx, nranks, rank, handles, recv_vals, recv_f, val_bounds, val_dst, &
+                                              f_bounds, f_dst) bind(C, name="femx_peer_connect")
+      import :: c_ptr, c_int, c_int64_t, c_char
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nranks, rank
+      character(kind=c_char), intent(in) :: handles(*)
+      integer(c_int64_t), intent(in) :: recv_vals(*), recv_f(*), val_bounds(*), val_dst(*), f_bounds(*), f_dst(*)
+    end function
+    integer(c_int) function femx_peer_recv(ctx, vals_recv, f_recv) bind(C, name="femx_peer_recv")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+      type(c_ptr), intent(out) :: vals_recv, f_recv
+    end function
+    integer(c_int) function femx_peer_disconnect(ctx) bind(C, name="femx_peer_disconnect")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
   end interface
 
 contains

@@ -145,6 +145,18 @@ int femx_residual_forces(femx_ctx *ctx, const double *u_total_local, const doubl
                          double t_total, double *out, int where);
 /* RecoverStress + RecoverNodalStress + nodal average, src/main.F90:253-279.
  * stress_node [nlnds][cp] row-major (or column-major stress_node(nlnds,cpdim) by layout) */
+/* Loads.  femx_set_loads takes the arrays ReadDistForces / ReadDistTractions leave on a rank
+ * (src/m_io.F90:330-372, :414-475): fnode[nfrcs] GLOBAL 1-based node, fval[nfrcs][pdim+2] = components, t1, t2;
+ * telsd[ntrcs][2] = LOCAL 1-based element (0 = skip, src/m_global.F90:427), 1-based side; tval[ntrcs][pdim+2].
+ * Row-major.  Call after femx_build_plan (and again when the loads change).
+ * femx_form_rhs = FormRHS (src/m_global.F90:373-436): f[pdim*nnds] <- 0, time-ramped nodal forces, tractions spread
+ * by ApplyTraction (:343-368) with EdgeAreaNodes* (src/m_elems.F90:282-599) as vvec*area/nps per side node (traction
+ * t1, t2 are divided by dt as the reference does, nodal ones are not), contributions per dof added in the reference's
+ * call order, then EnforceBCForce (:439-455) INSERTs 1e30*bcval*dt/t on constrained dofs.  nceqs is unsupported
+ * (the reference never allocates cval, src/main.F90:108-109). */
+int femx_set_loads(femx_ctx *ctx, int nfrcs, const int *fnode, const double *fval, int ntrcs, const int *telsd,
+                   const double *tval);
+int femx_form_rhs(femx_ctx *ctx, double t_init, double dt, double t_total, double *f, int where);
 int femx_stress(femx_ctx *ctx, const double *uu_local, double *stress_node, int layout, int where);
 
 /* ---- multi-GPU (one ctx per rank) ----------------------------------- */

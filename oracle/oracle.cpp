@@ -707,4 +707,92 @@ double orc_time_assembly(const orc_mesh *M, int prealloc, const double *u_local,
   return std::chrono::duration<double>(t1 - t0).count();
 }
 
+
+// ---- loads and the right-hand side ----
+// MatDet of a 3x3 (src/m_utils.F90:60-66) on the columns TriArea builds (src/m_utils.F90:25-33)
+static double det3_ones(double a1, double a2, double a3, double b1, double b2, double b3) {
+  // A = [a1 b1 1; a2 b2 1; a3 b3 1]
+  return a1 * (b2 * 1.0 - 1.0 * b3) - b1 * (a2 * 1.0 - 1.0 * a3) + 1.0 * (a2 * b3 - b2 * a3);
+}
+static double tri_area(const double *p1, const double *p2, const double *p3) {
+  const double d1 = det3_ones(p1[0], p2[0], p3[0], p1[1], p2[1], p3[1]);
+  const double d2 = det3_ones(p1[1], p2[1], p3[1], p1[2], p2[2], p3[2]);
+  const double d3 = det3_ones(p1[2], p2[2], p3[2], p1[0], p2[0], p3[0]);
+  return 0.5 * std::sqrt(std::fabs(d1) * std::fabs(d1) + std::fabs(d2) * std::fabs(d2) + std::fabs(d3) * std::fabs(d3));
+}
+
+// EdgeAreaNodes{Tri,Qua,Tet,Hex} (src/m_elems.F90:282-293, 366-378, 469-482, 583-599): local node slots (0-based)
+// of side `side` (1-based) and its length / area; returns nodes per side (elNodePerSide, src/m_elems.F90:28)
+int orc_edge_area_nodes(int type, const double *ecoords, int side, double *area, int *slots) {
+  static const int tri[3][2] = {{0, 1}, {1, 2}, {2, 0}};
+  static const int qua[4][2] = {{0, 1}, {1, 2}, {2, 3}, {3, 0}};
+  static const int tet[4][3] = {{0, 1, 3}, {1, 2, 3}, {0, 2, 3}, {0, 1, 2}};
+  static const int hex[6][4] = {{0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}, {0, 1, 2, 3}, {4, 5, 6, 7}};
+  if (type == ORC_TRI || type == ORC_QUA) {
+    const int *j = type == ORC_TRI ? tri[side - 1] : qua[side - 1];
+    slots[0] = j[0]; slots[1] = j[1];
+    const double dx = ecoords[j[0] * 2] - ecoords[j[1] * 2], dy = ecoords[j[0] * 2 + 1] - ecoords[j[1] * 2 + 1];
+    *area = std::sqrt(dx * dx + dy * dy);
+    return 2;
+  }
+  if (type == ORC_TET) {
+    const int *j = tet[side - 1];
+    for (int q = 0; q < 3; ++q) slots[q] = j[q];
+    *area = tri_area(ecoords + 3 * j[0], ecoords + 3 * j[1], ecoords + 3 * j[2]);
+    return 3;
+  }
+  const int *j = hex[side - 1];
+  for (int q = 0; q < 4; ++q) slots[q] = j[q];
+  const double ta1 = tri_area(ecoords + 3 * j[0], ecoords + 3 * j[1], ecoords + 3 * j[2]);   // QuadArea, src/m_utils.F90:36-42
+  const double ta2 = tri_area(ecoords + 3 * j[0], ecoords + 3 * j[2], ecoords + 3 * j[3]);
+  *area = std::fabs(ta1) + std::fabs(ta2);
+  return 4;
+}
+
+// FormRHS (src/m_global.F90:373-436): Vec_F = 0; time-ramped nodal forces (fnode global 1-based, fval(nfrcs, pdim+2)
+// = components, t1, t2); tractions (telsd = local element 1-based / side, tval(ntrcs, pdim+2); NOTE t1, t2 are divided
+// by dt here and only here, :414-415) spread by ApplyTraction (:343-368) as vvec*area/nps on the side's nodes;
+// then EnforceBCForce (:439-455) INSERTs 1e30*bcval*dt/t on the constrained dofs.  nceqs is not supported by the
+// reference itself (cval is never allocated, src/main.F90:108-109).
+void orc_form_rhs(const orc_mesh *M, int nfrcs, const int *fnode, const double *fval, int ntrcs, const int *telsd,
+                  const double *tval, double t_init, double dt, double t_total, double *f) {
+  const int pd = M->pdim, w = pd + 2;
+  const int64_t n = (int64_t)pd * M->nnds;
+  for (int64_t i = 0; i < n; ++i) f[i] = 0.0;
+  const double t_end = t_init + dt;
+  for (int i = 0; i < nfrcs; ++i) {
+    const double t1 = fval[i * w + pd], t2 = fval[i * w + pd + 1];
+    if (t_end < t1 || t_init > t2) continue;
+    const double interval = std::fmin(t2, t_end) - std::fmax(t1, t_init);
+    for (int d = 0; d < pd; ++d) f[(int64_t)pd * fnode[i] - pd + d] += fval[i * w + d] * interval / (t2 - t1);
+  }
+  for (int i = 0; i < ntrcs; ++i) {
+    const double t1 = tval[i * w + pd] / dt, t2 = tval[i * w + pd + 1] / dt;
+    if (t_end < t1 || t_init > t2) continue;
+    const double interval = std::fmin(t2, t_end) - std::fmax(t1, t_init);
+    const int el = telsd[i * 2], side = telsd[i * 2 + 1];
+    if (el == 0) continue;
+    const int e = el - 1, type = M->etype[e], nen = orc_nen(type);
+    const int *nd = &M->eind[M->eptr[e]];
+    double xe[24];
+    for (int a = 0; a < nen; ++a)
+      for (int d = 0; d < pd; ++d) xe[a * pd + d] = M->coords[(size_t)(nd[a] - 1) * pd + d];
+    double area;
+    int slots[4];
+    const int nps = orc_edge_area_nodes(type, xe, side, &area, slots);
+    double vvec[3];
+    for (int d = 0; d < pd; ++d) vvec[d] = tval[i * w + d] * (interval / (t2 - t1));
+    for (int d = 0; d < pd; ++d) vvec[d] = vvec[d] * area / (double)nps;
+    for (int q = 0; q < nps; ++q) {
+      const int g = M->nl2g[nd[slots[q]] - 1];
+      for (int d = 0; d < pd; ++d) f[(int64_t)pd * g - pd + d] += vvec[d];
+    }
+  }
+  for (int i = 0; i < M->nbcs; ++i) {
+    const int node = M->bcnode[i * (1 + pd)];
+    for (int d = 0; d < pd; ++d)
+      if (M->bcnode[i * (1 + pd) + 1 + d] == 0) f[(int64_t)pd * node - pd + d] = kPenalty * M->bcval[i * pd + d] * dt / t_total;
+  }
+}
+
 }  // extern "C"

@@ -112,6 +112,11 @@ orc_csr *orc_jacobian(const orc_mesh *, const orc_csr *K, const double *u_total_
 void orc_residual(const orc_mesh *, const orc_csr *J, const double *u_total_local,
                   const double *du_global, const double *f_ext_global, double dt,
                   double t_total, int quirks, double *r_global);
+/* loads: EdgeAreaNodes* (src/m_elems.F90:282-599), FormRHS + ApplyTraction + EnforceBCForce
+ * (src/m_global.F90:343-455).  fval / tval rows are (components[pdim], t1, t2); telsd rows (local element, side). */
+int orc_edge_area_nodes(int type, const double *ecoords, int side, double *area, int *slots);
+void orc_form_rhs(const orc_mesh *, int nfrcs, const int *fnode, const double *fval, int ntrcs, const int *telsd,
+                  const double *tval, double t_init, double dt, double t_total, double *f /*[pdim*nnds]*/);
 /* elastic internal force f = sum_e Ke u_e, scattered to global dofs (matrix-free K*u) */
 void orc_fint(const orc_mesh *, const double *u_local, double *f_global);
 /* src/main.F90:253-279: nodal-averaged stress, [nlnds*cp] row-major */

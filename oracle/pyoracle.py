@@ -234,6 +234,26 @@ def residual(mesh, J, u_total_local, du_global, f_ext_global, dt, t_total, quirk
     return r
 
 
+def form_rhs(mesh, fnode, fval, telsd, tval, t_init, dt, t_total):
+    """FormRHS (src/m_global.F90:373-436) on the rank-local mesh: global-length Vec_F."""
+    fn = np.ascontiguousarray(fnode, dtype=np.int32).reshape(-1)
+    fv = np.ascontiguousarray(fval, dtype=np.float64).reshape(len(fn), -1) if len(fn) else np.zeros((0, mesh.pdim + 2))
+    te = np.ascontiguousarray(telsd, dtype=np.int32).reshape(-1, 2)
+    tv = np.ascontiguousarray(tval, dtype=np.float64).reshape(len(te), -1) if len(te) else np.zeros((0, mesh.pdim + 2))
+    f = np.zeros(mesh.ndof)
+    lib().orc_form_rhs(C.byref(mesh.c), len(fn), _i(fn), _d(fv), len(te), _i(te), _d(tv), C.c_double(t_init), C.c_double(dt),
+                       C.c_double(t_total), _d(f))
+    return f
+
+
+def edge_area_nodes(etype, ecoords, side):
+    x = np.ascontiguousarray(ecoords, dtype=np.float64)
+    area = C.c_double()
+    slots = (C.c_int * 4)()
+    nps = lib().orc_edge_area_nodes(int(etype), _d(x), int(side), C.byref(area), slots)
+    return area.value, list(slots[:nps])
+
+
 def fint(mesh, u_local):
     u = np.ascontiguousarray(u_local, dtype=np.float64)
     f = np.zeros(mesh.ndof)

@@ -202,6 +202,26 @@ def _spmv(Jo, x, n, orc):
     return y
 
 
+def test_form_rhs_vs_oracle(fx, orc, golden):
+    """FormRHS on the device (nodal-force ramps, ApplyTraction + EdgeAreaNodes*, EnforceBCForce): the kernel adds each
+    dof's contributions in the reference's call order with unfused roundings -> bit-exact against the oracle."""
+    for name, m in _meshes(golden):
+        fx.set_mesh(m).build_plan()
+        om = orc.Mesh(m)
+        fnode, fval, telsd, tval = mg.random_loads(m, seed=len(name))
+        fx.set_loads(fnode, fval, telsd, tval)
+        biggest = 0.0
+        for t_init in (0.0, 0.5 * m.dt, 3.0 * m.dt):
+            f = fx.FormRHS(t_init, m.dt, m.t)
+            f_o = orc.form_rhs(om, fnode, fval, telsd, tval, t_init, m.dt, m.t)
+            assert np.array_equal(f, f_o), (name, t_init, np.abs(f - f_o).max())
+            biggest = max(biggest, np.abs(f_o).max())
+        assert biggest > 0.0, name
+    fx.set_loads()                                   # no loads: zeros + the BC override only
+    f = fx.FormRHS(0.0, m.dt, m.t)
+    assert np.array_equal(f, orc.form_rhs(om, [], [], [], [], 0.0, m.dt, m.t)), name
+
+
 def test_stress_vs_oracle(fx, orc, golden):
     for name, m in _meshes(golden):
         fx.set_mesh(m).build_plan()

@@ -111,3 +111,70 @@ def test_csr_matsetvalues_semantics(orc):
     rp, ci, va = orc.Csr(h).export(3)
     assert rp.tolist() == [0, 1, 4, 4] and ci.tolist() == [2, 0, 1, 2]
     assert va.tolist() == [0.0, 3.0, 7.0, 3.0]
+
+
+# ---- loads: EdgeAreaNodes*, ApplyTraction, FormRHS, EnforceBCForce -- unpinned by the reference's
+# fixtures (no expected Vec_F anywhere), pinned here analytically
+def test_edge_area_nodes_closed_forms(orc):
+    hexa = REF_SHAPES[fm.HEX] * [1.0, 2.0, 3.0]          # box 2 x 4 x 6
+    want = {1: (12.0, [0, 1, 5, 4]), 2: (24.0, [1, 2, 6, 5]), 3: (12.0, [2, 3, 7, 6]), 4: (24.0, [3, 0, 4, 7]),
+            5: (8.0, [0, 1, 2, 3]), 6: (8.0, [4, 5, 6, 7])}
+    for side, (a, nodes) in want.items():
+        area, slots = orc.edge_area_nodes(fm.HEX, hexa, side)
+        assert abs(area - a) <= 1e-14 * a and slots == nodes
+    tet = REF_SHAPES[fm.TET]
+    for side, (a, nodes) in {1: (0.5, [0, 1, 3]), 2: (np.sqrt(3) / 2, [1, 2, 3]), 3: (0.5, [0, 2, 3]), 4: (0.5, [0, 1, 2])}.items():
+        area, slots = orc.edge_area_nodes(fm.TET, tet, side)
+        assert abs(area - a) <= 1e-15 and slots == nodes
+    qua = REF_SHAPES[fm.QUA] * [1.5, 0.5]
+    for side, (a, nodes) in {1: (3.0, [0, 1]), 2: (1.0, [1, 2]), 3: (3.0, [2, 3]), 4: (1.0, [3, 0])}.items():
+        area, slots = orc.edge_area_nodes(fm.QUA, qua, side)
+        assert abs(area - a) <= 1e-15 and slots == nodes
+    tri = REF_SHAPES[fm.TRI]
+    assert orc.edge_area_nodes(fm.TRI, tri, 2) == (np.sqrt(2.0), [1, 2])
+    assert orc.edge_area_nodes(fm.TRI, tri, 3)[1] == [2, 0]
+
+
+def test_form_rhs_ramps_tractions_and_bc_override(orc):
+    from fem_b200 import meshgen as mg
+    import dataclasses
+    m = mg.quad_rect(2, 2)                               # unit cells, nodes 1..9 row by row
+    bcnode = np.array([[1, 0, 1], [3, 0, 0]], np.int32)  # node 1: x fixed; node 3: both
+    bcval = np.array([[0.02, 9.0], [0.0, -0.5]])
+    m = dataclasses.replace(m, bcnode=bcnode, bcval=bcval)
+    om = orc.Mesh(m)
+    t, dt, t_init = 2.0, 0.25, 0.5                       # this interval: [0.5, 0.75]
+    fnode = [5, 5, 2, 9]
+    fval = [[8.0, -4.0, 0.0, 2.0],                       # window covers the interval: 0.25 / 2 of the load
+            [1.0, 1.0, 0.7, 1.7],                        # starts inside: (0.75 - 0.7) / 1.0
+            [3.0, 3.0, 0.8, 1.0],                        # starts after t_end: nothing
+            [6.0, 0.0, 0.0, 0.5]]                        # ends exactly at t_init: interval of length 0 -> adds 0
+    telsd = [[1, 2], [2, 4], [0, 1]]                     # right edge of cell 1 = left edge of cell 2 (nodes 2, 5); element 0 skipped
+    tval = [[10.0, 0.0, 0.0, 1.0],                       # tractions: t1, t2 are divided by dt (src/m_global.F90:414-415) -> window [0, 4]
+            [0.0, 4.0, 0.0, 1.0],
+            [99.0, 99.0, 0.0, 1.0]]
+    f = orc.form_rhs(om, fnode, fval, telsd, tval, t_init, dt, t).reshape(-1, 2)
+    want = np.zeros((9, 2))
+    want[4] += np.array([8.0, -4.0]) * 0.25 / 2.0
+    want[4] += np.array([1.0, 1.0]) * (0.75 - 0.7) / (1.7 - 0.7)
+    ramp = 0.25 / 4.0
+    for node in (1, 4):                                  # 0-based nodes 2 and 5: edge length 1, two nodes
+        want[node] += np.array([10.0, 0.0]) * ramp * 1.0 / 2 + np.array([0.0, 4.0]) * ramp * 1.0 / 2
+    pen = float(np.float32(1e30))
+    want[0, 0] = pen * 0.02 * dt / t                     # EnforceBCForce overrides whatever was summed
+    want[2] = [pen * 0.0 * dt / t, pen * -0.5 * dt / t]
+    assert np.allclose(f, want, rtol=1e-15, atol=0.0)
+    assert f[1, 0] == 10.0 * ramp / 2 and f[8, 0] == 0.0
+
+
+def test_form_rhs_hex_face_traction_total(orc):
+    from fem_b200 import meshgen as mg
+    m = mg.hex_cube(3, clamp=False)
+    om = orc.Mesh(m)
+    # traction on side 6 (top face) of every top-layer element: total force = traction * area of the top
+    top = [e + 1 for e in range(m.nels) if np.allclose(m.coords[m.elem_nodes(e)[4:] - 1, 2], m.coords[:, 2].max())]
+    telsd = [[e, 6] for e in top]
+    tval = [[0.0, 0.0, -7.0, 0.0, 1.0]] * len(top)
+    f = orc.form_rhs(om, [], [], telsd, tval, 0.0, 1.0, 1.0).reshape(-1, 3)
+    area = np.ptp(m.coords[:, 0]) * np.ptp(m.coords[:, 1])
+    assert abs(f[:, 2].sum() + 7.0 * area) <= 1e-12 * 7.0 * area and np.abs(f[:, :2]).max() == 0.0
