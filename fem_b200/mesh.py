@@ -44,6 +44,8 @@ class Mesh:
     bcval: np.ndarray          # [nbcs, pdim]
     fnode: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros(0, np.int32))
     fval: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros((0, 0)))
+    telsd: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros((0, 2), np.int32))   # [ntrcs, 2] element (1-based), side
+    tval: np.ndarray = dataclasses.field(default_factory=lambda: np.zeros((0, 0)))              # [ntrcs, pdim+2] components, t1, t2
     t: float = 1.0
     dt: float = 1.0
     nodal_bw: int = 10
@@ -166,10 +168,16 @@ def read_inp(path_or_text: str) -> Mesh:
         toks = r.read(1 + pdim + 2)
         fnode[i] = int(toks[0])
         fval[i] = [_f(x) for x in toks[1:]]
+    telsd = np.zeros((ntrcs, 2), np.int32)               # ReadDistTractions, src/m_io.F90:436-439
+    tval = np.zeros((ntrcs, pdim + 2))
+    for i in range(ntrcs):
+        toks = r.read(2 + pdim + 2)
+        telsd[i] = [int(toks[0]), int(toks[1])]
+        tval[i] = [_f(x) for x in toks[2:]]
     return Mesh(pdim=pdim, etype=np.array(etype), eptr=np.array(eptr), eind=np.array(eind),
                 emat=np.array(emat), enlmat=np.array(enl), coords=coords,
                 nl2g=np.arange(1, nnds + 1), nnds=nnds, mat=mat, cohprops=coh, bcnode=bcnode,
-                bcval=bcval, fnode=fnode, fval=fval, t=t, dt=dt, nodal_bw=nodal_bw,
+                bcval=bcval, fnode=fnode, fval=fval, telsd=telsd, tval=tval, t=t, dt=dt, nodal_bw=nodal_bw,
                 stype=stype.strip("'\"")).normalized()
 
 
@@ -178,7 +186,7 @@ def write_inp(m: Mesh, path: str) -> None:
     assert np.array_equal(m.nl2g, np.arange(1, m.nnds + 1)), "write_inp wants a global mesh"
     with open(path, "w") as fh:
         fh.write(f"{m.stype} {m.pdim} {m.nodal_bw}\n")
-        fh.write(f"{m.nels} {m.nnds} {len(m.mat)} {len(m.cohprops)} 0 {len(m.fnode)} 0 {len(m.bcnode)}\n")
+        fh.write(f"{m.nels} {m.nnds} {len(m.mat)} {len(m.cohprops)} 0 {len(m.fnode)} {len(m.telsd)} {len(m.bcnode)}\n")
         fh.write(f"{m.t!r} {m.dt!r}\n")
         for e in range(m.nels):
             nodes = " ".join(str(int(x)) for x in m.elem_nodes(e))
@@ -194,6 +202,69 @@ def write_inp(m: Mesh, path: str) -> None:
                      " ".join(repr(float(v)) for v in m.bcval[i]) + "\n")
         for i in range(len(m.fnode)):
             fh.write(f"{int(m.fnode[i])} " + " ".join(repr(float(v)) for v in m.fval[i]) + "\n")
+        for i in range(len(m.telsd)):
+            fh.write(f"{int(m.telsd[i][0])} {int(m.telsd[i][1])} " + " ".join(repr(float(v)) for v in m.tval[i]) + "\n")
+
+
+# --------------------------------------------------------------------------- VTK writer
+VTK_ID = {TRI: 5, QUA: 9, TET: 10, HEX: 12, COH: 9}     # getVtkid, src/m_elems.F90:108-120
+
+
+def fortran_f0(v: float, d: int) -> str:
+    """Fortran `F0.d` edit descriptor as gfortran prints it: minimal width, no leading zero for |v| < 1
+    (`.050000`, `-.000000`), sign kept for negative zero and for negatives that round to zero."""
+    t = f"{float(v):.{d}f}"
+    if t.startswith("0."):
+        return t[1:]
+    if t.startswith("-0."):
+        return "-" + t[2:]
+    return t
+
+
+def write_vtk(m: Mesh, stress_node: np.ndarray, u_local: np.ndarray, path: Optional[str] = None) -> str:
+    """WriteOutput (src/m_io.F90:480-555): legacy ASCII VTK of one rank -- local points (F0.3, z = 0 appended in
+    2-D), cells with 0-based local node ids, nodal STRESS (cpdim components, F0.6) and displacement vectors
+    (F0.6).  Byte-for-byte what the reference writes (tests/test_host_cpu.py checks the golden files); compare
+    ARRAYS for the 1e-10 field tolerance, the text carries six decimals.  Returns the text; writes it if `path`."""
+    pd, n = m.pdim, m.nlnds
+    s = np.asarray(stress_node, float).reshape(n, m.cpdim)
+    u = np.asarray(u_local, float).reshape(n, pd)
+    pad = [0.0] if pd == 2 else []
+    out = ["# vtk DataFile Version 2.0", "File written by Defmod", "ASCII", "DATASET UNSTRUCTURED_GRID", f"POINTS {n} double"]
+    out += [" ".join(fortran_f0(v, 3) for v in list(x) + pad) for x in m.coords]
+    out.append(f"CELLS {m.nels} {int(m.eptr[-1]) + m.nels}")
+    for e in range(m.nels):
+        nd = m.elem_nodes(e)
+        out.append(" ".join(str(int(v)) for v in [len(nd)] + list(nd - 1)))
+    out.append(f"CELL_TYPES {m.nels}")
+    out += [str(VTK_ID[int(t)]) for t in m.etype]
+    out += [f"POINT_DATA {n}", f"SCALARS STRESS FLOAT {m.cpdim}", "LOOKUP_TABLE DEFAULT"]
+    out += [" ".join(fortran_f0(v, 6) for v in row) for row in s]
+    out.append("VECTORS displacements double")
+    out += [" ".join(fortran_f0(v, 6) for v in list(row) + pad) for row in u]
+    text = "\n".join(out) + "\n"
+    if path:
+        with open(path, "w") as fh:
+            fh.write(text)
+    return text
+
+
+def read_vtk(text: str):
+    """Parse a WriteOutput file back: (coords[n, 3], cells list of 0-based node lists, cell types, stress[n, cp], disp[n, 3])."""
+    tok = text.split("\n")
+    i = next(k for k, l in enumerate(tok) if l.startswith("POINTS"))
+    n = int(tok[i].split()[1])
+    pts = np.array([[float(v) for v in tok[i + 1 + k].split()] for k in range(n)])
+    i = next(k for k, l in enumerate(tok) if l.startswith("CELLS"))
+    ne = int(tok[i].split()[1])
+    cells = [[int(v) for v in tok[i + 1 + k].split()[1:]] for k in range(ne)]
+    i = next(k for k, l in enumerate(tok) if l.startswith("CELL_TYPES"))
+    types = [int(tok[i + 1 + k]) for k in range(ne)]
+    i = next(k for k, l in enumerate(tok) if l.startswith("LOOKUP_TABLE"))
+    stress = np.array([[float(v) for v in tok[i + 1 + k].split()] for k in range(n)])
+    i = next(k for k, l in enumerate(tok) if l.startswith("VECTORS"))
+    disp = np.array([[float(v) for v in tok[i + 1 + k].split()] for k in range(n)])
+    return pts, cells, types, stress, disp
 
 
 # --------------------------------------------------------------------------- distribution
@@ -211,10 +282,28 @@ def localize(g: Mesh, epart: np.ndarray, rank: int) -> Mesh:
     nl2g = np.unique(gnodes)                      # ascending global ids -> local 1..nlnds
     work = np.zeros(g.nnds + 1, np.int32)
     work[nl2g] = np.arange(1, len(nl2g) + 1)
+    fnode, fval, telsd, tval = distribute_loads(g, epart, int(epart.max()) + 1, rank)
     return dataclasses.replace(
         g, etype=g.etype[sel], eptr=eptr.astype(np.int32), eind=work[gnodes], emat=g.emat[sel],
         enlmat=g.enlmat[sel], coords=g.coords[nl2g - 1], nl2g=nl2g.astype(np.int32),
-        eglobal=sel.astype(np.int64)).normalized()
+        eglobal=sel.astype(np.int64), fnode=fnode, fval=fval, telsd=telsd, tval=tval).normalized()
+
+
+def distribute_loads(g: Mesh, epart: np.ndarray, nprcs: int, rank: int):
+    """What ReadDistForces / ReadDistTractions leave on `rank` (src/m_io.F90:330-372, :414-475): nodal forces dealt
+    round-robin (item i goes to rank i mod nprcs, GLOBAL node ids kept), tractions follow their element's partition
+    with the element id renumbered to the rank-local one (emap).  Returns fnode, fval, telsd, tval for femx_set_loads."""
+    epart = np.asarray(epart)
+    fnode, fval = g.fnode[rank::nprcs], np.asarray(g.fval)[rank::nprcs]
+    telsd, tval = np.asarray(g.telsd).reshape(-1, 2), np.asarray(g.tval)
+    emap = np.zeros(len(epart) + 1, np.int32)
+    mine = np.flatnonzero(epart == rank)
+    emap[mine + 1] = np.arange(1, len(mine) + 1)
+    keep = epart[telsd[:, 0] - 1] == rank if len(telsd) else np.zeros(0, bool)
+    loc = telsd[keep].copy()
+    if len(loc):
+        loc[:, 0] = emap[loc[:, 0]]
+    return fnode, fval, loc, tval[keep] if len(telsd) else tval
 
 
 def petsc_ownership(n: int, nranks: int, rank: int):

@@ -73,6 +73,9 @@ def main():
         "jacobian_matview_cohesive_test_2": matview(f"{REF}/tmp.txt"),
         "elastic_vtk_rank0": vtk_fields(f"{REF}/SNES_test/elastic/0_output_000000.vtk"),
         "elastic_vtk_rank1": vtk_fields(f"{REF}/SNES_test/elastic/1_output_000000.vtk"),
+        # raw text of the same two files: the byte-for-byte target of fem_b200.mesh.write_vtk (WriteOutput, src/m_io.F90:480-555)
+        "elastic_vtk_rank0_text": open(f"{REF}/SNES_test/elastic/0_output_000000.vtk").read(),
+        "elastic_vtk_rank1_text": open(f"{REF}/SNES_test/elastic/1_output_000000.vtk").read(),
         "uel_ip_forces": uel_forces(f"{REF}/CZM_for_instability_test.log"),
         "decks": {n: open(f"{REF}/{n}.inp").read()
                   for n in ("lin_two_quads_qs", "cohesive_test_2", "two_quads_qs")},
