@@ -206,7 +206,7 @@ int femx_build_plan(femx_ctx *c) {
   for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
   UP(dm.lam_mu, lm);
   UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
-  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent);
+  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent);
   UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
   // stress multiplicity (count_node, src/main.F90:263); mesh constant, computed once
   std::vector<int32_t> cnt(c->nlnds, 0);
@@ -231,7 +231,7 @@ int femx_build_plan(femx_ctx *c) {
   if ((rc = dev_alloc(c, &c->d_coh_fe, 8 * (int64_t)P.coh_elems.size()))) return rc;
   // fused hex8 path (variant 2): only if the mesh provably is a logical grid of hex8
   c->hex = femx::HexPlan();
-  if (c->opts.assembly_variant != 1 && c->opts.assembly_variant != 9) {
+  if (c->opts.assembly_variant != 1 && c->opts.assembly_variant != 9 && c->opts.assembly_variant != 11) {
     build_hex_plan(P, c->etype.data(), c->eptr.data(), c->emat.data(), c->E_nu.data(), c->nmts, &c->hex, &c->hex.why);
     if (c->hex.ok) {
       femx::DevHex &hx = c->dhex;

@@ -50,15 +50,17 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
   // auto (0): the 16-warp symmetric tile kernel for a logical hex8 grid, else the fused rows kernel, else two-pass
   const int av0 = c->opts.assembly_variant;
-  const bool fused = c->hex.ok && av0 != 1 && av0 != 9;
-  const bool rows = !fused && av0 != 1 && rows_fused_ok(c);
+  const bool fused = c->hex.ok && av0 != 1 && av0 != 9 && av0 != 11;
+  const bool simplex = !fused && av0 != 1 && av0 != 9 && rows_simplex_ok(c);   // pure tri3 / tet4 mesh
+  const bool rows = !fused && !simplex && av0 != 1 && rows_fused_ok(c);
   if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
+  if (av0 == 11 && !simplex) { c->err = "simplex rows kernel: needs a pure tri3 / tet4 mesh with at most 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
   const bool peer = c->peer.connected;
   // peer exchange: reserved[3] = 1 lets the assembly kernel store interface rows at their owner itself (variants 0, 5, 9);
   // default is the push kernel behind the unchanged assembly kernel
-  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5) : rows);
+  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5) : (rows || simplex));
   c->peer.in_kernel = peer_fused;
-  if (!fused && !rows) {
+  if (!fused && !rows && !simplex) {
     if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
     if (fint && (rc = ensure(c, &c->d_fe, c->plan.fe_off[c->nels]))) return rc;
   }
@@ -70,6 +72,8 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
                    : av == 6 ? launch_hex_sym3(c, d_u, d_vals, d_fint) : av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint)
                    : av == 4 ? launch_hex_sym5(c, d_u, d_vals, d_fint)   /* the first 8-warp kernel lives on as variant 8 */
                    : (av == 3 ? launch_hex_ws(c, d_u, d_vals, d_fint) : launch_hex_fused(c, d_u, d_vals, d_fint));
+  } else if (simplex) {
+    c->launches += launch_rows_simplex(c, d_u, d_vals, d_fint);
   } else if (rows) {
     c->launches += launch_rows_fused(c, d_u, d_vals, d_fint);
   } else {

@@ -45,6 +45,8 @@ struct Plan {
   std::vector<int64_t> rbe_ptr;    // [nlnds+1] first entry of node r in rb_ent
   std::vector<uint16_t> rb_off;    // node r: nb+1 node-local offsets at [bptr[r] + r ...]
   std::vector<uint16_t> rb_ent;    // shared-memory offset (doubles) of the contributing block: incident index * rb_slot + b * pd^2
+  std::vector<uint16_t> sx_ent;    // simplex rows kernel: (incident index << 4) | (a << 2) | b, same order / offsets as rb_ent
+  bool simplex = false;            // every element is a tri3 / tet4 (one integration point)
   int rb_slot = 0, rb_foff = 0;    // slot pitch per incident element (odd) and offset of its f share inside the slot
   int max_inc = 0;                 // largest number of elements around a node
   // cohesive overlay: blocks / nodes touched by nonlinear elements, contributions ascending
@@ -147,6 +149,7 @@ struct DevMesh {
   int64_t *rbe_ptr = nullptr;
   uint16_t *rb_off = nullptr;
   uint16_t *rb_ent = nullptr;
+  uint16_t *sx_ent = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 

@@ -34,5 +34,7 @@ PeerTab peer_tab(const femx_ctx *c);          // peer.cu
 int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, const double *d_fint);
 bool rows_fused_ok(const femx_ctx *c);
 int launch_rows_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+bool rows_simplex_ok(const femx_ctx *c);     // rows_simplex.cu
+int launch_rows_simplex(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 
 }  // namespace femx

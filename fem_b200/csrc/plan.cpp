@@ -125,6 +125,9 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
     const int slot = P->rb_slot;
     P->rb_off.assign((size_t)P->nblk + nlnds, 0);
     P->rb_ent.assign((size_t)P->rbe_ptr[nlnds], 0);
+    P->simplex = nels > 0;
+    for (int e = 0; e < nels; ++e) P->simplex = P->simplex && (etype[e] == FEMX_TRI || etype[e] == FEMX_TET);
+    P->sx_ent.assign(P->simplex ? (size_t)P->rbe_ptr[nlnds] : 0, 0);
     if (P->max_inc <= 32)
       parallel_for(nlnds, [&](int64_t lo, int64_t hi) {
         std::vector<int32_t> cntk;
@@ -142,7 +145,11 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
           int idx = 0;
           for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p, ++idx) {   // ascending element order
             const int e = P->n2e_elem[p], a = P->n2e_a[p], nen = eptr[e + 1] - eptr[e];
-            for (int b = 0; b < nen; ++b) ent[cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++] = (uint16_t)(idx * slot + b * d2);
+            for (int b = 0; b < nen; ++b) {
+              const int c = cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++;
+              ent[c] = (uint16_t)(idx * slot + b * d2);
+              if (P->simplex) P->sx_ent[P->rbe_ptr[r] + c] = (uint16_t)((idx << 4) | (a << 2) | b);
+            }
           }
         }
       });

@@ -14,7 +14,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from .mesh import COH, HEX, QUA, TET, Mesh, from_uniform
+from .mesh import TRI, COH, HEX, QUA, TET, Mesh, from_uniform
 
 _M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
 
@@ -124,6 +124,17 @@ def quad_rect(nx: int, ny: int, E=3.0e10, nu=0.25) -> Mesh:
     yy, xx = np.meshgrid(np.arange(ny + 1.0), np.arange(nx + 1.0), indexing="ij")
     coords = np.stack([xx.reshape(-1), yy.reshape(-1)], axis=1)
     return from_uniform(2, QUA, conn, coords, E=E, nu=nu, nodal_bw=8)
+
+
+def tri_rect(nx: int, ny: int, E=3.0e10, nu=0.25) -> Mesh:
+    """nx x ny unit cells cut into two tri3 each (alternating diagonals, so nodes see 4 to 8 triangles)."""
+    q = quad_rect(nx, ny, E=E, nu=nu)
+    c = q.eind.reshape(-1, 4)
+    flip = ((np.arange(len(c)) % nx + np.arange(len(c)) // nx) % 2).astype(bool)
+    t1 = np.where(flip[:, None], c[:, [0, 1, 3]], c[:, [0, 1, 2]])
+    t2 = np.where(flip[:, None], c[:, [1, 2, 3]], c[:, [0, 2, 3]])
+    conn = np.stack([t1, t2], axis=1).reshape(-1, 3)
+    return from_uniform(2, TRI, conn, q.coords, E=E, nu=nu, nodal_bw=8)
 
 
 def cohesive_strip(nx: int, ny: int, E=3640.0, nu=0.3, props=(100.0, 0.01, 0.01, 1.0, 0.0, 0.0),

@@ -88,6 +88,7 @@ def _meshes(golden):
     yield "hex_rect", mg.hex_cube(5)
     yield "tet4_jitter", mg.jitter(mg.tet_cube(4))
     yield "quad_jitter", mg.jitter(mg.quad_rect(9, 7))
+    yield "tri_jitter", mg.jitter(mg.tri_rect(9, 7))
     yield "coh_strip", mg.jitter(mg.cohesive_strip(12, 3))
     # a rank-local mesh: ragged node set, nl2g not the identity
     g = mg.jitter(mg.hex_cube(5))
@@ -130,14 +131,25 @@ def test_pattern_values_fint_vs_oracle(fx, orc, golden):
 def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
     """Variant 9 (fused rows kernel: element row blocks stay in shared memory) against variant 1 (two-pass through
     the packed Ke scratch) and the oracle, on every element mix incl. cohesive zeros and an unstructured hex mesh."""
-    cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("tet_jitter", mg.jitter(mg.tet_cube(5)))]
+    cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("tet_jitter", mg.jitter(mg.tet_cube(5))),
+                                     ("tri_wide", mg.jitter(mg.tri_rect(40, 3))), ("tet_rank1of2", None)]
     for name, m in cases:
+        if m is None:                                   # rank-local tet mesh: ragged node set, nl2g not the identity
+            g = mg.jitter(mg.tet_cube(5))
+            m = fm.localize(g, mg.slab_partition(g, 2), 1)
+            m = dataclasses.replace(m, bcnode=m.bcnode[:0], bcval=m.bcval[:0])
         u = mg.displacement_field(m)
         om = orc.Mesh(m)
         _, _, va_o = orc.assemble_K(om).export(om.ndof)
         f_o = orc.fint(om, u.reshape(-1))
         res = {}
-        for var in (9, 1):
+        simplex = bool(np.all((m.etype == fm.TRI) | (m.etype == fm.TET)))
+        if not simplex:                                 # variant 11 (simplex rows kernel) must refuse other meshes
+            with api.Femx(assembly_variant=11) as f:
+                f.set_mesh(m).build_plan()
+                with pytest.raises(api.FemxError):
+                    f.assemble_K()
+        for var in (9, 1) + ((11,) if simplex else ()):
             with api.Femx(assembly_variant=var) as f:
                 f.set_mesh(m).build_plan()
                 vals, fint = f.assemble_K_fint(u)
@@ -146,6 +158,8 @@ def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
                 assert np.array_equal(f.assemble_K(), vals), (name, var)
                 res[var] = vals
         assert close(res[9], res[1], TOL_MAT), name      # same summation order except the split diagonal block
+        if simplex:
+            assert close(res[11], res[1], TOL_MAT), name
 
 
 def test_golden_matview_through_cuda(golden):
