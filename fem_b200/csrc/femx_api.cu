@@ -196,6 +196,7 @@ int femx_build_plan(femx_ctx *c) {
     if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
   }
   femx::Plan &P = c->plan;
+  for (size_t p = 0; p < P.sx_mat.size(); ++p) P.sx_mat[p] = c->emat[P.n2e_elem[p]] - 1;
   femx::DevMesh &dm = c->dm;
   dm.pdim = c->pdim; dm.nels = c->nels; dm.nlnds = c->nlnds; dm.nnds = c->nnds; dm.cp = c->pdim == 2 ? 3 : 6;
   c->nnz = (int64_t)c->pdim * c->pdim * P.nblk;
@@ -206,7 +207,7 @@ int femx_build_plan(femx_ctx *c) {
   for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
   UP(dm.lam_mu, lm);
   UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
-  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent);
+  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent); UP(dm.sx_inc, P.sx_inc); UP(dm.sx_mat, P.sx_mat);
   UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
   // stress multiplicity (count_node, src/main.F90:263); mesh constant, computed once
   std::vector<int32_t> cnt(c->nlnds, 0);

@@ -46,6 +46,8 @@ struct Plan {
   std::vector<uint16_t> rb_off;    // node r: nb+1 node-local offsets at [bptr[r] + r ...]
   std::vector<uint16_t> rb_ent;    // shared-memory offset (doubles) of the contributing block: incident index * rb_slot + b * pd^2
   std::vector<uint16_t> sx_ent;    // simplex rows kernel: (incident index << 4) | (a << 2) | b, same order / offsets as rb_ent
+  std::vector<int32_t> sx_inc;     // simplex rows kernel: per (node, incident element) the element's 0-based nodes, padded to 4
+  std::vector<int32_t> sx_mat;     // ... and its 0-based material row
   bool simplex = false;            // every element is a tri3 / tet4 (one integration point)
   int rb_slot = 0, rb_foff = 0;    // slot pitch per incident element (odd) and offset of its f share inside the slot
   int max_inc = 0;                 // largest number of elements around a node
@@ -150,6 +152,7 @@ struct DevMesh {
   uint16_t *rb_off = nullptr;
   uint16_t *rb_ent = nullptr;
   uint16_t *sx_ent = nullptr;
+  int32_t *sx_inc = nullptr, *sx_mat = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 

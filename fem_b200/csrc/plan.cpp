@@ -128,6 +128,8 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
     P->simplex = nels > 0;
     for (int e = 0; e < nels; ++e) P->simplex = P->simplex && (etype[e] == FEMX_TRI || etype[e] == FEMX_TET);
     P->sx_ent.assign(P->simplex ? (size_t)P->rbe_ptr[nlnds] : 0, 0);
+    P->sx_inc.assign(P->simplex ? 4 * (size_t)P->n2e_ptr[nlnds] : 0, 0);
+    P->sx_mat.assign(P->simplex ? (size_t)P->n2e_ptr[nlnds] : 0, 0);
     if (P->max_inc <= 32)
       parallel_for(nlnds, [&](int64_t lo, int64_t hi) {
         std::vector<int32_t> cntk;
@@ -145,6 +147,9 @@ int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int 
           int idx = 0;
           for (int64_t p = P->n2e_ptr[r]; p < P->n2e_ptr[r + 1]; ++p, ++idx) {   // ascending element order
             const int e = P->n2e_elem[p], a = P->n2e_a[p], nen = eptr[e + 1] - eptr[e];
+            if (P->simplex) {   // flattened incidence record: no element -> connectivity -> node chain on the device
+              for (int b = 0; b < nen; ++b) P->sx_inc[4 * p + b] = P->conn0[eptr[e] + b];
+            }
             for (int b = 0; b < nen; ++b) {
               const int c = cntk[P->bpos[P->eb_ptr[e] + a * nen + b]]++;
               ent[c] = (uint16_t)(idx * slot + b * d2);

@@ -25,7 +25,7 @@ constexpr int kWarps = 8;
 constexpr int kChunks = 4;   // the diagonal block is summed by up to this many lanes
 
 template <int PD, int G, bool PEER>
-__global__ void __launch_bounds__(kWarps * 32)
+__global__ void __launch_bounds__(kWarps * 32, 3)
 rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, const PeerTab pt) {
   constexpr int T = PD == 2 ? FEMX_TRI : FEMX_TET;
   constexpr int NEN = PD + 1, D2 = PD * PD, NPW = 32 / G;
@@ -40,34 +40,57 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
   double *dpart = sm_diag + ((size_t)w * NPW + gi) * DPART;
   const int64_t ngroups = ((int64_t)dm.nlnds + NPW - 1) / NPW;
   const int64_t stride = (int64_t)gridDim.x * kWarps;
-  for (int64_t wg = (int64_t)blockIdx.x * kWarps + w; wg < ngroups; wg += stride) {
+  // row metadata of the NEXT group is fetched while the current one is processed (one level of the dependent-load
+  // chain off the critical path); the incidence records hold the element's nodes directly (plan: sx_inc)
+  struct Meta { int64_t p0, b0; int ninc, nb, kd; };
+  auto fetch = [&](int64_t g) {
+    Meta m{0, 0, 0, 0, 0};
+    const int64_t r = g * NPW + gi;
+    if (g < ngroups && r < dm.nlnds) {
+      m.p0 = dm.n2e_ptr[r]; m.ninc = (int)(dm.n2e_ptr[r + 1] - m.p0);
+      m.b0 = dm.bptr[r]; m.nb = (int)(dm.bptr[r + 1] - m.b0);
+      m.kd = dm.bdiag[r];
+    }
+    return m;
+  };
+  int64_t wg = (int64_t)blockIdx.x * kWarps + w;
+  Meta nxt = fetch(wg);
+  for (; wg < ngroups; wg += stride) {
     const int64_t r = wg * NPW + gi;
     const bool node_on = r < dm.nlnds;
-    int ninc = 0;
+    const Meta cur = nxt;
+    const int ninc = cur.ninc;
     // ---- phase A: gradients of one incident element per lane
+    int4 nd4 = make_int4(0, 0, 0, 0);
+    int mat = 0;
+    if (gl < ninc) {
+      nd4 = *reinterpret_cast<const int4 *>(dm.sx_inc + 4 * (cur.p0 + gl));
+      mat = dm.sx_mat[cur.p0 + gl];
+    }
+    // first task of the lane in phase B: its list bounds travel together with the incidence record
+    const uint16_t *off = dm.rb_off + cur.b0 + r;
+    int t_off0 = 0, t_off1 = 0, d_off0 = 0, d_off1 = 0;
     if (node_on) {
-      const int64_t p0 = dm.n2e_ptr[r];
-      ninc = (int)(dm.n2e_ptr[r + 1] - p0);
-      if (gl < ninc) {
-        const int e = dm.n2e_elem[p0 + gl];
-        const int32_t *cn = dm.conn0 + dm.eptr[e];
-        double X[NEN][PD];
+      if (gl < cur.nb) { t_off0 = off[gl]; t_off1 = off[gl + 1]; }
+      d_off0 = off[cur.kd]; d_off1 = off[cur.kd + 1];
+    }
+    nxt = fetch(wg + stride);
+    if (gl < ninc) {
+      const int nds[4] = {nd4.x, nd4.y, nd4.z, nd4.w};
+      double X[NEN][PD];
 #pragma unroll
-        for (int b = 0; b < NEN; ++b) {
-          const int nd = cn[b];
+      for (int b = 0; b < NEN; ++b)
 #pragma unroll
-          for (int d = 0; d < PD; ++d) X[b][d] = dm.coords[(int64_t)nd * PD + d];
-        }
-        double g[NEN][PD];
-        const double wd = phys_grad<T>(X, 0, g);
-        const int m = dm.emat[e] - 1;
+        for (int d = 0; d < PD; ++d) X[b][d] = dm.coords[(int64_t)nds[b] * PD + d];
+      const double lam = dm.lam_mu[2 * mat], mu = dm.lam_mu[2 * mat + 1];
+      double g[NEN][PD];
+      const double wd = phys_grad<T>(X, 0, g);
 #pragma unroll
-        for (int b = 0; b < NEN; ++b)
+      for (int b = 0; b < NEN; ++b)
 #pragma unroll
-          for (int d = 0; d < PD; ++d) mine[b * PD + d] = g[b][d];
-        mine[NEN * PD] = wd * dm.lam_mu[2 * m];
-        mine[NEN * PD + 1] = wd * dm.lam_mu[2 * m + 1];
-      }
+        for (int d = 0; d < PD; ++d) mine[b * PD + d] = g[b][d];
+      mine[NEN * PD] = wd * lam;
+      mine[NEN * PD + 1] = wd * mu;
     }
     __syncwarp();
     // ---- phase B: one block (or one chunk of the diagonal block) per lane
@@ -76,16 +99,15 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
     for (int i = 0; i < PD; ++i) fpart[i] = 0.0;
     int nchunk = 1;
     if (node_on) {
-      const int64_t b0 = dm.bptr[r];
-      const int nb = (int)(dm.bptr[r + 1] - b0);
+      const int64_t b0 = cur.b0;
+      const int nb = cur.nb;
       const int rowlen = PD * nb;
-      const uint16_t *off = dm.rb_off + b0 + r;
-      const uint16_t *ent = dm.sx_ent + dm.rbe_ptr[r];
-      const int kd = dm.bdiag[r];
+      const uint16_t *ent = dm.sx_ent + NEN * cur.p0;   // every element lists NEN contributions: rbe_ptr = NEN * n2e_ptr
+      const int kd = cur.kd;
       // diagonal chunks: as many as there are idle lanes in the last pass over the blocks, at most kChunks
       const int spare = (G - nb % G) % G;
       nchunk = min(kChunks, 1 + spare);
-      const int dlo = off[kd], dn = off[kd + 1] - dlo, clen = (dn + nchunk - 1) / nchunk;
+      const int dlo = d_off0, dn = d_off1 - dlo, clen = (dn + nchunk - 1) / nchunk;
       double *prow[PD];
 #pragma unroll
       for (int i = 0; i < PD; ++i) prow[i] = vals + (D2 * b0 + (int64_t)i * rowlen);
@@ -98,13 +120,14 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
       for (int t = gl; t < nb + nchunk - 1; t += G) {
         // task t: block t, or chunk (t - nb + 1) of the diagonal block
         const int k = t < nb ? t : kd;
-        int c0 = off[k], c1 = off[k + 1], chunk = -1;
+        int c0, c1, chunk = -1;
+        if (t == gl) { c0 = t_off0; c1 = t_off1; } else { c0 = off[k]; c1 = off[k + 1]; }
         if (k == kd) {
           chunk = t < nb ? 0 : t - nb + 1;
           c0 = dlo + chunk * clen;
           c1 = min(dlo + dn, c0 + clen);
         }
-        double acc[D2];
+        double acc[D2], tr = 0.0;
 #pragma unroll
         for (int q = 0; q < D2; ++q) acc[q] = 0.0;
         for (int c = c0; c < c1; ++c) {
@@ -112,20 +135,18 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
           const double *sl = grp + (en >> 4) * SLOT;
           const double *ga = sl + ((en >> 2) & 3) * PD, *gb = sl + (en & 3) * PD;
           const double cl = sl[NEN * PD], cm = sl[NEN * PD + 1];
-          double la[PD], ma[PD], vb[PD], dot = 0.0;
+          double la[PD], ma[PD], vb[PD];
 #pragma unroll
           for (int i = 0; i < PD; ++i) { const double a = ga[i]; la[i] = cl * a; ma[i] = cm * a; vb[i] = gb[i]; }
 #pragma unroll
-          for (int i = 0; i < PD; ++i) dot += ma[i] * vb[i];
+          for (int i = 0; i < PD; ++i) tr = fma(ma[i], vb[i], tr);
 #pragma unroll
           for (int i = 0; i < PD; ++i)
 #pragma unroll
-            for (int j = 0; j < PD; ++j) {
-              double v = la[i] * vb[j] + ma[j] * vb[i];
-              if (i == j) v += dot;
-              acc[i * PD + j] += v;
-            }
+            for (int j = 0; j < PD; ++j) acc[i * PD + j] = fma(ma[j], vb[i], fma(la[i], vb[j], acc[i * PD + j]));
         }
+#pragma unroll
+        for (int i = 0; i < PD; ++i) acc[i * PD + i] += tr;   // delta_ij mu g_a . g_b, summed over the contributions
         if (fint) {   // this block's (or chunk's) share of f_r = sum_k K_rk u_k
           const int64_t col = dm.bcol[b0 + k];
 #pragma unroll
@@ -148,8 +169,8 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
     }
     __syncwarp();
     if (node_on && nchunk > 1) {   // diagonal block = its chunks in order, one entry per lane
-      const int64_t b0 = dm.bptr[r];
-      const int nb = (int)(dm.bptr[r + 1] - b0), kd = dm.bdiag[r];
+      const int64_t b0 = cur.b0;
+      const int nb = cur.nb, kd = cur.kd;
       for (int q = gl; q < D2; q += G) {
         const int i = q / PD, j = q % PD;
         double s = dpart[q];

@@ -51,7 +51,7 @@ def main():
         d_f = fx.device_buffer(8 * fx.nrows)
         d_s = fx.device_buffer(8 * 6 * m.nlnds)
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_vals.ptr, d_f.ptr, api.DEVICE)), args.reps)
-        line(f"C3 tet4 {args.tet}^3x6", "K + f_int (auto = variant 9, fused rows kernel)", m.nels, ms, best, 215.0,
+        line(f"C3 tet4 {args.tet}^3x6", "K + f_int (auto = variant 11, simplex rows kernel)", m.nels, ms, best, 215.0,
              {"nnz": int(fx.nnz), "plan_build_s": round(plan_s, 2)})
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_stress(fx.h, d_u.ptr, d_s.ptr, api.ROW_MAJOR, api.DEVICE)), args.reps)
         line(f"C3 tet4 {args.tet}^3x6", "nodal-averaged stress", m.nels, ms, best, 36.5)
