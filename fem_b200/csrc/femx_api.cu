@@ -196,6 +196,25 @@ int femx_build_plan(femx_ctx *c) {
     if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
   }
   femx::Plan &P = c->plan;
+  if (P.simplex) {   // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians and mu > 0
+    const int pd = c->pdim;
+    for (int m = 0; m < c->nmts && P.simplex; ++m) {
+      double lam, mu;
+      lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lam, &mu);
+      if (!(mu > 0.0) || !std::isfinite(lam / mu)) P.simplex = false;
+    }
+    for (int e = 0; e < c->nels && P.simplex; ++e) {
+      const int *nd = &c->eind[c->eptr[e]];
+      double d[3][3];
+      for (int b = 1; b <= pd; ++b)
+        for (int k = 0; k < pd; ++k) d[b - 1][k] = c->coords[(size_t)(nd[b] - 1) * pd + k] - c->coords[(size_t)(nd[0] - 1) * pd + k];
+      const double det = pd == 2 ? d[0][0] * d[1][1] - d[0][1] * d[1][0]
+                                 : d[0][0] * (d[1][1] * d[2][2] - d[1][2] * d[2][1]) - d[0][1] * (d[1][0] * d[2][2] - d[1][2] * d[2][0]) +
+                                       d[0][2] * (d[1][0] * d[2][1] - d[1][1] * d[2][0]);
+      if (!(det > 0.0)) P.simplex = false;
+    }
+    if (!P.simplex) { P.sx_ent.clear(); P.sx_inc.clear(); P.sx_mat.clear(); }
+  }
   for (size_t p = 0; p < P.sx_mat.size(); ++p) P.sx_mat[p] = c->emat[P.n2e_elem[p]] - 1;
   femx::DevMesh &dm = c->dm;
   dm.pdim = c->pdim; dm.nels = c->nels; dm.nlnds = c->nlnds; dm.nnds = c->nnds; dm.cp = c->pdim == 2 ? 3 : 6;

@@ -6,7 +6,9 @@
 // so instead of parking the 4 x 9 values of a row block per (node, incident element) in shared memory (39 doubles) and
 // reading every one of them back once per CSR value, the incident lanes park the GRADIENTS (12 doubles + 2
 // coefficients) and the CSR blocks are formed where they are summed:
-//   phase A  lane i of the node's group: gradients of incident element i -> shared memory slot (15 doubles, odd pitch);
+//   phase A  the lanes of the node's group: gradients of the incident elements, scaled by sqrt(w detJ mu), and
+//            rho = lambda / mu -> one shared-memory slot per element (K_ab = rho s_a s_b^T + s_b s_a^T + (s_a . s_b) I;
+//            the plan admits a mesh to this kernel only if every element has detJ > 0 and mu > 0);
 //   phase B  lane k: block k of the node's row = sum over the contributing (element, a, b) of the plan's list, in
 //            ascending element order (MatSetValues ADD semantics, src/main.F90:157-171, without atomics); the diagonal
 //            block (one contribution per incident element) is cut into chunks taken by otherwise idle lanes and
@@ -14,6 +16,8 @@
 //            butterfly-sums the internal force.
 // Per contribution: 8 shared loads + ~30 FP64 operations for 9 matrix entries (rows_fused.cu: 9 loads + 9 index
 // loads + 9 adds), no per-value index arithmetic.
+#include <cstdio>
+
 #include "elem_math.cuh"
 #include "launch.h"
 
@@ -21,25 +25,31 @@ namespace femx {
 
 namespace {
 
-constexpr int kWarps = 8;
-constexpr int kChunks = 4;   // the diagonal block is summed by up to this many lanes
+constexpr int kChunks = 4;   // the diagonal block is cut into up to this many tasks
+constexpr int kChunkLen = 6; // ... of about this many contributions (the typical length of an off-diagonal list)
 
-template <int PD, int G, bool PEER>
-__global__ void __launch_bounds__(kWarps * 32, 3)
-rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, const PeerTab pt) {
+template <int PD, int G, int WARPS, bool PEER>
+__global__ void __launch_bounds__(WARPS * 32)
+rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int mslots,
+                    const PeerTab pt) {
   constexpr int T = PD == 2 ? FEMX_TRI : FEMX_TET;
   constexpr int NEN = PD + 1, D2 = PD * PD, NPW = 32 / G;
-  constexpr int SLOT = (NEN * PD + 2) | 1;          // gradients, w detJ lambda, w detJ mu; odd pitch
+  // slot of one incident element: per node a 16-byte aligned scaled gradient (tet: s0 s1 s2 rho, tri: s0 s1 and rho
+  // in a quad of its own); pitch = odd multiple of 16 bytes so that the lanes' 128-bit stores spread over the banks
+  constexpr int NS = PD == 3 ? 4 : 2;               // doubles per node
+  constexpr int COEF = NEN * NS;                    // tri: offset of rho
+  constexpr int SLOT = PD == 3 ? 18 : 10;
   constexpr int DPART = kChunks * D2;               // diagonal partials of one group
-  __shared__ double sm_slot[kWarps * 32 * SLOT];
-  __shared__ double sm_diag[kWarps * NPW * DPART];
+  extern __shared__ __align__(16) double sm_dyn[];
+  // G lanes own one node row; a warp works on NPW = 32 / G rows at once (independent dependent-load chains in flight);
+  // a group holds mslots = max elements around a node slots, its lanes take the incident elements / the row's tasks
+  // round-robin
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int gl = lane % G, gi = lane / G;
-  double *mine = sm_slot + ((size_t)w * 32 + lane) * SLOT;
-  const double *grp = sm_slot + ((size_t)w * 32 + gi * G) * SLOT;
-  double *dpart = sm_diag + ((size_t)w * NPW + gi) * DPART;
+  double *grp = sm_dyn + ((size_t)(w * NPW + gi) * mslots) * SLOT;
+  double *dpart = sm_dyn + (size_t)WARPS * NPW * mslots * SLOT + ((size_t)w * NPW + gi) * DPART;
   const int64_t ngroups = ((int64_t)dm.nlnds + NPW - 1) / NPW;
-  const int64_t stride = (int64_t)gridDim.x * kWarps;
+  const int64_t stride = (int64_t)gridDim.x * WARPS;
   // row metadata of the NEXT group is fetched while the current one is processed (one level of the dependent-load
   // chain off the critical path); the incidence records hold the element's nodes directly (plan: sx_inc)
   struct Meta { int64_t p0, b0; int ninc, nb, kd; };
@@ -53,29 +63,26 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
     }
     return m;
   };
-  int64_t wg = (int64_t)blockIdx.x * kWarps + w;
+  int64_t wg = (int64_t)blockIdx.x * WARPS + w;
   Meta nxt = fetch(wg);
   for (; wg < ngroups; wg += stride) {
     const int64_t r = wg * NPW + gi;
     const bool node_on = r < dm.nlnds;
     const Meta cur = nxt;
-    const int ninc = cur.ninc;
-    // ---- phase A: gradients of one incident element per lane
-    int4 nd4 = make_int4(0, 0, 0, 0);
-    int mat = 0;
-    if (gl < ninc) {
-      nd4 = *reinterpret_cast<const int4 *>(dm.sx_inc + 4 * (cur.p0 + gl));
-      mat = dm.sx_mat[cur.p0 + gl];
-    }
-    // first task of the lane in phase B: its list bounds travel together with the incidence record
-    const uint16_t *off = dm.rb_off + cur.b0 + r;
-    int t_off0 = 0, t_off1 = 0, d_off0 = 0, d_off1 = 0;
+    const int ninc = cur.ninc, nb = cur.nb, kd = cur.kd;
+    const int64_t b0 = cur.b0;
+    // first task of the lane in phase B: its list bounds and column travel together with the incidence records
+    const uint16_t *off = dm.rb_off + b0 + r;
+    int t_off0 = 0, t_off1 = 0, d_off0 = 0, d_off1 = 0, t_col = 0;
     if (node_on) {
-      if (gl < cur.nb) { t_off0 = off[gl]; t_off1 = off[gl + 1]; }
-      d_off0 = off[cur.kd]; d_off1 = off[cur.kd + 1];
+      if (gl < nb) { t_off0 = off[gl]; t_off1 = off[gl + 1]; t_col = dm.bcol[b0 + gl]; }
+      d_off0 = off[kd]; d_off1 = off[kd + 1];
     }
     nxt = fetch(wg + stride);
-    if (gl < ninc) {
+    // ---- phase A: gradients of the incident elements, one per lane and pass
+    for (int q = gl; q < ninc; q += G) {
+      const int4 nd4 = *reinterpret_cast<const int4 *>(dm.sx_inc + 4 * (cur.p0 + q));
+      const int mat = dm.sx_mat[cur.p0 + q];
       const int nds[4] = {nd4.x, nd4.y, nd4.z, nd4.w};
       double X[NEN][PD];
 #pragma unroll
@@ -85,82 +92,83 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
       const double lam = dm.lam_mu[2 * mat], mu = dm.lam_mu[2 * mat + 1];
       double g[NEN][PD];
       const double wd = phys_grad<T>(X, 0, g);
+      double *mine = grp + q * SLOT;
+      const double sc = sqrt(wd * mu), rho = lam / mu;
 #pragma unroll
-      for (int b = 0; b < NEN; ++b)
-#pragma unroll
-        for (int d = 0; d < PD; ++d) mine[b * PD + d] = g[b][d];
-      mine[NEN * PD] = wd * lam;
-      mine[NEN * PD + 1] = wd * mu;
+      for (int b = 0; b < NEN; ++b) {
+        double2 *qd = reinterpret_cast<double2 *>(mine + b * NS);
+        qd[0] = make_double2(g[b][0] * sc, g[b][1] * sc);
+        if constexpr (PD == 3) qd[1] = make_double2(g[b][2] * sc, rho);
+      }
+      if constexpr (PD == 2) *reinterpret_cast<double2 *>(mine + COEF) = make_double2(rho, 0.0);
     }
     __syncwarp();
-    // ---- phase B: one block (or one chunk of the diagonal block) per lane
+    // ---- phase B: tasks = the row's blocks, the diagonal block cut into chunks; lane gl takes tasks gl, gl + G, ...
     double fpart[PD];
 #pragma unroll
     for (int i = 0; i < PD; ++i) fpart[i] = 0.0;
-    int nchunk = 1;
+    const int dlo = d_off0, dn = d_off1 - d_off0;
+    const int nchunk = max(1, min(kChunks, (dn + kChunkLen - 1) / kChunkLen));
+    const int clen = (dn + nchunk - 1) / nchunk;
     if (node_on) {
-      const int64_t b0 = cur.b0;
-      const int nb = cur.nb;
       const int rowlen = PD * nb;
       const uint16_t *ent = dm.sx_ent + NEN * cur.p0;   // every element lists NEN contributions: rbe_ptr = NEN * n2e_ptr
-      const int kd = cur.kd;
-      // diagonal chunks: as many as there are idle lanes in the last pass over the blocks, at most kChunks
-      const int spare = (G - nb % G) % G;
-      nchunk = min(kChunks, 1 + spare);
-      const int dlo = d_off0, dn = d_off1 - dlo, clen = (dn + nchunk - 1) / nchunk;
-      double *prow[PD];
-#pragma unroll
-      for (int i = 0; i < PD; ++i) prow[i] = vals + (D2 * b0 + (int64_t)i * rowlen);
-      if constexpr (PEER) {
-        if (!peer_local(pt, D2 * b0, D2 * b0 + (int64_t)PD * rowlen)) {
-#pragma unroll
-          for (int i = 0; i < PD; ++i) prow[i] = peer_row(pt, vals, D2 * b0 + (int64_t)i * rowlen);
-        }
-      }
+      bool remote = false;
+      if constexpr (PEER) remote = !peer_local(pt, D2 * b0, D2 * b0 + (int64_t)PD * rowlen);
       for (int t = gl; t < nb + nchunk - 1; t += G) {
         // task t: block t, or chunk (t - nb + 1) of the diagonal block
         const int k = t < nb ? t : kd;
-        int c0, c1, chunk = -1;
-        if (t == gl) { c0 = t_off0; c1 = t_off1; } else { c0 = off[k]; c1 = off[k + 1]; }
+        int c0, c1, chunk = -1, col;
+        if (t == gl && t < nb) { c0 = t_off0; c1 = t_off1; col = t_col; } else { c0 = off[k]; c1 = off[k + 1]; col = dm.bcol[b0 + k]; }
         if (k == kd) {
           chunk = t < nb ? 0 : t - nb + 1;
           c0 = dlo + chunk * clen;
           c1 = min(dlo + dn, c0 + clen);
         }
+        int en = c0 < c1 ? ent[c0] : 0;
+        double uk[PD];
+        if (fint) {
+#pragma unroll
+          for (int j = 0; j < PD; ++j) uk[j] = u[(int64_t)col * PD + j];
+        }
         double acc[D2], tr = 0.0;
 #pragma unroll
         for (int q = 0; q < D2; ++q) acc[q] = 0.0;
         for (int c = c0; c < c1; ++c) {
-          const int en = ent[c];
+          const int en_next = c + 1 < c1 ? ent[c + 1] : 0;   // the next entry travels while this one is used
           const double *sl = grp + (en >> 4) * SLOT;
-          const double *ga = sl + ((en >> 2) & 3) * PD, *gb = sl + (en & 3) * PD;
-          const double cl = sl[NEN * PD], cm = sl[NEN * PD + 1];
-          double la[PD], ma[PD], vb[PD];
+          const double2 *qa = reinterpret_cast<const double2 *>(sl + ((en >> 2) & 3) * NS);
+          const double2 *qb = reinterpret_cast<const double2 *>(sl + (en & 3) * NS);
+          double ga[PD], vb[PD], la[PD], rho;
+          { const double2 t2 = qa[0], v2 = qb[0]; ga[0] = t2.x; ga[1] = t2.y; vb[0] = v2.x; vb[1] = v2.y; }
+          if constexpr (PD == 3) { const double2 t3 = qa[1]; ga[2] = t3.x; rho = t3.y; vb[2] = qb[1].x; }
+          else rho = sl[COEF];
 #pragma unroll
-          for (int i = 0; i < PD; ++i) { const double a = ga[i]; la[i] = cl * a; ma[i] = cm * a; vb[i] = gb[i]; }
+          for (int i = 0; i < PD; ++i) la[i] = rho * ga[i];
 #pragma unroll
-          for (int i = 0; i < PD; ++i) tr = fma(ma[i], vb[i], tr);
+          for (int i = 0; i < PD; ++i) tr = fma(ga[i], vb[i], tr);
 #pragma unroll
           for (int i = 0; i < PD; ++i)
 #pragma unroll
-            for (int j = 0; j < PD; ++j) acc[i * PD + j] = fma(ma[j], vb[i], fma(la[i], vb[j], acc[i * PD + j]));
+            for (int j = 0; j < PD; ++j) acc[i * PD + j] = fma(ga[j], vb[i], fma(la[i], vb[j], acc[i * PD + j]));
+          en = en_next;
         }
 #pragma unroll
-        for (int i = 0; i < PD; ++i) acc[i * PD + i] += tr;   // delta_ij mu g_a . g_b, summed over the contributions
+        for (int i = 0; i < PD; ++i) acc[i * PD + i] += tr;   // delta_ij s_a . s_b, summed over the contributions
         if (fint) {   // this block's (or chunk's) share of f_r = sum_k K_rk u_k
-          const int64_t col = dm.bcol[b0 + k];
 #pragma unroll
-          for (int j = 0; j < PD; ++j) {
-            const double uj = u[col * PD + j];
+          for (int j = 0; j < PD; ++j)
 #pragma unroll
-            for (int i = 0; i < PD; ++i) fpart[i] += acc[i * PD + j] * uj;
-          }
+            for (int i = 0; i < PD; ++i) fpart[i] = fma(acc[i * PD + j], uk[j], fpart[i]);
         }
         if (chunk < 0 || nchunk == 1) {
 #pragma unroll
-          for (int i = 0; i < PD; ++i)
+          for (int i = 0; i < PD; ++i) {
+            double *row = vals + (D2 * b0 + (int64_t)i * rowlen);
+            if constexpr (PEER) { if (remote) row = peer_row(pt, vals, D2 * b0 + (int64_t)i * rowlen); }
 #pragma unroll
-            for (int j = 0; j < PD; ++j) prow[i][PD * k + j] = acc[i * PD + j];
+            for (int j = 0; j < PD; ++j) row[PD * k + j] = acc[i * PD + j];
+          }
         } else {
 #pragma unroll
           for (int q = 0; q < D2; ++q) dpart[chunk * D2 + q] = acc[q];
@@ -169,8 +177,6 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
     }
     __syncwarp();
     if (node_on && nchunk > 1) {   // diagonal block = its chunks in order, one entry per lane
-      const int64_t b0 = cur.b0;
-      const int nb = cur.nb, kd = cur.kd;
       for (int q = gl; q < D2; q += G) {
         const int i = q / PD, j = q % PD;
         double s = dpart[q];
@@ -200,31 +206,37 @@ rows_simplex_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict
   }
 }
 
-template <int PD, int G>
+template <int PD, int G, int WARPS>
 int launch_g(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+  constexpr int NPW = 32 / G, SLOT = PD == 3 ? 18 : 10, DPART = kChunks * PD * PD;
   const PeerTab pt = c->peer.in_kernel ? peer_tab(c) : PeerTab{};
+  const int mslots = c->plan.max_inc;
+  const size_t smem = sizeof(double) * ((size_t)WARPS * NPW * mslots * SLOT + (size_t)WARPS * NPW * DPART);
   int nsm = 148, per_sm = 1;
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
   auto go = [&](auto kern) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kWarps * 32, 0);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, smem);
     if (per_sm < 1) per_sm = 1;
-    const int64_t ngroups = ((int64_t)c->nlnds + 32 / G - 1) / (32 / G);
-    int64_t grid = (ngroups + kWarps - 1) / kWarps;
+    const int64_t ngroups = ((int64_t)c->nlnds + NPW - 1) / NPW;
+    int64_t grid = (ngroups + WARPS - 1) / WARPS;
     const int64_t cap = (int64_t)nsm * per_sm * 4;
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
-    kern<<<(unsigned)grid, kWarps * 32, 0, c->stream>>>(c->dm, d_u, d_vals, d_fint, pt);
+    if (c->opts.reserved[2] & 32) fprintf(stderr, "femx: simplex rows kernel G %d, %d warps, smem %zu B, %d CTAs per SM, grid %lld\n", G, WARPS, smem, per_sm, (long long)grid);
+    kern<<<(unsigned)grid, WARPS * 32, smem, c->stream>>>(c->dm, d_u, d_vals, d_fint, mslots, pt);
   };
-  if (pt.n > 0) go(rows_simplex_kernel<PD, G, true>); else go(rows_simplex_kernel<PD, G, false>);
+  if (pt.n > 0) go(rows_simplex_kernel<PD, G, WARPS, true>); else go(rows_simplex_kernel<PD, G, WARPS, false>);
   return 1;
 }
 
 template <int PD>
 int launch_pd(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, int g) {
   switch (g) {
-    case 8: return launch_g<PD, 8>(c, d_u, d_vals, d_fint);
-    case 16: return launch_g<PD, 16>(c, d_u, d_vals, d_fint);
-    default: return launch_g<PD, 32>(c, d_u, d_vals, d_fint);
+    case 4: return launch_g<PD, 4, 4>(c, d_u, d_vals, d_fint);
+    case 16: return launch_g<PD, 16, 4>(c, d_u, d_vals, d_fint);
+    case 32: return launch_g<PD, 32, 8>(c, d_u, d_vals, d_fint);
+    default: return launch_g<PD, 8, 4>(c, d_u, d_vals, d_fint);
   }
 }
 
@@ -233,8 +245,8 @@ int launch_pd(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, in
 bool rows_simplex_ok(const femx_ctx *c) { return c->plan.simplex && c->plan.max_inc >= 1 && c->plan.max_inc <= 32; }
 
 int launch_rows_simplex(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
-  int g = 8;   // groups of at least 8 lanes: room for the diagonal chunks
-  while (g < c->plan.max_inc) g *= 2;
+  // lanes per node row: 16 for tet4, 8 for tri3 (two / four rows in flight per warp) unless overridden (opts.reserved[0] = 4, 8, 16, 32: tuning knob)
+  const int g = c->opts.reserved[0] > 0 ? c->opts.reserved[0] : (c->pdim == 3 ? 16 : 8);
   return c->pdim == 2 ? launch_pd<2>(c, d_u, d_vals, d_fint, g) : launch_pd<3>(c, d_u, d_vals, d_fint, g);
 }
 

@@ -162,6 +162,27 @@ def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
             assert close(res[11], res[1], TOL_MAT), name
 
 
+def test_inverted_simplex_falls_back_to_the_general_kernel(orc):
+    """The simplex rows kernel scales gradients by sqrt(w detJ mu); a mesh with an inverted element (negative detJ, which
+    the reference assembles as is) must be refused by variant 11 and routed to the fused rows kernel by auto."""
+    m = mg.jitter(mg.tet_cube(3))
+    eind = m.eind.copy()
+    p = m.eptr[7]
+    eind[p], eind[p + 1] = eind[p + 1], eind[p]
+    m = dataclasses.replace(m, eind=eind)
+    om = orc.Mesh(m)
+    _, _, va_o = orc.assemble_K(om).export(om.ndof)
+    u = mg.displacement_field(m)
+    with api.Femx() as f:
+        f.set_mesh(m).build_plan()
+        vals, fint = f.assemble_K_fint(u)
+        assert close(vals, va_o, TOL_MAT) and close(fint, orc.fint(om, u.reshape(-1)), TOL_MAT)
+    with api.Femx(assembly_variant=11) as f:
+        f.set_mesh(m).build_plan()
+        with pytest.raises(api.FemxError):
+            f.assemble_K()
+
+
 def test_golden_matview_through_cuda(golden):
     """examples/tmp.txt: the Jacobian of cohesive_test_2.inp, now from the CUDA path."""
     g = golden["jacobian_matview_cohesive_test_2"]

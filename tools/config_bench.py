@@ -37,12 +37,14 @@ def main():
     ap.add_argument("--reps", type=int, default=7)
     ap.add_argument("--tet", type=int, default=94)
     ap.add_argument("--quad", type=int, default=1000)
+    ap.add_argument("--g", type=int, default=0, help="simplex rows kernel: lanes per node row (tuning knob, 0 = default)")
+    ap.add_argument("--dbg", type=int, default=0)
     args = ap.parse_args()
 
     # ---- C3: tet4 assembly + stress (two-pass path: element rows -> packed scratch -> ordered gather)
     m = mg.tet_cube(args.tet)
     u = mg.displacement_field(m)
-    with api.Femx() as fx:
+    with api.Femx(tile=args.g, dbg=args.dbg) as fx:
         t0 = time.time()
         fx.set_mesh(m).build_plan()
         plan_s = time.time() - t0
