@@ -61,13 +61,14 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, else 9, else 1),
+/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, 11 for a pure tri3 / tet4
+ * mesh, else 9, else 1),
  * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
  * 3 = its warp-specialised form, 5 = symmetric pair-block kernel on 16 warps (6, 7, 8: its measured tile / thread
- * variants, 4 = alias of 8), 9 = fused rows kernel for any element mix */
+ * variants, 4 = alias of 8), 9 = fused rows kernel for any element mix, 11 = simplex rows kernel (tri3 / tet4 only) */
 typedef struct {
   int quirks;            /* FEMX_Q_* bits                                   */
-  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8 hex8 tile kernels, 9 fused rows */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8 hex8 tile kernels, 9 fused rows, 11 simplex rows */
   int reserved[6];
 } femx_opts;
 
