@@ -196,6 +196,8 @@ int femx_build_plan(femx_ctx *c) {
     if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
   }
   femx::Plan &P = c->plan;
+  c->nl2g_identity = c->nlnds == c->nnds;
+  for (int i = 0; i < c->nlnds && c->nl2g_identity; ++i) c->nl2g_identity = c->nl2g[i] == i + 1;
   if (P.simplex) {   // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians and mu > 0
     const int pd = c->pdim;
     for (int m = 0; m < c->nmts && P.simplex; ++m) {

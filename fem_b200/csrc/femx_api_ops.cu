@@ -235,11 +235,20 @@ static int residual_impl(femx_ctx *c, const double *jvals, const double *u_total
   c->launches += launch_cohesive_mesh(c, d_u, dt, c->d_coh_fe, nullptr);
   c->launches += launch_cohesive_force_gather(c, d_br);
   c->launches += launch_bc_force(c, dt, t_total, d_br);  // EnforceBCForce :439-455
+  cudaEvent_t evm = nullptr;
+  if (c->opts.reserved[2] & 32) { cudaEventCreate(&evm); cudaEventRecord(evm, c->stream); }
   if (jvals) {
     if (c->nlnds != c->nnds) CK(cudaMemsetAsync(d_r, 0, sizeof(double) * (size_t)nglob, c->stream));
     c->launches += launch_spmv_sub(c, d_j, d_du, d_br, d_r);  // VecScale(-1); MatMultAdd :225-226
   }
   if ((rc = end_timing(c))) return rc;
+  if (evm) {
+    cudaStreamSynchronize(c->stream);
+    float a = 0.f, b = 0.f;
+    cudaEventElapsedTime(&a, c->ev0, evm); cudaEventElapsedTime(&b, evm, c->ev1);
+    fprintf(stderr, "femx: residual force part %.4f ms, J du part %.4f ms\n", a, b);
+    cudaEventDestroy(evm);
+  }
   if ((rc = copy_back(c, r, d_r, nglob, where))) return rc;
   return finish_call(c, true);
 }

@@ -183,6 +183,7 @@ struct femx_ctx {
   std::vector<double> coords, E_nu, cohprops, bcval;
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
+  bool nl2g_identity = false;   // nl2g[i] == i + 1 for every local node (checked once in femx_build_plan)
   femx::Plan plan;
   femx::HexPlan hex;
   femx::DevHex dhex;

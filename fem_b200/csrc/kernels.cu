@@ -334,35 +334,41 @@ __global__ void form_rhs_kernel(DevMesh dm, DevLoads L, double t_init, double t_
   f[L.dof[i]] = s;
 }
 
-// y[g] = sum_k J[row, k] * x[col] - sub[g] over the local node rows (one warp per node)
-template <int PD>
+// y[g] = sum_k J[row, k] * x[col] - sub[g] over the local node rows (MatMultAdd, src/m_global.F90:225-226).
+// G lanes own one node: its PD matrix rows are PD consecutive runs of rowlen = PD * nb values, read lane <-> consecutive
+// value (coalesced); 32 / G nodes per warp keep several dependent column -> x gathers in flight.  Fixed summation order:
+// lane partials over v = gl, gl + G, ..., then a butterfly over the group.
+template <int PD, int G>
 __global__ void __launch_bounds__(256) spmv_sub_kernel(DevMesh dm, const double *__restrict__ vals,
                                                        const double *__restrict__ x, const double *__restrict__ sub,
-                                                       double *__restrict__ y) {
-  const int lane = threadIdx.x & 31;
-  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (r >= dm.nlnds) return;
-  const int64_t b0 = dm.bptr[r];
-  const int nb = (int)(dm.bptr[r + 1] - b0);
+                                                       double *__restrict__ y, int ident) {
+  constexpr int NPW = 32 / G;
+  const int lane = threadIdx.x & 31, gl = lane % G, gi = lane / G;
+  const int64_t r = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * NPW + gi;
+  const bool on = r < dm.nlnds;
   double acc[PD];
 #pragma unroll
   for (int i = 0; i < PD; ++i) acc[i] = 0.0;
-  for (int k = lane; k < nb; k += 32) {
-    const int64_t gc = (int64_t)PD * (dm.nl2g[dm.bcol[b0 + k]] - 1);
+  if (on) {
+    const int64_t b0 = dm.bptr[r];
+    const int nb = (int)(dm.bptr[r + 1] - b0), rowlen = PD * nb;
+    const double *row = vals + PD * PD * b0;
+    for (int rem = gl; rem < rowlen; rem += G) {
+      const int k = rem / PD, j = rem - k * PD;
+      const int col = dm.bcol[b0 + k];
+      const int64_t gc = (int64_t)PD * (ident ? col : dm.nl2g[col] - 1) + j;
+      const double xv = x[gc];
 #pragma unroll
-    for (int j = 0; j < PD; ++j) {
-      const double xv = x[gc + j];
-#pragma unroll
-      for (int i = 0; i < PD; ++i) acc[i] += vals[PD * PD * b0 + (int64_t)i * PD * nb + PD * k + j] * xv;
+      for (int i = 0; i < PD; ++i) acc[i] = fma(row[(int64_t)i * rowlen + rem], xv, acc[i]);
     }
   }
 #pragma unroll
-  for (int i = 0; i < PD; ++i)
-    for (int o = 16; o > 0; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
-  if (lane == 0) {
-    const int64_t g = (int64_t)PD * (dm.nl2g[r] - 1);
+  for (int o = G / 2; o > 0; o >>= 1)
 #pragma unroll
-    for (int i = 0; i < PD; ++i) y[g + i] = acc[i] - sub[g + i];
+    for (int i = 0; i < PD; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+  if (on && gl < PD) {
+    const int64_t g = (int64_t)PD * (dm.nl2g[r] - 1) + gl;
+    y[g] = (gl == 0 ? acc[0] : (gl == 1 ? acc[1] : acc[PD - 1])) - sub[g];
   }
 }
 
@@ -558,9 +564,13 @@ int launch_form_rhs(femx_ctx *c, double t_init, double dt, double *d_f) {
 }
 
 int launch_spmv_sub(femx_ctx *c, const double *d_vals, const double *d_x, const double *d_sub, double *d_y) {
-  const int bs = 256, g = nblocks((int64_t)c->nlnds * 32, bs);
-  if (c->pdim == 2) spmv_sub_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y);
-  else spmv_sub_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y);
+  const int bs = 256;
+  const bool ident = c->nl2g_identity;   // single rank: skip the nl2g indirection
+  if (c->pdim == 2) {   // quad / tri rows hold ~9 blocks = 18 values per run: 8 lanes per node
+    spmv_sub_kernel<2, 8><<<nblocks(((int64_t)c->nlnds + 3) / 4 * 32, bs), bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y, ident);
+  } else {              // tet ~15 blocks = 45 values, hex 27 blocks = 81 values per run: 16 lanes per node
+    spmv_sub_kernel<3, 16><<<nblocks(((int64_t)c->nlnds + 1) / 2 * 32, bs), bs, 0, c->stream>>>(c->dm, d_vals, d_x, d_sub, d_y, ident);
+  }
   return 1;
 }
 
