@@ -193,7 +193,8 @@ __global__ void element_stress_kernel(int n, const double *__restrict__ ecoords,
 }
 
 // ---------------------------------------------------------------- stress, mesh level
-template <int T>
+// ONEIP (pure tri3 / tet4 mesh): the nodal value of a one-point element is its single stress, stored once per element
+template <int T, bool ONEIP>
 __global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int32_t *__restrict__ elems, int n,
                                                           const double *__restrict__ uu, double *__restrict__ sn_out) {
   constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, NIP = ET<T>::NIP, CP = ET<T>::CP;
@@ -216,23 +217,36 @@ __global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int3
     ip_stress<T>(X, U, dm.lam_mu[2 * m], dm.lam_mu[2 * m + 1], sig);
     nodal_from_ip<T>(sig, sn);
 #pragma unroll
-    for (int a = 0; a < NEN; ++a)
+    for (int a = 0; a < (ONEIP ? 1 : NEN); ++a)
 #pragma unroll
       for (int c = 0; c < CP; ++c) out[a * CP + c] = sn[a][c];
   }
 }
 
-// nodal sum in ascending element order, then the average (src/main.F90:258-279)
-__global__ void node_stress_gather_kernel(DevMesh dm, const double *__restrict__ sn, double *__restrict__ out,
-                                          int col_major) {
+// nodal sum in ascending element order, then the average (src/main.F90:258-279).  One thread per (node, component);
+// the incidence loop runs in batches of four so that the dependent loads (element id -> value) of a batch are in flight
+// together while the adds keep the reference's order.  ONEIP: one stored stress per element, nen nodes per element.
+template <bool ONEIP>
+__global__ void __launch_bounds__(256) node_stress_gather_kernel(DevMesh dm, const double *__restrict__ sn, double *__restrict__ out,
+                                                                 int col_major, int nen) {
   const int cp = dm.cp;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= (int64_t)dm.nlnds * cp) return;
   const int64_t r = tid / cp;
   const int c = (int)(tid % cp);
+  const int64_t p1 = dm.n2e_ptr[r + 1];
+  int64_t p = dm.n2e_ptr[r];
+  auto at = [&](int64_t q) -> const double * {
+    if constexpr (ONEIP) return sn + (int64_t)dm.n2e_elem[q] * nen * cp + c;
+    else return sn + ((int64_t)dm.eptr[dm.n2e_elem[q]] + dm.n2e_a[q]) * cp + c;
+  };
   double s = 0.0;
-  for (int64_t p = dm.n2e_ptr[r]; p < dm.n2e_ptr[r + 1]; ++p)
-    s += sn[((int64_t)dm.eptr[dm.n2e_elem[p]] + dm.n2e_a[p]) * cp + c];
+  for (; p + 4 <= p1; p += 4) {
+    const double *a0 = at(p), *a1 = at(p + 1), *a2 = at(p + 2), *a3 = at(p + 3);
+    const double v0 = *a0, v1 = *a1, v2 = *a2, v3 = *a3;
+    s += v0; s += v1; s += v2; s += v3;
+  }
+  for (; p < p1; ++p) s += *at(p);
   s = s / (double)dm.node_count[r];
   out[col_major ? (int64_t)c * dm.nlnds + r : tid] = s;
 }
@@ -520,20 +534,29 @@ int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const
 
 int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major) {
   int launches = 0;
+  bool oneip = !c->buckets.empty();   // pure tri3 or pure tet4 mesh: one stress per element, uniform element size
+  for (auto &b : c->buckets) oneip = oneip && (b.n == 0 || b.type == FEMX_TRI || b.type == FEMX_TET);
   for (auto &b : c->buckets) {
     if (!b.n) continue;
     const int bs = 128, g = nblocks(b.n, bs);
     switch (b.type) {
-      case FEMX_TRI: mesh_stress_kernel<FEMX_TRI><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
-      case FEMX_QUA: mesh_stress_kernel<FEMX_QUA><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
-      case FEMX_TET: mesh_stress_kernel<FEMX_TET><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
-      case FEMX_HEX: mesh_stress_kernel<FEMX_HEX><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
-      case FEMX_COH: mesh_stress_kernel<FEMX_COH><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_TRI:
+        if (oneip) mesh_stress_kernel<FEMX_TRI, true><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
+        else mesh_stress_kernel<FEMX_TRI, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
+        break;
+      case FEMX_QUA: mesh_stress_kernel<FEMX_QUA, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_TET:
+        if (oneip) mesh_stress_kernel<FEMX_TET, true><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
+        else mesh_stress_kernel<FEMX_TET, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
+        break;
+      case FEMX_HEX: mesh_stress_kernel<FEMX_HEX, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_COH: mesh_stress_kernel<FEMX_COH, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
     }
     ++launches;
   }
-  const int bs = 256;
-  node_stress_gather_kernel<<<nblocks((int64_t)c->nlnds * c->dm.cp, bs), bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major);
+  const int bs = 256, g = nblocks((int64_t)c->nlnds * c->dm.cp, bs);
+  if (oneip) node_stress_gather_kernel<true><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, c->pdim + 1);
+  else node_stress_gather_kernel<false><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, 0);
   return launches + 1;
 }
 
