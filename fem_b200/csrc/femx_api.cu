@@ -218,6 +218,17 @@ int femx_build_plan(femx_ctx *c) {
     if (!P.simplex) { P.sx_ent.clear(); P.sx_inc.clear(); P.sx_mat.clear(); }
   }
   for (size_t p = 0; p < P.sx_mat.size(); ++p) P.sx_mat[p] = c->emat[P.n2e_elem[p]] - 1;
+  P.ri_nodes.clear(); P.ri_info.clear();
+  if (c->pdim == 2 && P.max_inc >= 1 && P.max_inc <= 32) {   // flattened incidence records of the fused rows kernel
+    const size_t ninc = (size_t)P.n2e_ptr[c->nlnds];
+    P.ri_nodes.assign(4 * ninc, 0); P.ri_info.assign(ninc, 0);
+    for (size_t p = 0; p < ninc; ++p) {
+      const int e = P.n2e_elem[p], nen = c->eptr[e + 1] - c->eptr[e];
+      for (int b = 0; b < nen; ++b) P.ri_nodes[4 * p + b] = P.conn0[c->eptr[e] + b];
+      const int m = c->etype[e] == FEMX_COH ? 0 : c->emat[e] - 1;
+      P.ri_info[p] = c->etype[e] | (P.n2e_a[p] << 4) | (m << 8);
+    }
+  }
   femx::DevMesh &dm = c->dm;
   dm.pdim = c->pdim; dm.nels = c->nels; dm.nlnds = c->nlnds; dm.nnds = c->nnds; dm.cp = c->pdim == 2 ? 3 : 6;
   c->nnz = (int64_t)c->pdim * c->pdim * P.nblk;
@@ -228,7 +239,7 @@ int femx_build_plan(femx_ctx *c) {
   for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
   UP(dm.lam_mu, lm);
   UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
-  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent); UP(dm.sx_inc, P.sx_inc); UP(dm.sx_mat, P.sx_mat);
+  UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent); UP(dm.sx_inc, P.sx_inc); UP(dm.sx_mat, P.sx_mat); UP(dm.ri_nodes, P.ri_nodes); UP(dm.ri_info, P.ri_info);
   UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
   // stress multiplicity (count_node, src/main.F90:263); mesh constant, computed once
   std::vector<int32_t> cnt(c->nlnds, 0);

@@ -46,6 +46,8 @@ struct Plan {
   std::vector<uint16_t> rb_off;    // node r: nb+1 node-local offsets at [bptr[r] + r ...]
   std::vector<uint16_t> rb_ent;    // shared-memory offset (doubles) of the contributing block: incident index * rb_slot + b * pd^2
   std::vector<uint16_t> sx_ent;    // simplex rows kernel: (incident index << 4) | (a << 2) | b, same order / offsets as rb_ent
+  std::vector<int32_t> ri_nodes;   // 2-D meshes, fused rows kernel: per (node, incident element) the element's 0-based nodes padded to 4
+  std::vector<int32_t> ri_info;    // ... and type | local node << 4 | 0-based material row << 8 (cohesive: row 0)
   std::vector<int32_t> sx_inc;     // simplex rows kernel: per (node, incident element) the element's 0-based nodes, padded to 4
   std::vector<int32_t> sx_mat;     // ... and its 0-based material row
   bool simplex = false;            // every element is a tri3 / tet4 (one integration point)
@@ -153,6 +155,7 @@ struct DevMesh {
   uint16_t *rb_ent = nullptr;
   uint16_t *sx_ent = nullptr;
   int32_t *sx_inc = nullptr, *sx_mat = nullptr;
+  int32_t *ri_nodes = nullptr, *ri_info = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };
 

@@ -21,7 +21,7 @@ namespace {
 constexpr int kWarps = 8;
 
 template <int T>
-__device__ __forceinline__ void row_of(const DevMesh &dm, int e, int a, const double *__restrict__ u, double *out, int foff) {
+__device__ __forceinline__ void row_of(const DevMesh &dm, const int32_t *cn, int m, int a, const double *__restrict__ u, double *out, int foff) {
   constexpr int NEN = ET<T>::NEN, DIM = ET<T>::DIM, D2 = DIM * DIM;
   if constexpr (T == FEMX_COH) {
     // E = nu = 0 -> D = 0 (src/m_global.F90:250-252): explicit zero blocks that still enter the pattern
@@ -30,7 +30,6 @@ __device__ __forceinline__ void row_of(const DevMesh &dm, int e, int a, const do
 #pragma unroll
     for (int i = 0; i < DIM; ++i) out[foff + i] = 0.0;
   } else {
-    const int32_t *cn = dm.conn0 + dm.eptr[e];
     double X[NEN][DIM];
     int nd[NEN];
 #pragma unroll
@@ -39,7 +38,6 @@ __device__ __forceinline__ void row_of(const DevMesh &dm, int e, int a, const do
 #pragma unroll
       for (int d = 0; d < DIM; ++d) X[b][d] = dm.coords[(int64_t)nd[b] * DIM + d];
     }
-    const int m = dm.emat[e] - 1;
     const double lam = dm.lam_mu[2 * m], mu = dm.lam_mu[2 * m + 1];
     double acc[NEN][D2];
     ke_row_blocks<T>(X, a, lam, mu, acc);
@@ -82,39 +80,55 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
   const int64_t ngroups = ((int64_t)dm.nlnds + NPW - 1) / NPW;
   const int64_t stride = (int64_t)gridDim.x * kWarps;
   // incidence of the first node group; the next one is fetched while the current one is being processed
+  // 2-D meshes: the plan holds a flattened record per incidence (the element's nodes, type, local node, material row:
+  // ri_nodes / ri_info), so the chain element -> type / connectivity -> nodes is off the device's critical path
   int64_t wg = (int64_t)blockIdx.x * kWarps + w;
   int ninc = 0, e = 0, a = 0;
+  int4 rn = make_int4(0, 0, 0, 0);
+  auto fetch_inc = [&](int64_t p) {
+    if constexpr (PD == 2) {
+      rn = *reinterpret_cast<const int4 *>(dm.ri_nodes + 4 * p);
+      e = dm.ri_info[p];   // type | a << 4 | material row << 8
+    } else {
+      e = dm.n2e_elem[p]; a = dm.n2e_a[p];
+    }
+  };
   {
     const int64_t r = wg * NPW + gi;
     if (wg < ngroups && r < dm.nlnds) {
       const int64_t p0 = dm.n2e_ptr[r];
       ninc = (int)(dm.n2e_ptr[r + 1] - p0);
-      if (gl < ninc) { e = dm.n2e_elem[p0 + gl]; a = dm.n2e_a[p0 + gl]; }
+      if (gl < ninc) fetch_inc(p0 + gl);
     }
   }
   for (; wg < ngroups; wg += stride) {
     const int64_t r = wg * NPW + gi;
     const bool node_on = r < dm.nlnds;
     const int ninc_cur = ninc, e_cur = e, a_cur = a;
+    const int4 rn_cur = rn;
     {   // prefetch
-      const int64_t rn = (wg + stride) * NPW + gi;
+      const int64_t rnext = (wg + stride) * NPW + gi;
       ninc = 0;
-      if (wg + stride < ngroups && rn < dm.nlnds) {
-        const int64_t p0 = dm.n2e_ptr[rn];
-        ninc = (int)(dm.n2e_ptr[rn + 1] - p0);
-        if (gl < ninc) { e = dm.n2e_elem[p0 + gl]; a = dm.n2e_a[p0 + gl]; }
+      if (wg + stride < ngroups && rnext < dm.nlnds) {
+        const int64_t p0 = dm.n2e_ptr[rnext];
+        ninc = (int)(dm.n2e_ptr[rnext + 1] - p0);
+        if (gl < ninc) fetch_inc(p0 + gl);
       }
     }
     // ---- phase A: one incident element per lane
     if (gl < ninc_cur) {
-      const int t = dm.etype[e_cur];
       if constexpr (PD == 2) {
-        if (t == FEMX_QUA) row_of<FEMX_QUA>(dm, e_cur, a_cur, u, mine, foff);
-        else if (t == FEMX_TRI) row_of<FEMX_TRI>(dm, e_cur, a_cur, u, mine, foff);
-        else row_of<FEMX_COH>(dm, e_cur, a_cur, u, mine, foff);
+        const int32_t cn[4] = {rn_cur.x, rn_cur.y, rn_cur.z, rn_cur.w};
+        const int t = e_cur & 15, aa = (e_cur >> 4) & 15, m = e_cur >> 8;
+        if (t == FEMX_QUA) row_of<FEMX_QUA>(dm, cn, m, aa, u, mine, foff);
+        else if (t == FEMX_TRI) row_of<FEMX_TRI>(dm, cn, m, aa, u, mine, foff);
+        else row_of<FEMX_COH>(dm, cn, m, aa, u, mine, foff);
       } else {
-        if (!HEX || t == FEMX_TET) row_of<FEMX_TET>(dm, e_cur, a_cur, u, mine, foff);
-        else if constexpr (HEX) row_of<FEMX_HEX>(dm, e_cur, a_cur, u, mine, foff);
+        const int t = dm.etype[e_cur];
+        const int32_t *cn = dm.conn0 + dm.eptr[e_cur];
+        const int m = dm.emat[e_cur] - 1;
+        if (!HEX || t == FEMX_TET) row_of<FEMX_TET>(dm, cn, m, a_cur, u, mine, foff);
+        else if constexpr (HEX) row_of<FEMX_HEX>(dm, cn, m, a_cur, u, mine, foff);
       }
     }
     __syncwarp();
