@@ -186,6 +186,8 @@ struct femx_ctx {
   std::vector<double> coords, E_nu, cohprops, bcval;
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
+  int own_nranks = 1, own_rank = 0;            // femx_set_ownership (PETSC_DECIDE row split of this rank)
+  int64_t own_row_start = 0, own_row_end = -1;
   bool nl2g_identity = false;   // nl2g[i] == i + 1 for every local node (checked once in femx_build_plan)
   femx::Plan plan;
   femx::HexPlan hex;

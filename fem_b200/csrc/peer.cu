@@ -159,6 +159,7 @@ int femx_peer_connect(femx_ctx *c, int nranks, int rank, const char *handles, co
   ARG(c->peer.arena, "femx_peer_arena_create first");
   ARG(nranks >= 2 && nranks <= kMaxPeers && rank >= 0 && rank < nranks, "peer exchange handles 2..8 ranks of one node");
   ARG(handles && recv_vals && recv_f && val_bounds && val_dst && f_bounds && f_dst, "NULL argument");
+  ARG(c->own_row_end < 0 || (c->own_nranks == nranks && c->own_rank == rank), "femx_set_ownership named another rank / rank count");
   ARG(val_bounds[0] == 0 && val_bounds[nranks] == c->nnz, "val_bounds must span the local values");
   ARG(f_bounds[0] == 0 && f_bounds[nranks] == (int64_t)c->pdim * c->nlnds, "f_bounds must span the local dofs");
   CK(cudaSetDevice(c->device));

@@ -162,7 +162,8 @@ int femx_stress(femx_ctx *ctx, const double *uu_local, double *stress_node, int 
 
 /* ---- multi-GPU (one ctx per rank) ----------------------------------- */
 /* rows [row_start,row_end) of the global matrix are owned by this rank: the PETSC_DECIDE
- * split of MatCreateAIJ, src/main.F90:154.  Must precede femx_build_plan. */
+ * split of MatCreateAIJ, src/main.F90:154.  Recorded and cross-checked by femx_peer_connect; the value ranges per
+ * owner are passed there. */
 int femx_set_ownership(femx_ctx *ctx, int nranks, int rank, int64_t row_start, int64_t row_end);
 /* Ordered merge used after the interface exchange: out[s] = sum_{q in [ptr[s], ptr[s+1])} src(idx[q]) in list
  * order (deterministic), src = a for idx < na else b[idx - na].  All pointers are DEVICE pointers.
@@ -192,6 +193,8 @@ int femx_peer_connect(femx_ctx *ctx, int nranks, int rank, const char *handles, 
                       const int64_t *f_bounds, const int64_t *f_dst);
 int femx_peer_recv(femx_ctx *ctx, const double **vals_recv, const double **f_recv);
 int femx_peer_disconnect(femx_ctx *ctx);
+/* Reserved: the library creates no NCCL communicator of its own (both return FEMX_ERR_UNSUPPORTED); the exchange is
+ * femx_peer_* above or the host's MPI / NCCL on the contiguous value slices. */
 int femx_nccl_unique_id(char id[128]);
 int femx_comm_init(femx_ctx *ctx, const char id[128]);
 
