@@ -72,7 +72,8 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
   extern __shared__ double sm_rows[];
   constexpr int D2 = PD * PD, NPW = 32 / G;
   constexpr int PARTS = G / D2;                  // lanes per diagonal-block value when the group is wide enough to split it
-  constexpr bool SPLIT = PARTS >= 2;
+  constexpr bool BLK = G <= 8;   // few elements around a node (quad4 / tri3 / hex8): phase B maps lane <-> block
+  constexpr bool SPLIT = !BLK && PARTS >= 2;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int gl = lane % G, gi = lane / G;
   double *mine = sm_rows + ((size_t)w * 32 + lane) * slot;
@@ -150,8 +151,37 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
           for (int i = 0; i < PD; ++i) prow[i] = peer_row(pt, vals, D2 * b0 + (int64_t)i * rowlen);
         }
       }
+      if constexpr (BLK) {   // one list walk per block instead of one per value
+        const bool al16 = !PEER && (reinterpret_cast<size_t>(vals) & 15) == 0;
+        for (int k = gl; k < nb; k += G) {
+          int c = off[k];
+          const int c1 = off[k + 1];
+          double acc[D2];
+#pragma unroll
+          for (int q = 0; q < D2; ++q) acc[q] = 0.0;
+          int en = c < c1 ? ent[c] : 0;
+          for (; c < c1; ++c) {
+            const int en_next = c + 1 < c1 ? ent[c + 1] : 0;   // the next entry travels while this one is used
+            const double *src = grp + en;
+#pragma unroll
+            for (int q = 0; q < D2; ++q) acc[q] += src[q];
+            en = en_next;
+          }
+#pragma unroll
+          for (int i = 0; i < PD; ++i) {
+            double *row = vrow + (int64_t)i * rowlen;
+            if constexpr (PEER) row = prow[i];
+            if (PD == 2 && al16) {   // 2-D: 4 b0 + i * 2 nb + 2 k is even, every block row is 16-byte aligned
+              *reinterpret_cast<double2 *>(row + 2 * k) = make_double2(acc[i * 2], acc[i * 2 + 1]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < PD; ++j) row[PD * k + j] = acc[i * PD + j];
+            }
+          }
+        }
+      }
       const int kd = SPLIT ? dm.bdiag[r] : -1;   // the diagonal block has one contribution per incident element: split it
-      for (int v = gl; v < nv; v += G) {
+      for (int v = gl; !BLK && v < nv; v += G) {
         const int i = (v >= rowlen) + (PD == 3 && v >= 2 * rowlen), rem = v - i * rowlen, k = rem / PD, j = rem - k * PD;
         if (k == kd) continue;
         const double *src = grp + i * PD + j;
