@@ -54,6 +54,7 @@ SIGNATURES = {
     "femx_stress": (C.c_int, [V, V, V, C.c_int, C.c_int]),
     "femx_set_ownership": (C.c_int, [V, C.c_int, C.c_int, C.c_int64, C.c_int64]),
     "femx_gather_sum": (C.c_int, [V, V, C.c_int64, V, V, V, C.c_int64, V]),
+    "femx_stress_partial": (C.c_int, [V, V, V, V, C.c_int]),
     "femx_set_loads": (C.c_int, [V, C.c_int, c_int_p, c_double_p, C.c_int, c_int_p, c_double_p]),
     "femx_form_rhs": (C.c_int, [V, C.c_double, C.c_double, C.c_double, V, C.c_int]),
     "femx_peer_arena_create": (C.c_int, [V, C.c_int64, C.c_int64, V]),

@@ -348,8 +348,7 @@ int femx_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, c
   return finish_call(c, true);
 }
 
-int femx_stress(femx_ctx *c, const double *uu_local, double *stress_node, int layout, int where) {
-  if (!c) return FEMX_ERR_ARG;
+static int stress_impl(femx_ctx *c, const double *uu_local, double *stress_node, int layout, int where, int average) {
   ARG(c->has_plan && uu_local && stress_node, "femx_build_plan first / NULL argument");
   CK(cudaSetDevice(c->device));
   const int cp = c->pdim == 2 ? 3 : 6;
@@ -361,10 +360,24 @@ int femx_stress(femx_ctx *c, const double *uu_local, double *stress_node, int la
   if ((rc = stage_out(c, stress_node, nout, where, &c->d_vec[2], &d_out))) return rc;
   if ((rc = ensure(c, &c->d_sn, (int64_t)c->eptr[c->nels] * cp))) return rc;
   if ((rc = begin_timing(c))) return rc;
-  c->launches += launch_mesh_stress(c, d_u, c->d_sn, d_out, layout == FEMX_COL_MAJOR);
+  c->launches += launch_mesh_stress(c, d_u, c->d_sn, d_out, layout == FEMX_COL_MAJOR, average);
   if ((rc = end_timing(c))) return rc;
   if ((rc = copy_back(c, stress_node, d_out, nout, where))) return rc;
   return finish_call(c, true);
+}
+
+int femx_stress(femx_ctx *c, const double *uu_local, double *stress_node, int layout, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  return stress_impl(c, uu_local, stress_node, layout, where, 1);
+}
+
+int femx_stress_partial(femx_ctx *c, const double *uu_local, double *stress_sum, int32_t *count_node, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  int rc = stress_impl(c, uu_local, stress_sum, FEMX_ROW_MAJOR, where, 0);
+  if (rc || !count_node) return rc;
+  CK(cudaMemcpy(count_node, c->dm.node_count, sizeof(int32_t) * (size_t)c->nlnds,
+                where == FEMX_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost));
+  return FEMX_OK;
 }
 
 }  // extern "C"

@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int3
 // together while the adds keep the reference's order.  ONEIP: one stored stress per element, nen nodes per element.
 template <bool ONEIP>
 __global__ void __launch_bounds__(256) node_stress_gather_kernel(DevMesh dm, const double *__restrict__ sn, double *__restrict__ out,
-                                                                 int col_major, int nen) {
+                                                                 int col_major, int nen, int average) {
   const int cp = dm.cp;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= (int64_t)dm.nlnds * cp) return;
@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(256) node_stress_gather_kernel(DevMesh dm, con
     s += v0; s += v1; s += v2; s += v3;
   }
   for (; p < p1; ++p) s += *at(p);
-  s = s / (double)dm.node_count[r];
+  if (average) s = s / (double)dm.node_count[r];   // multi-rank hosts divide by the global count themselves
   out[col_major ? (int64_t)c * dm.nlnds + r : tid] = s;
 }
 
@@ -532,7 +532,7 @@ int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const
   return 1;
 }
 
-int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major) {
+int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major, int average) {
   int launches = 0;
   bool oneip = !c->buckets.empty();   // pure tri3 or pure tet4 mesh: one stress per element, uniform element size
   for (auto &b : c->buckets) oneip = oneip && (b.n == 0 || b.type == FEMX_TRI || b.type == FEMX_TET);
@@ -555,8 +555,8 @@ int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_
     ++launches;
   }
   const int bs = 256, g = nblocks((int64_t)c->nlnds * c->dm.cp, bs);
-  if (oneip) node_stress_gather_kernel<true><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, c->pdim + 1);
-  else node_stress_gather_kernel<false><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, 0);
+  if (oneip) node_stress_gather_kernel<true><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, c->pdim + 1, average);
+  else node_stress_gather_kernel<false><<<g, bs, 0, c->stream>>>(c->dm, d_sn, d_out, col_major, 0, average);
   return launches + 1;
 }
 

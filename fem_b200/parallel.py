@@ -276,3 +276,83 @@ class DistributedAssembly:
                                     C.c_void_p(ptr.data_ptr()), C.c_void_p(idx.data_ptr()), len(ep.colidx),
                                     C.c_void_p(out.data_ptr())))
         return out
+
+
+# --------------------------------------------------------------------------- nodal stress across ranks
+def shared_node_lists(nl2g: np.ndarray, all_nl2g: list, rank: int):
+    """For every peer q: positions (in MY local numbering) of the nodes rank q holds too, in ascending global id --
+    the same order on both sides, so slot i of what I send is slot i of what q expects from me."""
+    mine = np.asarray(nl2g, np.int64)
+    out = []
+    for q, other in enumerate(all_nl2g):
+        if q == rank:
+            out.append(np.zeros(0, np.int64))
+        else:
+            common = np.intersect1d(mine, np.asarray(other, np.int64), assume_unique=True)
+            out.append(np.searchsorted(mine, common))
+    return out
+
+
+def combine_partials(own: np.ndarray, recv: list, shared: list, rank: int):
+    """Sum of the ranks' partials in ascending RANK order (deterministic, identical on every rank that shares the
+    node): contributions of lower ranks, then mine, then higher ranks.  Works on numpy arrays or torch tensors."""
+    total = own * 0
+    for q in range(len(shared)):
+        if q == rank:
+            total = total + own
+        elif len(shared[q]):
+            total[shared[q]] = total[shared[q]] + recv[q]
+    return total
+
+
+class DistributedStress:
+    """RecoverStress / RecoverNodalStress + the cross-rank nodal average (src/main.F90:253-291): every rank computes
+    the sums of its own elements (femx_stress_partial); nodes shared with other ranks get the peers' partial sums
+    (torch.distributed all_to_all over NCCL; gloo in the CPU tests) added in rank order and are divided by the global
+    count -- what the reference obtains from the dense Mat_Stress assembly and MPI_AllReduce of count_node every step.
+    The counts are mesh constants and are exchanged once."""
+
+    def __init__(self, fx, dist, device):
+        import torch
+        self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
+        P, rank = dist.get_world_size(), dist.get_rank()
+        self.P, self.rank = P, rank
+        m = fx.mesh
+        self.cp = m.cpdim
+        n_all = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(P)]
+        dist.all_gather(n_all, torch.tensor([m.nlnds], dtype=torch.int64, device=device))
+        sizes = [int(t.item()) for t in n_all]
+        pad = max(sizes)
+        buf = torch.zeros(pad, dtype=torch.int64, device=device)
+        buf[:m.nlnds] = torch.from_numpy(np.asarray(m.nl2g, np.int64)).to(device)
+        alls = [torch.empty_like(buf) for _ in range(P)]
+        dist.all_gather(alls, buf)
+        all_nl2g = [alls[q][:sizes[q]].cpu().numpy() for q in range(P)]
+        self.shared = shared_node_lists(m.nl2g, all_nl2g, rank)
+        self.shared_dev = [torch.from_numpy(s).to(device) for s in self.shared]
+        self.sums = torch.empty(m.nlnds * self.cp, dtype=torch.float64, device=device)
+        counts = torch.empty(m.nlnds, dtype=torch.int32, device=device)
+        self._counts_local = counts
+        self.count_global = None
+
+    def _exchange(self, rows):
+        """rows [nlnds, k] tensor of partials -> list of what each peer holds for the nodes we share."""
+        torch = self.torch
+        ins = [rows[self.shared_dev[q]].contiguous() for q in range(self.P)]
+        outs = [torch.empty_like(t) for t in ins]
+        self.dist.all_to_all(outs, ins)
+        return outs
+
+    def stress(self, d_u_ptr):
+        """Averaged nodal stress [nlnds, cp] of this rank's local nodes (device tensor); d_u_ptr = device pointer of uu_local."""
+        import ctypes as C
+        torch, fx = self.torch, self.fx
+        first = self.count_global is None
+        fx._ck(fx.L.femx_stress_partial(fx.h, d_u_ptr, C.c_void_p(self.sums.data_ptr()),
+                                        C.c_void_p(self._counts_local.data_ptr()) if first else None, 1))
+        if first:
+            cl = self._counts_local.to(torch.float64).reshape(-1, 1)
+            self.count_global = combine_partials(cl, self._exchange(cl), self.shared_dev, self.rank)
+        part = self.sums.reshape(-1, self.cp)
+        total = combine_partials(part, self._exchange(part), self.shared_dev, self.rank)
+        return total / self.count_global

@@ -146,6 +146,11 @@ int femx_residual_forces(femx_ctx *ctx, const double *u_total_local, const doubl
                          double t_total, double *out, int where);
 /* RecoverStress + RecoverNodalStress + nodal average, src/main.F90:253-279.
  * stress_node [nlnds][cp] row-major (or column-major stress_node(nlnds,cpdim) by layout) */
+/* Multi-rank form of the same: the SUM of the nodal values of this rank's own elements per local node
+ * (stress_sum[nlnds*cp] row-major, ascending element order) and the rank's count_node[nlnds] (may be NULL), without
+ * the division -- the host adds the partials of the ranks sharing a node and divides by the global count, what the
+ * reference does through Mat_Stress and MPI_AllReduce (src/main.F90:270-289).  fem_b200/parallel.py: DistributedStress. */
+int femx_stress_partial(femx_ctx *ctx, const double *uu_local, double *stress_sum, int32_t *count_node, int where);
 /* Loads.  femx_set_loads takes the arrays ReadDistForces / ReadDistTractions leave on a rank
  * (src/m_io.F90:330-372, :414-475): fnode[nfrcs] GLOBAL 1-based node, fval[nfrcs][pdim+2] = components, t1, t2;
  * telsd[ntrcs][2] = LOCAL 1-based element (0 = skip, src/m_global.F90:427), 1-based side; tval[ntrcs][pdim+2].

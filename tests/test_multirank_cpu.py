@@ -100,6 +100,38 @@ def _worker(rank, world, port, kind, out):
         ug = mg.displacement_field(g)
         f_ref = orc.fint(og, ug.reshape(-1))[r0:r1]
         assert np.all(np.abs(f_own - f_ref) <= 1e-12 * max(np.abs(f_ref).max(), 1e-300)), "owned internal force"
+        # nodal stress across ranks: partial sums of the rank's own elements + the peers' for shared nodes, in rank order
+        ul = mg.displacement_field(loc)
+        s_avg, cnt = orc.stress(om, ul.reshape(-1))               # local average and local count
+        part = s_avg * cnt[:, None]
+        sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(sizes, torch.tensor([loc.nlnds], dtype=torch.int64))
+        padn = max(int(t.item()) for t in sizes)
+        buf = torch.zeros(padn, dtype=torch.int64); buf[:loc.nlnds] = torch.from_numpy(loc.nl2g.astype(np.int64))
+        alls = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(alls, buf)
+        all_nl2g = [alls[q][:int(sizes[q].item())].numpy() for q in range(world)]
+        shared = par.shared_node_lists(loc.nl2g, all_nl2g, rank)
+
+        def swap(rows):
+            got = [None] * world
+            reqs = []
+            for q in range(world):
+                if q == rank or not len(shared[q]):
+                    continue
+                got[q] = torch.empty((len(shared[q]), rows.shape[1]), dtype=torch.float64)
+                reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(rows[shared[q]])), q, tag=7))
+                reqs.append(dist.irecv(got[q], q, tag=7))
+            for rq in reqs:
+                rq.wait()
+            return [g.numpy() if g is not None else None for g in got]
+
+        cnt_g = par.combine_partials(cnt[:, None].astype(float), swap(cnt[:, None].astype(float)), shared, rank)
+        s_g = par.combine_partials(part, swap(part), shared, rank) / cnt_g
+        s_ref, cnt_ref = orc.stress(og, ug.reshape(-1))
+        assert np.array_equal(cnt_g[:, 0], cnt_ref[loc.nl2g - 1]), "global node multiplicity"
+        want = s_ref[loc.nl2g - 1]
+        assert np.all(np.abs(s_g - want) <= 1e-10 * np.maximum(np.abs(want), np.abs(s_ref).max())), "nodal stress across ranks"
         out.put((rank, int(ep.recv_counts.sum()), len(merged)))
     finally:
         dist.destroy_process_group()

@@ -60,6 +60,15 @@ def main():
         f_ref = orc.fint(og, mg.displacement_field(g).reshape(-1))
         f = d_f.cpu().numpy()
         good = good and np.all(np.abs(f - f_ref) <= 1e-12 * np.maximum(np.abs(f_ref), np.abs(f_ref).max()))
+        if rep == 0 and peer == 0:                 # nodal stress across ranks (femx_stress_partial + DistributedStress)
+            ds = par.DistributedStress(fx, dist, dev)
+            s_loc = ds.stress(C.c_void_p(d_u.data_ptr())).cpu().numpy()
+            s_loc2 = ds.stress(C.c_void_p(d_u.data_ptr())).cpu().numpy()
+            s_ref, _ = orc.stress(og, mg.displacement_field(g).reshape(-1))
+            want = s_ref[loc.nl2g - 1]
+            sgood = np.all(np.abs(s_loc - want) <= 1e-10 * np.maximum(np.abs(want), np.abs(s_ref).max())) and np.array_equal(s_loc, s_loc2)
+            print(f"[rank {rank}] {name} nodal stress over {world} ranks {'OK' if sgood else 'MISMATCH'}", flush=True)
+            good = good and bool(sgood)
         print(f"[rank {rank}] {name} {('nccl', 'peer-push', 'peer-fused')[peer]} #{rep}: owned rows [{r0},{r1}) nnz {len(merged)} recv {int(da.ep.recv_counts.sum())} "
               f"{'OK' if good else 'MISMATCH'}", flush=True)
         ok = ok and bool(good)

@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--exchange", choices=("peer", "nccl"), default="peer")
+    ap.add_argument("--stress", action="store_true", help="also time the nodal-averaged stress recovery (wall clock per call)")
     args = ap.parse_args()
     rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(lr)
@@ -83,7 +84,20 @@ def main():
     dev_ms = sum(step() for _ in range(args.steps))
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - w0)
-    t = torch.tensor([dev_ms, wall_ms, float(m.nels), float(fx.nnz)], device=dev, dtype=torch.float64)
+    stress_ms = 0.0
+    if args.stress:   # nodal-averaged stress incl. the cross-rank sum (wall time: kernels + NCCL all_to_all of the shared nodes)
+        d_s = fx.device_buffer(8 * m.cpdim * m.nlnds)
+        ds = par.DistributedStress(fx, dist, dev) if world > 1 else None
+        one = (lambda: ds.stress(d_u.ptr)) if ds else (lambda: fx._ck(fx.L.femx_stress(fx.h, d_u.ptr, d_s.ptr, api.ROW_MAJOR, api.DEVICE)))
+        for _ in range(args.warmup):
+            one()
+        barrier()
+        s0 = time.perf_counter()
+        for _ in range(args.steps):
+            one()
+        barrier()
+        stress_ms = 1e3 * (time.perf_counter() - s0) / args.steps
+    t = torch.tensor([dev_ms, wall_ms, float(m.nels), float(fx.nnz), stress_ms], device=dev, dtype=torch.float64)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
@@ -96,6 +110,7 @@ def main():
                           "max_elements_per_rank": int(tmax[2]), "nnz_local_sum": int(tsum[3]),
                           "exchange": ("peer push kernel + step barrier" if da is not None and da.peer else "nccl all_to_all") if world > 1 else "none",
                           "recv_bytes_rank0": int(da.ep.recv_counts.sum()) * 8 if da is not None else 0,
+                          "stress_wall_ms_per_call": float(tmax[4]) if args.stress else None,
                           "steps": args.steps, "warmup": args.warmup, "setup_s": round(setup_s, 1)}), flush=True)
     if da is not None:
         da.close()
