@@ -3,12 +3,14 @@
 //
 // Every rank owns a receive arena (cudaMalloc, exported with cudaIpcGetMemHandle, mapped by its peers over
 // NVLink / NVSwitch).  Because the rank-local CSR lists rows in ascending global order, the values bound for
-// rank q are ONE contiguous range of local value offsets; the assembly kernels (hex_sym2.cu, rows_fused.cu)
-// look a row's first offset up in the PeerTab and store the row straight into q's arena instead of the local
-// array -- compute and transfer are one kernel, the stores of the 3 % interface rows ride the NVLink write
-// path while the other CTAs keep assembling.  A one-warp kernel behind the assembly kernel then raises this
-// rank's step counter in every peer's arena (system-scope release) and waits for theirs (acquire): when
-// femx_assemble_* returns, the rank's own slice and everything its peers sent are complete.
+// rank q are ONE contiguous range of local value offsets (likewise the internal-force entries in local dof
+// order).  Default: peer_push_kernel, launched behind the assembly kernel on the same stream, copies those
+// ranges into the owners' arenas with coalesced remote stores and its last CTA runs the step barrier -- this
+// rank's step counter is raised in every peer's arena (system-scope release) and the peers' counters are
+// awaited (acquire): when femx_assemble_* returns, the rank's own slice and everything its peers sent are
+// complete.  Opt-in (opts.reserved[3] = 1): the PEER instantiations of hex_sym2_kernel / fused_rows_kernel /
+// rows_simplex_kernel look a row's first offset up in the PeerTab and store it remotely themselves; only the
+// barrier kernel follows (measured slower).
 // Receive areas are double-buffered on the step parity, so a peer that is one assembly ahead never
 // overwrites values the host solver may still be reading; the step barrier keeps it from getting two ahead.
 #include "api_util.h"

@@ -129,6 +129,12 @@ module femx
       type(c_ptr), value :: ctx, a, b, ptr, idx, out
       integer(c_int64_t), value :: na, nout
     end function
+    ! multi-rank nodal stress: sums of this rank's elements + its count_node (src/main.F90:253-291)
+    integer(c_int) function femx_stress_partial(ctx, uu_local, stress_sum, count_node, where) bind(C, name="femx_stress_partial")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, uu_local, stress_sum, count_node
+      integer(c_int), value :: where
+    end function
     ! FormRHS (src/m_global.F90:373-436): fnode / fval / telsd / tval as ReadDistForces / ReadDistTractions leave them,
     ! TRANSPOSED to row-major (the Fortran arrays are (count, pdim+2) column-major)
     integer(c_int) function femx_set_loads(ctx, nfrcs, fnode, fval, ntrcs, telsd, tval) bind(C, name="femx_set_loads")
