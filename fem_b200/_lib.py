@@ -49,6 +49,7 @@ SIGNATURES = {
     "femx_assemble_K_fint": (C.c_int, [V, V, V, V, C.c_int]),
     "femx_apply_kbc": (C.c_int, [V, V, C.c_int]),
     "femx_jacobian": (C.c_int, [V, V, V, C.c_double, V, C.c_int]),
+    "femx_jacobian_update": (C.c_int, [V, V, V, C.c_double, V, C.c_int]),
     "femx_residual": (C.c_int, [V, V, V, V, V, C.c_double, C.c_double, V, C.c_int]),
     "femx_residual_forces": (C.c_int, [V, V, V, C.c_double, C.c_double, V, C.c_int]),
     "femx_stress": (C.c_int, [V, V, V, C.c_int, C.c_int]),

@@ -188,9 +188,9 @@ int femx_apply_kbc(femx_ctx *c, double *vals, int where) {
   return finish_call(c, false);
 }
 
-int femx_jacobian(femx_ctx *c, const double *kvals, const double *u_total_local, double dt, double *jvals, int where) {
-  if (!c) return FEMX_ERR_ARG;
+static int jacobian_impl(femx_ctx *c, const double *kvals, const double *u_total_local, double dt, double *jvals, int where, bool update) {
   ARG(c->has_plan && kvals && u_total_local && jvals, "femx_build_plan first / NULL argument");
+  ARG(!update || (where == FEMX_DEVICE && jvals != kvals), "femx_jacobian_update works on a resident Jacobian (FEMX_DEVICE, jvals != kvals)");
   CK(cudaSetDevice(c->device));
   int rc;
   const double *d_u = nullptr, *d_k = nullptr;
@@ -199,14 +199,24 @@ int femx_jacobian(femx_ctx *c, const double *kvals, const double *u_total_local,
   if ((rc = stage_in(c, kvals, c->nnz, where, &c->d_kstage, &d_k))) return rc;
   if ((rc = stage_out(c, jvals, c->nnz, where, &c->d_vals, &d_j))) return rc;
   if ((rc = begin_timing(c))) return rc;
-  // MatCopy(Mat_K, Jacobian) src/m_global.F90:123
-  if (d_j != d_k) CK(cudaMemcpyAsync(d_j, d_k, sizeof(double) * (size_t)c->nnz, cudaMemcpyDeviceToDevice, c->stream));
+  // MatCopy(Mat_K, Jacobian) src/m_global.F90:123; the update form rewrites only what a cohesive element or a BC touches
+  if (d_j != d_k && !update) CK(cudaMemcpyAsync(d_j, d_k, sizeof(double) * (size_t)c->nnz, cudaMemcpyDeviceToDevice, c->stream));
   c->launches += launch_cohesive_mesh(c, d_u, dt, nullptr, c->d_coh_ke);
   c->launches += launch_jacobian_overlay(c, d_k, d_j);
   c->launches += launch_apply_kbc(c, d_j);  // ApplyKBC(Jacobian) :154
   if ((rc = end_timing(c))) return rc;
   if ((rc = copy_back(c, jvals, d_j, c->nnz, where))) return rc;
   return finish_call(c, true);
+}
+
+int femx_jacobian(femx_ctx *c, const double *kvals, const double *u_total_local, double dt, double *jvals, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  return jacobian_impl(c, kvals, u_total_local, dt, jvals, where, false);
+}
+
+int femx_jacobian_update(femx_ctx *c, const double *kvals, const double *u_total_local, double dt, double *jvals, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  return jacobian_impl(c, kvals, u_total_local, dt, jvals, where, true);
 }
 
 static int residual_impl(femx_ctx *c, const double *jvals, const double *u_total_local, const double *du,

@@ -92,6 +92,12 @@ module femx
       real(c_double), value :: dt
       integer(c_int), value :: where
     end function
+    integer(c_int) function femx_jacobian_update(ctx, kvals, u_total_local, dt, jvals, where) bind(C, name="femx_jacobian_update")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx, kvals, u_total_local, jvals
+      real(c_double), value :: dt
+      integer(c_int), value :: where
+    end function
     integer(c_int) function femx_residual(ctx, jvals, u_total_local, du, f_ext, dt, t_total, r, where) &
         bind(C, name="femx_residual")
       import :: c_ptr, c_int, c_double

@@ -137,6 +137,12 @@ int femx_apply_kbc(femx_ctx *ctx, double *vals, int where);
  * kvals = values from femx_assemble_K (+apply_kbc), same memory space as jvals */
 int femx_jacobian(femx_ctx *ctx, const double *kvals, const double *u_total_local, double dt,
                   double *jvals, int where);
+/* Newton iterations after the first: jvals already holds a Jacobian that femx_jacobian / femx_jacobian_update built
+ * from the SAME kvals, so only the blocks a cohesive element touches are rebuilt from K (J = K + sum) and the BC
+ * diagonals re-inserted -- O(interface) instead of the reference's MatCopy of all nnz values per call
+ * (src/m_global.F90:123).  Device-resident only (where = FEMX_DEVICE, jvals != kvals); same result bit for bit. */
+int femx_jacobian_update(femx_ctx *ctx, const double *kvals, const double *u_total_local, double dt,
+                         double *jvals, int where);
 /* CalcResidual, src/m_global.F90:161-235 (single rank: vectors are global [pdim*nnds]):
  * r = J*du - (f_ext + sum f_coh(u_total), BC rows <- 1e30*bcval*dt/t_total) */
 int femx_residual(femx_ctx *ctx, const double *jvals, const double *u_total_local, const double *du,

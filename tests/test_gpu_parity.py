@@ -237,6 +237,27 @@ def _spmv(Jo, x, n, orc):
     return y
 
 
+def test_jacobian_update_equals_full_rebuild(golden):
+    """femx_jacobian_update (Newton iterations after the first: only cohesive blocks and BC diagonals are rewritten)
+    must give the full femx_jacobian bit for bit, for a sequence of different openings on a resident Jacobian."""
+    import ctypes as C
+    m = mg.jitter(mg.cohesive_strip(12, 3))
+    nn = m.nlnds
+    with api.Femx(quirks=api.Q_UEL) as f:
+        f.set_mesh(m).build_plan()
+        kv = f.assemble_K()
+        d_k = f.device_buffer(8 * f.nnz).upload(kv)
+        d_j = f.device_buffer(8 * f.nnz)
+        rng = np.random.default_rng(5)
+        for it in range(4):
+            u = 1e-3 * rng.standard_normal((nn, 2))
+            d_u = f.device_buffer(u.nbytes).upload(u)
+            call = f.L.femx_jacobian if it == 0 else f.L.femx_jacobian_update
+            f._ck(call(f.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE))
+            assert np.array_equal(d_j.download(count=f.nnz), f.CalcJacobian(kv, u, m.dt)), it
+        assert f.L.femx_jacobian_update(f.h, d_k.ptr, d_u.ptr, float(m.dt), d_k.ptr, api.DEVICE) != 0   # in place: refused
+
+
 def test_form_rhs_vs_oracle(fx, orc, golden):
     """FormRHS on the device (nodal-force ramps, ApplyTraction + EdgeAreaNodes*, EnforceBCForce): the kernel adds each
     dof's contributions in the reference's call order with unfused roundings -> bit-exact against the oracle."""

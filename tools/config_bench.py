@@ -79,6 +79,9 @@ def main():
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_jacobian(fx.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE)), args.reps)
         line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "CalcJacobian (copy K, cohesive overlay, BC diagonal)", m.nels, ms, best,
              16.0 * fx.nnz / m.nels)
+        ms, best = timed(fx, lambda: fx._ck(fx.L.femx_jacobian_update(fx.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE)), args.reps)
+        line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "CalcJacobian, Newton iterations after the first (femx_jacobian_update: cohesive blocks + BC diagonal only)",
+             m.nels, ms, best, 0.0)
         ms, best = timed(fx, lambda: fx._ck(fx.L.femx_residual(fx.h, d_j.ptr, d_u.ptr, d_du.ptr, d_fe.ptr, float(m.dt), float(m.t),
                                                                  d_r.ptr, api.DEVICE)), args.reps)
         line(f"C4 quad4 2x{args.quad}^2 + {args.quad} coh", "CalcResidual (cohesive forces, BC rows, J du - f)", m.nels, ms, best,
