@@ -243,11 +243,14 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         alg = algorithmic_bytes(m, nnz)
         achieved = alg / (ms_step * 1e-3) / 1e9
-        traffic = None
+        traffic, pipes = None, None
         try:   # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu capture
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
             if args.n == 100:
-                traffic = tj.get(KERNEL_NAME.get(args.variant, "?"), {}).get("traffic_bytes_per_launch")
+                ent = tj.get(KERNEL_NAME.get(args.variant, "?"), {})
+                traffic = ent.get("traffic_bytes_per_launch")
+                if "lsu_data_pipe_pct_of_peak" in ent:   # what actually bounds the kernel (committed ncu capture, not measured live)
+                    pipes = {k: ent[k] for k in ("lsu_data_pipe_pct_of_peak", "fp64_pipe_pct_of_peak", "dram_pct_of_peak")}
         except Exception:
             pass
         line = {"metric": "elements/sec (Ke+f_int assembly)", "value": value, "unit": "elements/s", "n_gpus": world,
@@ -267,7 +270,8 @@ def main():
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                              "frac_of_8TBs_nominal": achieved / 8000.0, "bytes_per_element": alg / m.nels, "algorithmic_bytes_per_launch": alg,
-                             "kernel": KERNEL_NAME.get(args.variant, "?") + " (one launch per step)", "traffic": traffic}}
+                             "kernel": KERNEL_NAME.get(args.variant, "?") + " (one launch per step)", "traffic": traffic,
+                             "ncu_pipe_utilisation": pipes}}
         if e2e:
             line["e2e"] = {"value": nels_total / (e2e_ms * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": e2e["h2d"],
                            "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms}
