@@ -133,6 +133,10 @@ def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
     the packed Ke scratch) and the oracle, on every element mix incl. cohesive zeros and an unstructured hex mesh."""
     cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("tet_jitter", mg.jitter(mg.tet_cube(5))),
                                      ("tri_wide", mg.jitter(mg.tri_rect(40, 3))), ("tet_rank1of2", None)]
+    # three materials with different moduli AND Poisson ratios (rho = lambda / mu varies per element)
+    three = np.array([[3e10, .25, 0, 0, 0], [7e9, .33, 0, 0, 0], [2.1e11, .1, 0, 0, 0]])
+    for nm, base in (("tet_3mat", mg.jitter(mg.tet_cube(4))), ("tri_3mat", mg.jitter(mg.tri_rect(7, 6))), ("quad_3mat", mg.jitter(mg.quad_rect(8, 5)))):
+        cases.append((nm, dataclasses.replace(base, mat=three, emat=(np.arange(base.nels) % 3 + 1).astype(np.int32))))
     for name, m in cases:
         if m is None:                                   # rank-local tet mesh: ragged node set, nl2g not the identity
             g = mg.jitter(mg.tet_cube(5))
