@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int3
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const int e = elems[idx];
-  double *out = sn_out + (int64_t)dm.eptr[e] * CP;
+  double *out = sn_out + (ONEIP ? (int64_t)e : (int64_t)dm.eptr[e]) * CP;   // ONEIP: dense [nels][cp]
   if constexpr (T == FEMX_COH) {
     for (int q = 0; q < NEN * CP; ++q) out[q] = 0.0;  // D5: contribution defined as zero
   } else {
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256) node_stress_gather_kernel(DevMesh dm, con
   const int64_t p1 = dm.n2e_ptr[r + 1];
   int64_t p = dm.n2e_ptr[r];
   auto at = [&](int64_t q) -> const double * {
-    if constexpr (ONEIP) return sn + (int64_t)dm.n2e_elem[q] * nen * cp + c;
+    if constexpr (ONEIP) return sn + (int64_t)dm.n2e_elem[q] * cp + c;
     else return sn + ((int64_t)dm.eptr[dm.n2e_elem[q]] + dm.n2e_a[q]) * cp + c;
   };
   double s = 0.0;
