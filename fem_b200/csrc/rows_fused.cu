@@ -85,6 +85,8 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
   // ri_nodes / ri_info), so the chain element -> type / connectivity -> nodes is off the device's critical path
   int64_t wg = (int64_t)blockIdx.x * kWarps + w;
   int ninc = 0, e = 0, a = 0;
+  int64_t b0n = 0, rben = 0;   // next group's row metadata: first block, block count, first list entry
+  int nbn = 0;
   int4 rn = make_int4(0, 0, 0, 0);
   auto fetch_inc = [&](int64_t p) {
     if constexpr (PD == 2) {
@@ -100,6 +102,7 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
       const int64_t p0 = dm.n2e_ptr[r];
       ninc = (int)(dm.n2e_ptr[r + 1] - p0);
       if (gl < ninc) fetch_inc(p0 + gl);
+      b0n = dm.bptr[r]; nbn = (int)(dm.bptr[r + 1] - b0n); rben = dm.rbe_ptr[r];
     }
   }
   for (; wg < ngroups; wg += stride) {
@@ -107,6 +110,12 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
     const bool node_on = r < dm.nlnds;
     const int ninc_cur = ninc, e_cur = e, a_cur = a;
     const int4 rn_cur = rn;
+    const int64_t b0 = b0n, rbe = rben;
+    const int nb = nbn;
+    // the lane's first block in phase B: its list bounds travel while phase A computes
+    const uint16_t *off = dm.rb_off + b0 + r;
+    int off0 = 0, off1 = 0;
+    if (BLK && node_on && gl < nb) { off0 = off[gl]; off1 = off[gl + 1]; }
     {   // prefetch
       const int64_t rnext = (wg + stride) * NPW + gi;
       ninc = 0;
@@ -114,6 +123,7 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
         const int64_t p0 = dm.n2e_ptr[rnext];
         ninc = (int)(dm.n2e_ptr[rnext + 1] - p0);
         if (gl < ninc) fetch_inc(p0 + gl);
+        b0n = dm.bptr[rnext]; nbn = (int)(dm.bptr[rnext + 1] - b0n); rben = dm.rbe_ptr[rnext];
       }
     }
     // ---- phase A: one incident element per lane
@@ -136,11 +146,8 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
     // ---- phase B: the node's CSR values in storage order
     const unsigned on_mask = __ballot_sync(0xffffffffu, node_on);
     if (node_on) {
-      const int64_t b0 = dm.bptr[r];
-      const int nb = (int)(dm.bptr[r + 1] - b0);
       const int rowlen = PD * nb, nv = PD * rowlen;
-      const uint16_t *off = dm.rb_off + b0 + r;
-      const uint16_t *ent = dm.rb_ent + dm.rbe_ptr[r];
+      const uint16_t *ent = dm.rb_ent + rbe;
       double *vrow = vals + D2 * b0;
       double *prow[PD];   // PEER: first value of each of the node's PD rows, at its owner
       if constexpr (PEER) {
@@ -154,8 +161,8 @@ fused_rows_kernel(DevMesh dm, const double *__restrict__ u, double *__restrict__
       if constexpr (BLK) {   // one list walk per block instead of one per value
         const bool al16 = !PEER && (reinterpret_cast<size_t>(vals) & 15) == 0;
         for (int k = gl; k < nb; k += G) {
-          int c = off[k];
-          const int c1 = off[k + 1];
+          int c = k == gl ? off0 : off[k];
+          const int c1 = k == gl ? off1 : off[k + 1];
           double acc[D2];
 #pragma unroll
           for (int q = 0; q < D2; ++q) acc[q] = 0.0;
