@@ -3,8 +3,8 @@ properties (the oracle cannot finish these in seconds; small-size oracle parity 
 test_gpu_parity.py):
   C2 hex8 100^3   -- two independent algorithms (symmetric pair-block kernel, node-row kernel) agree to
                      1e-12, rigid-body modes give zero internal force, a checksum of K u;
-  C3 tet4 94^3x6  -- two-pass path: rigid-body modes, constant stress of a linear field;
-  C4 quad4 2x(1000x1000) + 1000 cohesive -- K rigid translation of each block, Jacobian = K off the
+  C3 tet4 94^3x6  -- simplex rows kernel (auto): rigid-body modes, constant stress of a linear field;
+  C4 quad4 2x(1000x1000) + 1000 cohesive -- fused rows kernel (auto): K rigid translation of each block, Jacobian = K off the
                      interface, residual finite.
 """
 import numpy as np
