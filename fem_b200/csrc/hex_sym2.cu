@@ -40,6 +40,16 @@ namespace {
 #define FEMX_SYM_KERNEL hex_sym2_kernel
 #define FEMX_SYM_LAUNCH launch_hex_sym2
 #endif
+// FEMX_SYM_GPERM = 1 (variant 12, hex_sym6.cu): gather lanes are permuted inside the 27-value run so that the 15 values
+// with more than one cell contribution sit in the lower half-warp (their 2nd..4th loads cost one wavefront, not two),
+// and f is reduced with 8 instead of 15 shuffles
+#ifndef FEMX_SYM_GPERM
+#define FEMX_SYM_GPERM 0
+#endif
+// FEMX_SYM_PROF = 1 (diagnostic build, hex_sym7.cu): thread 0 of every CTA accumulates clock64 intervals per phase
+#ifndef FEMX_SYM_PROF
+#define FEMX_SYM_PROF 0
+#endif
 constexpr int NX = FEMX_SYM_NX, NY = FEMX_SYM_NY, NP = NX * NY;   // owned node positions of a tile (8 x 6: 3 per warp in the gather)
 constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // 63 cells per layer (all cells touching the tile)
 constexpr int ELP = FEMX_SYM_ELP;             // padded cell count (thread mapping: 8 threads per cell slot)
@@ -70,6 +80,9 @@ struct Smem {
   double fcarry[NP][3];
   HexRowMeta rowmeta[4][NP];
   uint2 tab[3][32];        // gather table: [dz + 1][lane] -> four 16-bit byte offsets (row i = 0) into the scratch
+#if FEMX_SYM_GPERM
+  unsigned lanec[32];      // gather lane constants kk | jj << 4 | active << 6 | uoff << 8 (read per step: no registers held across the FMA phase)
+#endif
   int nid[8][UL];
 };
 
@@ -155,12 +168,28 @@ __device__ __forceinline__ void fetch_esc(Smem &S, const DevHex &hx, const Tile 
 }
 
 __host__ __device__ constexpr int rm_index(int lx, int ly) { return ly * 2 + lx; }   // row-major node index inside a face
+// value (kk, j) of a 27-value run (kk = neighbour (dy + 1) * 3 + dx + 1, j = column component) that gather lane l serves
+__device__ __forceinline__ bool lane_value(int l, int &kk, int &j) {
+#if FEMX_SYM_GPERM
+  // lanes 0..14: the node itself and its four edge neighbours (2..4 contributing cells); lanes 16..27: the four diagonal
+  // neighbours (one cell).  A 64-bit shared load is served half-warp by half-warp, so loads 2..4 touch one half only.
+  if (l < 15) { const int q = l / 3; kk = q < 2 ? 1 + 2 * q : (q == 2 ? 4 : 2 * q - 1); j = l % 3; return true; }
+  if (l >= 16 && l < 28) { const int q = (l - 16) / 3; kk = (q & 1) * 2 + (q >> 1) * 6; j = (l - 16) % 3; return true; }
+  kk = 8; j = 2;
+  return false;
+#else
+  const int gl = l < 27 ? l : 26;
+  kk = gl / 3; j = gl % 3;
+  return l < 27;
+#endif
+}
 // gather table entry of lane l (value (kk, j) of a 27-value run) for group g = dz + 1, scalar row i = 0; row i sits
 // +8 i bytes further for dz = -1 (transposed block) and +8 SI i bytes for dz = 0, +1
 __device__ __forceinline__ uint2 table_entry(int g, int l) {
   unsigned o[4] = {0, 0, 0, 0};
-  if (l < 27) {
-    const int kk = l / 3, j = l % 3, dy = kk / 3 - 1, dx = kk % 3 - 1;
+  int kk, j;
+  if (lane_value(l, kk, j)) {
+    const int dy = kk / 3 - 1, dx = kk % 3 - 1;
     int n = 0;
     for (int oy = 0; oy < 2; ++oy)
       for (int ox = 0; ox < 2; ++ox) {
@@ -408,6 +437,13 @@ __device__ __forceinline__ double gather_val(unsigned eb, const uint2 t, int on0
   return ((c0 + c1) + c2) + c3;
 }
 
+#if FEMX_SYM_PROF
+__device__ unsigned long long g_prof[8];
+#define PROF_MARK(i) if (tid == 0) { const long long now_ = clock64(); atomicAdd(&g_prof[i], (unsigned long long)(now_ - tprev)); tprev = now_; }
+#else
+#define PROF_MARK(i)
+#endif
+
 __device__ __forceinline__ bool v_dummy(const double *p) { return p == nullptr; }   // diagnostic: never true
 
 }  // namespace
@@ -433,12 +469,20 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 #if FEMX_SYM_TPC == 8
   const bool top = type >= 2, isy = (type & 1) != 0;
 #endif
+#if !FEMX_SYM_GPERM
   // gather-phase lane constants
-  const int gl = lane < 27 ? lane : 26;
-  const int kk = gl / 3, jj = gl % 3;
+  int kk, jj;
+  const bool lact = lane_value(lane, kk, jj);
   const int uoff = ((kk / 3) * UX + (kk % 3)) * 3 + jj;   // halo'd node (px + dx + 1, py + dy + 1), component j
   // cells contributing to this lane's value: 4 around the node itself, 2 along an edge neighbour, 1 for a diagonal one
-  const int c_on0 = lane < 27, c_on1 = lane < 27 && (kk & 1 || kk == 4), c_on2 = lane < 27 && kk == 4;
+  const int c_on0 = lact, c_on1 = lact && (kk & 1 || kk == 4), c_on2 = lact && kk == 4;
+#else
+  if (tid < 32) {
+    int k_, j_;
+    const bool a_ = lane_value(tid, k_, j_);
+    S.lanec[tid] = (unsigned)k_ | (unsigned)j_ << 4 | (a_ ? 64u : 0u) | (unsigned)(((k_ / 3) * UX + (k_ % 3)) * 3 + j_) << 8;
+  }
+#endif
 
   if (CTAS > 1 && (dbg >> 8) > 0) {   // diagnostic: start the second resident CTA of an SM (dbg >> 8) x 256 clocks late
     const int lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
@@ -452,12 +496,18 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   __syncthreads();
   fetch_layer<WITH_F>(S, hx, T, u, T.l0 - 1, tid); fetch_layer<WITH_F>(S, hx, T, u, T.l0, tid);
 
+#if FEMX_SYM_PROF
+  long long tprev = clock64();
+#endif
   for (int it = 0; it < nsteps; ++it) {
     const int m = T.l0 - 1 + it;
     cp_async_wait_all();
     __syncthreads();              // layer data of m, m+1 is in; the previous gather has left the scratch
+    PROF_MARK(0)
     if (!(dbg & 1)) geometry(S, m, tid);
+    PROF_MARK(1)
     __syncthreads();
+    PROF_MARK(2)
     // prefetch for the next step: ids of m+3, node layer m+2, cell scale of m+1
     fetch_nid(S, hx, T, m + 3, tid);
     fetch_layer<WITH_F>(S, hx, T, u, m + 2, tid);
@@ -508,7 +558,9 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
         }
       }
     }
+    PROF_MARK(3)
     __syncthreads();              // everybody has left the gradient buffer
+    PROF_MARK(4)
     // ------------------------------------------------------------------ G' -> K, park in the scratch
     {
       double *sc = &S.a.scr[es * SS];
@@ -613,11 +665,19 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
       }
     }
 #endif
+    PROF_MARK(5)
     __syncthreads();
+    PROF_MARK(6)
     // ------------------------------------------------------------------ gather: rows of node layer m (dz = 0, +1) and m+1 (dz = -1)
     const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
     if (!(dbg & 4)) {
       const uint2 t0 = S.tab[0][lane], t1 = S.tab[1][lane], t2 = S.tab[2][lane];
+#if FEMX_SYM_GPERM
+      const unsigned lc = S.lanec[lane];
+      const int kk = lc & 15, jj = (lc >> 4) & 3, uoff = lc >> 8;
+      const bool lact = (lc & 64u) != 0;
+      const int c_on0 = lact, c_on1 = lact && (kk & 1 || kk == 4), c_on2 = lact && kk == 4;
+#endif
       const bool upper = (lane & 16) != 0;
 #pragma unroll
       for (int n = wu; n < NP; n += NW) {
@@ -628,7 +688,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
         // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
         const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
         const bool st = !(dbg & 8) || v_dummy(vals);
-        const bool on0 = st && act_hi && lane < 27 && k0 != 255, on1 = st && act_lo && lane < 27 && k1 != 255, on2 = st && act_lo && lane < 27 && k2 != 255;
+        const bool on0 = st && act_hi && lact && k0 != 255, on1 = st && act_lo && lact && k1 != 255, on2 = st && act_lo && lact && k2 != 255;
         double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
         const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
         bool remote = false;     // PEER: one of the two nodes' rows lives on another rank (3 % of the nodes)
@@ -662,31 +722,42 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
             const double flo = fma(v[i * 3 + 1], ulo, v[i * 3 + 2] * uhi), fhi = v[i * 3 + 0] * ulo;
             keep[i] = (upper ? fhi : flo) + __shfl_xor_sync(0xffffffffu, upper ? flo : fhi, 16);
           }
+#if FEMX_SYM_GPERM
+          // 3 sums over 16 lanes with 5 shuffles: after the xor-8 stage a lane carries two of them, after xor-4 one
+          // (lanes 0-3 of a half: component 0, 4-7: component 1, 8-11: component 2)
+          const bool b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
+          const double r0 = __shfl_xor_sync(0xffffffffu, b3 ? keep[0] : keep[2], 8);
+          const double r1 = __shfl_xor_sync(0xffffffffu, keep[1], 8);
+          const double x0 = (b3 ? keep[2] : keep[0]) + r0, x1 = b3 ? 0.0 : keep[1] + r1;
+          double mine = (b2 ? x1 : x0) + __shfl_xor_sync(0xffffffffu, b2 ? x0 : x1, 4);
+          mine += __shfl_xor_sync(0xffffffffu, mine, 2);
+          mine += __shfl_xor_sync(0xffffffffu, mine, 1);
+          const int li = (lane & 15) >> 2;
+          const bool wr = (lane & 3) == 0 && li < 3;
+#else
 #pragma unroll
           for (int d = 8; d >= 1; d >>= 1)
 #pragma unroll
             for (int i = 0; i < 3; ++i) keep[i] += __shfl_xor_sync(0xffffffffu, keep[i], d);
           const int li = lane & 15;
-          if (li < 3) {
-            const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
-            // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
-            if (!upper && act_lo) {
-              double *fp = fint + ((long long)rlo->grow + li);
-              if constexpr (PEER) {
-                const long long o = 3ll * S.nid[m & 7][(py + 1) * UX + px + 1] + li;
-                if (!peer_local_f(pt, o)) fp = peer_f(pt, fp, o);
-              }
-              *fp = S.fcarry[n][li] + mine;
+          const bool wr = li < 3;
+          const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
+#endif
+          // f of the lower node = (dz = -1 part carried from the previous step) + (dz = 0, +1 parts)
+          if (wr && !upper && act_lo) {
+            double *fp = fint + ((long long)rlo->grow + li);
+            if constexpr (PEER) {
+              const long long o = 3ll * S.nid[m & 7][(py + 1) * UX + px + 1] + li;
+              if (!peer_local_f(pt, o)) fp = peer_f(pt, fp, o);
             }
+            *fp = S.fcarry[n][li] + mine;
           }
           __syncwarp();
-          if (li < 3 && upper) {
-            const double mine = li == 0 ? keep[0] : (li == 1 ? keep[1] : keep[2]);
-            S.fcarry[n][li] = act_hi ? mine : 0.0;
-          }
+          if (wr && upper) S.fcarry[n][li] = act_hi ? mine : 0.0;
         }
       }
     }
+    PROF_MARK(7)
   }
 }
 
@@ -732,6 +803,21 @@ int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
   }
 #endif
   if (d_u) go(FEMX_SYM_KERNEL<true, false>); else go(FEMX_SYM_KERNEL<false, false>);
+#if FEMX_SYM_PROF
+  {
+    static const char *nm[8] = {"wait top", "geometry", "wait", "fetch + FMA", "wait", "G' -> K + scratch", "wait", "gather"};
+    unsigned long long h[8], z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaStreamSynchronize(c->stream);
+    cudaMemcpyFromSymbol(h, g_prof, sizeof(h));
+    cudaMemcpyToSymbol(g_prof, z, sizeof(z));
+    const double steps = (double)grid.x * grid.y * grid.z * (LZ + 1);
+    double tot = 0;
+    for (int i = 0; i < 8; ++i) tot += (double)h[i];
+    fprintf(stderr, "femx prof (warp 0, cycles per CTA step, %.0f CTA steps):", steps);
+    for (int i = 0; i < 8; ++i) fprintf(stderr, " %s %.0f |", nm[i], (double)h[i] / steps);
+    fprintf(stderr, " total %.0f\n", tot / steps);
+  }
+#endif
   return 1;
 }
 

@@ -24,7 +24,7 @@ def test_c2_hex100_cross_variant_and_rigid_modes():
     m = mg.jitter(mg.hex_cube(100, clamp=False))
     u = mg.displacement_field(m)
     out = {}
-    for var in (5, 3):
+    for var in (5, 3, 12, 13):
         with api.Femx(assembly_variant=var) as f:
             f.set_mesh(m).build_plan()
             vals, fint = f.assemble_K_fint(u)
@@ -38,6 +38,10 @@ def test_c2_hex100_cross_variant_and_rigid_modes():
     assert np.abs(out[5][0] - out[3][0]).max() <= 1e-12 * scale
     assert _rel(out[5][1], out[3][1]) <= 1e-12
     assert np.isfinite(out[5][0]).all()
+    # variant 12 (permuted gather lanes): every matrix value sums the same contributions in the same order -> same bits
+    for var in (12, 13):
+        assert np.array_equal(out[var][0], out[5][0]), var
+        assert _rel(out[var][1], out[5][1]) <= 1e-12, var
 
 
 def test_c3_tet94_rigid_modes_and_constant_stress():

@@ -405,7 +405,7 @@ def test_fused_hex_variant_vs_oracle_and_twopass(orc):
                 assert close(v3, va_o, TOL_MAT), (name, "ws", lz)
                 assert close(f3int, f_o, TOL_MAT), (name, "ws", lz)
                 assert np.array_equal(f3.assemble_K(), v3), (name, "ws", lz)
-        for var, lz in ((5, 0), (5, 25), (5, 3), (6, 0), (6, 25), (6, 3), (7, 0), (7, 25), (7, 3), (8, 0), (8, 3)):   # symmetric pair-block kernels
+        for var, lz in ((5, 0), (5, 25), (5, 3), (6, 0), (6, 25), (6, 3), (7, 0), (7, 25), (7, 3), (8, 0), (8, 3), (12, 0), (12, 25), (12, 3), (13, 0), (13, 25), (13, 3)):   # symmetric pair-block kernels
             with api.Femx(assembly_variant=var, lz=lz) as f4:
                 f4.set_mesh(m).build_plan()
                 v4, f4int = f4.assemble_K_fint(u)
