@@ -438,7 +438,7 @@ __device__ __forceinline__ double gather_val(unsigned eb, const uint2 t, int on0
 }
 
 #if FEMX_SYM_PROF
-__device__ unsigned long long g_prof[8];
+__device__ unsigned long long g_prof[10];
 #define PROF_MARK(i) if (tid == 0) { const long long now_ = clock64(); atomicAdd(&g_prof[i], (unsigned long long)(now_ - tprev)); tprev = now_; }
 #else
 #define PROF_MARK(i)
@@ -465,7 +465,16 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   // FMA-phase role (two warps each): 0/1 = bottom-face threads X/Y (finish the face started one layer below),
   // 2/3 = top-face threads X/Y (start the next face), 4..7 = 2 x 2 bottom x top blocks
   const int type = wu >> (WPT - 1);
+#if FEMX_SYM_GPERM && FEMX_SYM_TPC == 8 && FEMX_SYM_ELP == 64
+  // bottom x top warps (8..15): 16 cells x the two column pairs b0 of one row pair a0, so that lanes l and l + 16 read the
+  // same bottom-node operands (a 128-bit load with 16 distinct addresses costs two wavefronts instead of four)
+  const bool bt = type >= 4;
+  const int es = bt ? (wu & 3) * 16 + (lane & 15) : (w & (WPT - 1)) * 32 + lane;
+  const int bt_a0 = ((wu >> 2) & 1) * 2, bt_b0 = (lane >> 4) * 2;
+#else
   const int es = (w & (WPT - 1)) * 32 + lane;
+  const int bt_a0 = ((type - 4) >> 1) * 2, bt_b0 = ((type - 4) & 1) * 2;
+#endif
 #if FEMX_SYM_TPC == 8
   const bool top = type >= 2, isy = (type & 1) != 0;
 #endif
@@ -512,6 +521,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
     fetch_nid(S, hx, T, m + 3, tid);
     fetch_layer<WITH_F>(S, hx, T, u, m + 2, tid);
     fetch_esc(S, hx, T, m + 1, tid);
+    PROF_MARK(8)
 
     // ------------------------------------------------------------------ FMA phase
     const bool cell_on = S.esc[m & 3][es] != 0.0;
@@ -549,7 +559,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 #pragma unroll
       for (int q = 0; q < 40; ++q) acc[q] = 0.0;
       if (cell_on && !(dbg & 2)) {
-        const int a0 = ((type - 4) >> 1) * 2, b0 = ((type - 4) & 1) * 2;
+        const int a0 = bt_a0, b0 = bt_b0;
 #pragma unroll 2
         for (int ip = 0; ip < 8; ++ip) {
           double va[3][2], vb[3][2];
@@ -582,7 +592,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
           for (int q = 0; q < 20; ++q) S.carry[isy][q][es] = make_double2(acc[2 * q], acc[2 * q + 1]);
         }
       } else {
-        const int a0 = ((type - 4) >> 1) * 2, b0 = ((type - 4) & 1) * 2;
+        const int a0 = bt_a0, b0 = bt_b0;
 #pragma unroll
         for (int p = 0; p < 4; ++p) to_k_block(&acc[p * 9], rho);
 #pragma unroll
@@ -689,7 +699,12 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
         const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
         const bool st = !(dbg & 8) || v_dummy(vals);
         const bool on0 = st && act_hi && lact && k0 != 255, on1 = st && act_lo && lact && k1 != 255, on2 = st && act_lo && lact && k2 != 255;
+#if FEMX_SYM_GPERM
+        // value slots fit 32 bits (the CSR row pointers are int32): one IMAD.WIDE.U32 per store address
+        const unsigned q0 = (unsigned)rhi->base + 3u * k0 + jj, q1 = (unsigned)rlo->base + 3u * k1 + jj, q2 = (unsigned)rlo->base + 3u * k2 + jj;
+#else
         double *p0 = vals + (rhi->base + 3 * k0 + jj), *p1 = vals + (rlo->base + 3 * k1 + jj), *p2 = vals + (rlo->base + 3 * k2 + jj);
+#endif
         const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
         bool remote = false;     // PEER: one of the two nodes' rows lives on another rank (3 % of the nodes)
         if constexpr (PEER)
@@ -706,9 +721,15 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
             if (on1) b[3 * k1 + jj] = v[i * 3 + 1];
             if (on2) b[3 * k2 + jj] = v[i * 3 + 2];
           } else {
+#if FEMX_SYM_GPERM
+            if (on0) vals[q0 + (unsigned)(i * rs_hi)] = v[i * 3 + 0];
+            if (on1) vals[q1 + (unsigned)(i * rs_lo)] = v[i * 3 + 1];
+            if (on2) vals[q2 + (unsigned)(i * rs_lo)] = v[i * 3 + 2];
+#else
             if (on0) p0[i * rs_hi] = v[i * 3 + 0];
             if (on1) p1[i * rs_lo] = v[i * 3 + 1];
             if (on2) p2[i * rs_lo] = v[i * 3 + 2];
+#endif
           }
         }
         if (WITH_F && !(dbg & 16)) {
@@ -805,16 +826,16 @@ int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
   if (d_u) go(FEMX_SYM_KERNEL<true, false>); else go(FEMX_SYM_KERNEL<false, false>);
 #if FEMX_SYM_PROF
   {
-    static const char *nm[8] = {"wait top", "geometry", "wait", "fetch + FMA", "wait", "G' -> K + scratch", "wait", "gather"};
-    unsigned long long h[8], z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    static const char *nm[10] = {"wait top", "geometry", "wait", "FMA", "wait", "G' -> K + scratch", "wait", "gather", "fetch", "-"};
+    unsigned long long h[10], z[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     cudaStreamSynchronize(c->stream);
     cudaMemcpyFromSymbol(h, g_prof, sizeof(h));
     cudaMemcpyToSymbol(g_prof, z, sizeof(z));
     const double steps = (double)grid.x * grid.y * grid.z * (LZ + 1);
     double tot = 0;
-    for (int i = 0; i < 8; ++i) tot += (double)h[i];
+    for (int i = 0; i < 10; ++i) tot += (double)h[i];
     fprintf(stderr, "femx prof (warp 0, cycles per CTA step, %.0f CTA steps):", steps);
-    for (int i = 0; i < 8; ++i) fprintf(stderr, " %s %.0f |", nm[i], (double)h[i] / steps);
+    for (int i = 0; i < 9; ++i) fprintf(stderr, " %s %.0f |", nm[i], (double)h[i] / steps);
     fprintf(stderr, " total %.0f\n", tot / steps);
   }
 #endif
