@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BYTES_PER_EL = {"hex8": 2074.0}
-KERNEL_NAME = {0: "hex_sym2_kernel", 1: "elem_rows_kernel + gather_rows_kernel", 2: "hex_fused_kernel", 3: "hex_ws_kernel",
+KERNEL_NAME = {0: "hex_sym6_kernel", 1: "elem_rows_kernel + gather_rows_kernel", 2: "hex_fused_kernel", 3: "hex_ws_kernel",
                4: "hex_sym5_kernel", 5: "hex_sym2_kernel", 6: "hex_sym3_kernel", 7: "hex_sym4_kernel", 8: "hex_sym5_kernel", 12: "hex_sym6_kernel", 13: "hex_sym7_kernel"}   # conn 32 + mat 4 + coords 24.73 + u 24.73 + K 1963.5 + R 24.73
 
 

@@ -48,7 +48,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (u_local && (rc = stage_in(c, u_local, nloc, where, &c->d_u, &d_u))) return rc;
   if ((rc = stage_out(c, vals, c->nnz, where, &c->d_vals, &d_vals))) return rc;
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
-  // auto (0): the 16-warp symmetric tile kernel for a logical hex8 grid, else the fused rows kernel, else two-pass
+  // auto (0): the 16-warp symmetric tile kernel with permuted gather lanes (12) for a logical hex8 grid, else the fused rows kernel, else two-pass
   const int av0 = c->opts.assembly_variant;
   const bool fused = c->hex.ok && av0 != 1 && av0 != 9 && av0 != 11;
   const bool simplex = !fused && av0 != 1 && av0 != 9 && rows_simplex_ok(c);   // pure tri3 / tet4 mesh
@@ -56,9 +56,9 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
   if (av0 == 11 && !simplex) { c->err = "simplex rows kernel: needs a pure tri3 / tet4 mesh with at most 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
   const bool peer = c->peer.connected;
-  // peer exchange: reserved[3] = 1 lets the assembly kernel store interface rows at their owner itself (variants 0, 5, 9);
+  // peer exchange: reserved[3] = 1 lets the assembly kernel store interface rows at their owner itself (variants 0, 5, 12, 9);
   // default is the push kernel behind the unchanged assembly kernel
-  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5) : (rows || simplex));
+  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5 || av0 == 12) : (rows || simplex));
   c->peer.in_kernel = peer_fused;
   if (!fused && !rows && !simplex) {
     if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
@@ -67,7 +67,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
-    const int av = av0 == 0 ? 5 : av0;
+    const int av = av0 == 0 ? 12 : av0;
     c->launches += av == 13 ? launch_hex_sym7(c, d_u, d_vals, d_fint) : av == 12 ? launch_hex_sym6(c, d_u, d_vals, d_fint) : av == 8 ? launch_hex_sym5(c, d_u, d_vals, d_fint) : av == 7 ? launch_hex_sym4(c, d_u, d_vals, d_fint)
                    : av == 6 ? launch_hex_sym3(c, d_u, d_vals, d_fint) : av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint)
                    : av == 4 ? launch_hex_sym5(c, d_u, d_vals, d_fint)   /* the first 8-warp kernel lives on as variant 8 */

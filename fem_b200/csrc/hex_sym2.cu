@@ -65,7 +65,11 @@ constexpr int SS = 297;                       // doubles per cell of scratch (od
 // as rows [node a][i] of 12 doubles [node b][j], nodes in row-major (ly, lx) order, node pitch 37, row pitch 12.  Found by
 // exhaustive search: with these pitches every gather load (27 / 15 / 3 lanes) is within one wavefront of conflict-free.
 constexpr int FACE_OFF = 0, BT_OFF = 148, SA = 37, SI = 12;
+#if FEMX_SYM_GPERM
+constexpr int XP = 43;                        // doubles per row of the coordinate layer (30 used): 43 = 27 = 3 * EX mod 16, so cell slot es sits at bank 3 es mod 16 and the 16 cells of a half-warp hit 16 distinct banks
+#else
 constexpr int XP = 40;                        // doubles per row of the coordinate layer (27 used; 40 = 8 mod 16 keeps two cell rows on distinct banks)
+#endif
 static_assert(EL <= ELP && (ELP == 32 || ELP == 64), "thread mapping assumes 32 or 64 cell slots");
 
 struct Smem {
@@ -689,10 +693,25 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
       const int c_on0 = lact, c_on1 = lact && (kk & 1 || kk == 4), c_on2 = lact && kk == 4;
 #endif
       const bool upper = (lane & 16) != 0;
+#if FEMX_SYM_GPERM
+      static_assert(NP % NW == 0, "every warp gathers the same number of node positions");
+#pragma unroll
+      for (int q = 0; q < NP / NW; ++q) {     // constant trip count: the node iterations of a warp can overlap
+        const int n = wu + q * NW;
+#else
 #pragma unroll
       for (int n = wu; n < NP; n += NW) {
+#endif
         const int px = n % NX, py = n / NX;
         const unsigned eb = (unsigned)__cvta_generic_to_shared(&S.a.scr[(py * EX + px) * SS]);
+#if FEMX_SYM_GPERM
+        // displacement operands of f first: the predicated scratch loads below are volatile, nothing moves across them
+        double ulo = 0.0, uhi = 0.0;
+        if (WITH_F && !(dbg & 16)) {
+          ulo = (&S.ulay[m & 3][0][0])[(py * UX + px) * 3 + uoff];
+          uhi = (&S.ulay[(m + 1) & 3][0][0])[(py * UX + px) * 3 + uoff];
+        }
+#endif
         const HexRowMeta *rlo = &S.rowmeta[m & 3][n], *rhi = &S.rowmeta[(m + 1) & 3][n];
         const bool act_lo = lay_lo && rlo->nb > 0, act_hi = lay_hi && rhi->nb > 0;
         // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
@@ -735,8 +754,10 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
         if (WITH_F && !(dbg & 16)) {
           // f_r = sum_c K_rc u_c: lane products, butterfly-summed (fixed order); lanes 0-15 end up with the three
           // sums of the lower node, lanes 16-31 with those of the upper node
+#if !FEMX_SYM_GPERM
           const double ulo = (&S.ulay[m & 3][0][0])[(py * UX + px) * 3 + uoff];
           const double uhi = (&S.ulay[(m + 1) & 3][0][0])[(py * UX + px) * 3 + uoff];
+#endif
           double keep[3];
 #pragma unroll
           for (int i = 0; i < 3; ++i) {

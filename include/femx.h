@@ -61,14 +61,15 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh (5 for a logical hex8 grid, 11 for a pure tri3 / tet4
+/* assembly variants: 0 = best available for the mesh (12 for a logical hex8 grid, 11 for a pure tri3 / tet4
  * mesh, else 9, else 1),
  * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
  * 3 = its warp-specialised form, 5 = symmetric pair-block kernel on 16 warps (6, 7, 8: its measured tile / thread
- * variants, 4 = alias of 8), 9 = fused rows kernel for any element mix, 11 = simplex rows kernel (tri3 / tet4 only) */
+ * variants, 4 = alias of 8), 12 = variant 5 with the gather lanes ordered by contribution count (13: the same with
+ * per-phase clock accounting on stderr), 9 = fused rows kernel for any element mix, 11 = simplex rows kernel (tri3 / tet4 only) */
 typedef struct {
   int quirks;            /* FEMX_Q_* bits                                   */
-  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8 hex8 tile kernels, 9 fused rows, 11 simplex rows */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8, 12, 13 hex8 tile kernels, 9 fused rows, 11 simplex rows */
   int reserved[6];
 } femx_opts;
 
@@ -186,7 +187,7 @@ int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b,
  * are the contiguous local value range [val_bounds[q], val_bounds[q+1]) and the internal-force entries (numbered
  * pdim*local_node + i) the range [f_bounds[q], f_bounds[q+1]).  After femx_peer_connect, femx_assemble_K /
  * femx_assemble_K_fint push those ranges into rank q's receive arena over NVLink (remote stores of a kernel behind
- * the assembly kernel; with opts.reserved[3] = 1 and variants 0, 5, 9 the assembly kernel stores them there itself
+ * the assembly kernel; with opts.reserved[3] = 1 and variants 0, 5, 12, 9 the assembly kernel stores them there itself
  * and the non-owned ranges of the local arrays are not written), at val_dst[q] / f_dst[q] doubles from the start of
  * q's value / force receive area, and the call ends with a device-side step barrier among the ranks: at return the
  * rank's own slice of `vals` (and the owned rows of `fint`) plus everything its peers sent are complete.
