@@ -50,6 +50,9 @@ namespace {
 #ifndef FEMX_SYM_PROF
 #define FEMX_SYM_PROF 0
 #endif
+#ifndef FEMX_SYM_IPU
+#define FEMX_SYM_IPU 2    // unroll factor of the integration-point loops of the FMA phase (variant 12 uses 1; 4 spills: DESIGN 4.1a)
+#endif
 constexpr int NX = FEMX_SYM_NX, NY = FEMX_SYM_NY, NP = NX * NY;   // owned node positions of a tile (8 x 6: 3 per warp in the gather)
 constexpr int EX = NX + 1, EY = NY + 1, EL = EX * EY;   // 63 cells per layer (all cells touching the tile)
 constexpr int ELP = FEMX_SYM_ELP;             // padded cell count (thread mapping: 8 threads per cell slot)
@@ -58,6 +61,7 @@ constexpr int CTAS = FEMX_SYM_CTAS;           // resident CTAs per SM
 constexpr int UX = NX + 2, UY = NY + 2, UL = UX * UY;   // node positions per layer incl. halo
 constexpr int TPC = FEMX_SYM_TPC;              // threads per cell in the FMA phase: 8 (39 / 36 accumulators) or 4 (78 / 72)
 constexpr int NT = TPC * ELP;
+constexpr int IPU = FEMX_SYM_IPU;             // unroll factor of the FMA phase's integration-point loops
 constexpr int NW = NT / 32;
 constexpr int GS = 194;                       // doubles per cell in the gradient buffer (8 ip x 24 + 2; 16-byte stride odd)
 constexpr int SS = 297;                       // doubles per cell of scratch (odd: cell-strided 8-byte stores hit 16 distinct banks)
@@ -544,14 +548,14 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
       if (cell_on && need && !(dbg & 2)) {
         const double *gf = g + (top ? 4 : 0);
         if (isy) {
-#pragma unroll 2
+#pragma unroll IPU
           for (int ip = 0; ip < 8; ++ip) {
             double v[3][3];
             load_face_y(gf + ip * 24, v);
             fma_face_y(v, acc);
           }
         } else {
-#pragma unroll 2
+#pragma unroll IPU
           for (int ip = 0; ip < 8; ++ip) {
             double v[3][4];
             load_face_x(gf + ip * 24, v);
@@ -564,7 +568,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
       for (int q = 0; q < 40; ++q) acc[q] = 0.0;
       if (cell_on && !(dbg & 2)) {
         const int a0 = bt_a0, b0 = bt_b0;
-#pragma unroll 2
+#pragma unroll IPU
         for (int ip = 0; ip < 8; ++ip) {
           double va[3][2], vb[3][2];
           load_bt(g + ip * 24, a0, b0, va, vb);

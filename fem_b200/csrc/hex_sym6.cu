@@ -9,6 +9,7 @@
 #define FEMX_SYM_CTAS 1
 #define FEMX_SYM_TPC 8
 #define FEMX_SYM_GPERM 1
+#define FEMX_SYM_IPU 1
 #define FEMX_SYM_KERNEL hex_sym6_kernel
 #define FEMX_SYM_LAUNCH launch_hex_sym6
 #include "hex_sym2.cu"

@@ -8,6 +8,7 @@
 #define FEMX_SYM_TPC 8
 #define FEMX_SYM_GPERM 1
 #define FEMX_SYM_PROF 1
+#define FEMX_SYM_IPU 1
 #define FEMX_SYM_KERNEL hex_sym7_kernel
 #define FEMX_SYM_LAUNCH launch_hex_sym7
 #include "hex_sym2.cu"
