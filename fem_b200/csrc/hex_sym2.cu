@@ -527,11 +527,13 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
     PROF_MARK(2)
     // prefetch for the next step: ids of m+3, node layer m+2, cell scale of m+1
 #if FEMX_SYM_GPERM && FEMX_SYM_TPC == 8 && FEMX_SYM_ELP == 64 && !defined(FEMX_SYM_FETCH_LOW)
-    // issued by bottom x top warps 8-10 (36 instead of 39 FMA per point, shared operand loads): they reach the barrier first
-    if (wu >= 8 && wu < 8 + (UL + 31) / 32) {
-      fetch_nid(S, hx, T, m + 3, tid - 256);
-      fetch_layer<WITH_F>(S, hx, T, u, m + 2, tid - 256);
-      fetch_esc(S, hx, T, m + 1, tid - 256);
+    // issued by the bottom x top warps (36 instead of 39 FMA per point, shared operand loads: they reach the barrier first):
+    // node layer by warps 8-10, node ids by 11-13, cell scale by 14-15
+    static_assert(UL <= 96 && ELP <= 64, "three warps per prefetch role");
+    if (wu >= 8) {
+      if (wu < 11) fetch_layer<WITH_F>(S, hx, T, u, m + 2, tid - 256);
+      else if (wu < 14) fetch_nid(S, hx, T, m + 3, tid - 352);
+      else fetch_esc(S, hx, T, m + 1, tid - 448);
     }
 #else
     fetch_nid(S, hx, T, m + 3, tid);
