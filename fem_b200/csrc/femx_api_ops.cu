@@ -68,7 +68,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
     const int av = av0 == 0 ? 12 : av0;
-    c->launches += av == 20 ? launch_hex_mma(c, d_u, d_vals, d_fint) : av == 13 ? launch_hex_sym7(c, d_u, d_vals, d_fint) : av == 12 ? launch_hex_sym6(c, d_u, d_vals, d_fint) : av == 8 ? launch_hex_sym5(c, d_u, d_vals, d_fint) : av == 7 ? launch_hex_sym4(c, d_u, d_vals, d_fint)
+    c->launches += av == 20 ? launch_hex_mma(c, d_u, d_vals, d_fint) : av == 21 ? launch_hex_mma_prof(c, d_u, d_vals, d_fint) : av == 13 ? launch_hex_sym7(c, d_u, d_vals, d_fint) : av == 12 ? launch_hex_sym6(c, d_u, d_vals, d_fint) : av == 8 ? launch_hex_sym5(c, d_u, d_vals, d_fint) : av == 7 ? launch_hex_sym4(c, d_u, d_vals, d_fint)
                    : av == 6 ? launch_hex_sym3(c, d_u, d_vals, d_fint) : av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint)
                    : av == 4 ? launch_hex_sym5(c, d_u, d_vals, d_fint)   /* the first 8-warp kernel lives on as variant 8 */
                    : (av == 3 ? launch_hex_ws(c, d_u, d_vals, d_fint) : launch_hex_fused(c, d_u, d_vals, d_fint));

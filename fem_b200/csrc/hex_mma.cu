@@ -37,11 +37,19 @@ namespace {
 #ifndef FEMX_MMA_NYT
 #define FEMX_MMA_NYT 13
 #endif
+// FEMX_MMA_PROF = 1 (diagnostic build, hex_mma_prof.cu = variant 21): lane 0 of every warp accumulates clock64 intervals per phase
+#ifndef FEMX_MMA_PROF
+#define FEMX_MMA_PROF 0
+#endif
+#ifndef FEMX_MMA_KERNEL
+#define FEMX_MMA_KERNEL hex_mma_kernel
+#define FEMX_MMA_LAUNCH launch_hex_mma
+#endif
 constexpr int NXT = 7, EXC = NXT + 1;            // owned node columns, cell columns (= MMA warps)
 constexpr int NYT = FEMX_MMA_NYT, EYC = NYT + 1; // owned node rows, cell rows
 constexpr int UX = NXT + 2, UY = NYT + 2, UL = UX * UY;   // node positions of a layer incl. halo
 constexpr int NP = NXT * NYT;
-constexpr int NMW = 8, NGW = 8, NT = 32 * (NMW + NGW);
+constexpr int NMW = 8, NGW = 8, NT = 32 * (NMW + NGW);   // MMA and gather warps
 constexpr int RING = 4;                          // cell rows in flight between the MMA and the gather warps
 constexpr int LR = 3, NR = 4;                    // node-layer ring, node-id ring
 constexpr int TP = 36, CP = 6 * TP, SP = 1729;   // doubles per tile / cell / ring slot (annealed against bank conflicts, tools/hex_mma_anneal.py)
@@ -96,18 +104,16 @@ __device__ __forceinline__ bool mbar_try(unsigned long long *b, unsigned parity)
                : "=r"(ok) : "r"(saddr(b)), "r"(parity) : "memory");
   return ok != 0;
 }
-// a protocol error must not hang the GPU: give up after ~2 s and trap
-__device__ __noinline__ void mbar_wait_slow(unsigned long long *b, unsigned parity) {
-  const long long t0 = clock64();
-  while (!mbar_try(b, parity))
-    if (clock64() - t0 > 4000000000ll) {
-      printf("femx hex_mma_kernel: mbarrier wait timed out (block %d %d %d, thread %d, barrier offset %u, parity %u)\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x, saddr(b), parity);
-      __trap();
-    }
-}
+// a protocol error must not hang the GPU: give up after 2^22 failed polls (try_wait suspends the thread for a hardware-defined
+// interval each time, so this is a fraction of a second) and trap.  Inline on purpose: a call in the wait path would spill
+// the accumulators around it.
 __device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity) {
-  if (!mbar_try(b, parity)) mbar_wait_slow(b, parity);
+  if (mbar_try(b, parity)) return;
+  unsigned n = 0;
+  while (!mbar_try(b, parity)) {
+    __nanosleep(40);                     // polling goes through the shared-memory pipe the working warps need
+    if (++n > (1u << 22)) __trap();
+  }
 }
 __device__ __forceinline__ void dmma(double &c0, double &c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
@@ -160,6 +166,19 @@ __device__ __forceinline__ unsigned gather_off(int par, int g, int c, int i, int
 struct Tile {
   int i0, j0, l0, l1;
 };
+
+#if FEMX_MMA_PROF
+// MMA warps: 0 wait layer, 1 geometry, 2 carry + z-in, 3 operands + DMMA, 4 wait ring slot, 5 emit + z-out + arrive
+// gather warps: 8 wait layer, 9 prefetch, 10 wait cell row, 11 metadata + loads, 12 stores, 13 f, 14 arrive
+__device__ unsigned long long g_prof[24];
+#define PROF_DECL long long tprev = clock64(); long long pacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define PROF_MARK(i) { const long long now_ = clock64(); pacc[(i) & 7] += now_ - tprev; tprev = now_; }
+#define PROF_FLUSH(base) if (lane == 0) { for (int i_ = 0; i_ < 8; ++i_) atomicAdd(&g_prof[(base) + i_], (unsigned long long)pacc[i_]); }
+#else
+#define PROF_DECL long long tprev = 0; long long pacc[1] = {0};
+#define PROF_MARK(i)
+#define PROF_FLUSH(base)
+#endif
 
 // ------------------------------------------------------------------------------------------------ node-layer prefetch
 // (issued by the 256 threads of the gather warps; gt = thread index among them)
@@ -275,30 +294,35 @@ struct MmaLane {           // per-lane constants of an MMA warp
 
 // one cell of an MMA warp's column.  P = parity of the cell's +y nodes (cy + 1) & 1; acc[t][s]: tile t, column 2 q + s.
 template <int P>
-__device__ __forceinline__ void mma_cell(Smem &S, double (&acc)[6][2], const MmaLane &L, const double *gcell, double *zcell, double *rcell,
-                                         bool on, bool first_in_column, bool zin, double rho, unsigned long long *bar_empty, bool wait_empty,
-                                         unsigned empty_parity, unsigned long long *bar_full, int lane) {
-  const bool keep = !first_in_column && (L.m & 1) == 1 - P;   // pairs on the face shared with the previous cell stay in the accumulators
+__device__ __forceinline__ void mma_cell(Smem &S, double (&acc)[6][2], const MmaLane &L, const double *gcell, int cx, unsigned rc, int cy,
+                                         bool on, bool zin, double rho, int lane, long long &tprev, long long *pacc, int dbg) {
+  const bool rowmy = (L.m & 1) != P;                          // row node on the -y face of this cell
+  const bool keep = cy > 0 && (L.m & 1) == 1 - P;             // pairs on the face shared with the previous cell stay in the accumulators
+  double *zcell = &S.zc[cx][cy][0];
 #pragma unroll
   for (int t = 0; t < 6; ++t) {
     acc[t][P] = 0.0;
     if (!keep) acc[t][1 - P] = 0.0;
   }
-  const bool rowmy = (L.m & 1) != P;                          // row node on the -y face of this cell
-  if (zin && L.m < 4 && L.q < 2) {                            // bottom x bottom pairs start from the top x top sums of the cell below
-    const int zA = L.m * 2 + L.q, zB = 8 + (L.m >> 1) * 2 + L.q;
+  if (zin && L.m < 4 && L.q < 2 && !(dbg & 4)) {              // bottom x bottom pairs start from the top x top sums of the cell below
+    const double2 *zA = reinterpret_cast<const double2 *>(zcell + (L.m * 2 + L.q) * 6), *zB = reinterpret_cast<const double2 *>(zcell + (8 + (L.m >> 1) * 2 + L.q) * 6);
 #pragma unroll
-    for (int t = 0; t < 6; ++t) {
-      acc[t][1 - P] += zcell[t * ZT + zA];
-      if (rowmy) acc[t][P] += zcell[t * ZT + zB];
+    for (int k = 0; k < 3; ++k) {
+      const double2 a = zA[k];
+      acc[2 * k][1 - P] += a.x; acc[2 * k + 1][1 - P] += a.y;
+      if (rowmy) {
+        const double2 b = zB[k];
+        acc[2 * k][P] += b.x; acc[2 * k + 1][P] += b.y;
+      }
     }
   }
-  if (on) {
+  PROF_MARK(2)
+  if (on && !(dbg & 2)) {
     double g[3][2], rg[2][2];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-      const double2 v = *reinterpret_cast<const double2 *>(gcell + i * 64 + 2 * lane);
-      g[i][0] = v.x; g[i][1] = v.y;
+      const double2 w = *reinterpret_cast<const double2 *>(gcell + i * 64 + 2 * lane);
+      g[i][0] = w.x; g[i][1] = w.y;
     }
 #pragma unroll
     for (int s = 0; s < 2; ++s) { rg[0][s] = rho * g[0][s]; rg[1][s] = rho * g[1][s]; }
@@ -316,10 +340,17 @@ __device__ __forceinline__ void mma_cell(Smem &S, double (&acc)[6][2], const Mma
     }
   }
   const bool toptop = L.m >= 4 && L.q >= 2;
-  if (wait_empty) mbar_wait(bar_empty, empty_parity);
-  if (!toptop) {
+#if FEMX_MMA_PROF
+  if (acc[0][0] + acc[5][1] == 1.2345e300) tprev = 0;   // wait for the accumulators before reading the clock
+#endif
+  PROF_MARK(3)
+  const unsigned slot = rc % RING;
+  if (rc >= RING) mbar_wait(&S.bar_empty[slot], (rc / RING - 1) & 1);
+  PROF_MARK(4)
+  if (!toptop && !(dbg & 8)) {
     // K^{ii} = (rho + 1) D_i + tr, K^{ij} = O_ij  (elem_math.cuh block form of B_a^T D B_b)
     const double rho1 = rho + 1.0;
+    double *rcell = &S.ring[slot][cx * CP];
     {
       const double tr = acc[0][1 - P] + acc[3][1 - P] + acc[5][1 - P];
       double *r = rcell + L.offA[P];
@@ -332,23 +363,29 @@ __device__ __forceinline__ void mma_cell(Smem &S, double (&acc)[6][2], const Mma
       r[0 * TP] = fma(rho1, acc[0][P], tr); r[1 * TP] = acc[1][P]; r[2 * TP] = acc[2][P];
       r[3 * TP] = fma(rho1, acc[3][P], tr); r[4 * TP] = acc[4][P]; r[5 * TP] = fma(rho1, acc[5][P], tr);
     }
-  } else {                                                    // top x top pairs wait for the cell above
-    const int zA = (L.m - 4) * 2 + (L.q - 2), zB = 8 + ((L.m - 4) >> 1) * 2 + (L.q - 2);
+  } else if (toptop && !(dbg & 4)) {                          // top x top pairs wait for the cell above
+    double2 *zA = reinterpret_cast<double2 *>(zcell + ((L.m - 4) * 2 + (L.q - 2)) * 6), *zB = reinterpret_cast<double2 *>(zcell + (8 + ((L.m - 4) >> 1) * 2 + (L.q - 2)) * 6);
 #pragma unroll
-    for (int t = 0; t < 6; ++t) {
-      zcell[t * ZT + zA] = acc[t][1 - P];
-      if (rowmy) zcell[t * ZT + zB] = acc[t][P];
+    for (int t = 0; t < 6; t += 2) {
+      zA[t >> 1] = make_double2(acc[t][1 - P], acc[t + 1][1 - P]);
+      if (rowmy) zB[t >> 1] = make_double2(acc[t][P], acc[t + 1][P]);
     }
   }
   __syncwarp();
-  if (lane == 0) mbar_arrive(bar_full);
+  if (lane == 0) mbar_arrive(&S.bar_full[slot]);
+  PROF_MARK(5)
 }
 
 }  // namespace
 
 template <bool WITH_F>
 __global__ void __launch_bounds__(NT, 1)
-hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ) {
+FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg_in) {
+#if FEMX_MMA_PROF
+  const int dbg = dbg_in;   // diagnostic: bit 0 skip geometry, 1 DMMA, 2 z-carry, 3 ring stores, 4 gather loads, 5 value stores, 6 f
+#else
+  constexpr int dbg = 0;
+#endif
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31;
@@ -367,6 +404,7 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
 
   if (wu >= NMW) {
     // ============================================================================================ gather warps
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");      // the MMA warps take the registers (geometry + accumulators + pending stores)
     const int gw = wu - NMW, gt = tid - 32 * NMW;
     if (WITH_F && lane < 3)
       for (int item = gw; item < NP; item += NGW) S.fcarry[item][lane] = 0.0;   // read back by this warp only
@@ -392,11 +430,13 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
         tab[par][e] = gather_off(par, e0 / 6, (e0 / 3) & 1, e0 % 3, lane) | gather_off(par, e1 / 6, (e1 / 3) & 1, e1 % 3, lane) << 16;
       }
     const bool upper = (lane & 16) != 0;
+    PROF_DECL
     for (int it = 0; it < nsteps; ++it) {
       const int m = T.l0 - 1 + it;
       const bool lay_lo = m >= T.l0 && m <= T.l1, lay_hi = m + 1 >= T.l0 && m + 1 <= T.l1;
       mbar_wait(&S.bar_lay[(it + 1) % LR], ((it + 1) / LR) & 1);
       if (it == 0) mbar_wait(&S.bar_lay[0], 0);
+      PROF_MARK(8)
       bool prefetched = false;
       for (int item = gw; item < NP; item += NGW) {
         const int jn = item / NXT, px = item - jn * NXT;
@@ -409,11 +449,13 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
           cp_async_wait<1>();     // this thread's node ids of layer it + 2 (issued one step ago) have landed
           if (it + 2 <= nsteps) fetch_layer<WITH_F>(S, hx, T, u, it + 2, gt);
           cp_async_commit();
+          PROF_MARK(9)
         }
         const int par = (jn + 1) & 1;
         const unsigned rc = (unsigned)it * EYC + jn + 1;      // sequence number of the cell row above the node row
         const unsigned slotB = rc % RING, slotA = (rc - 1) % RING;
         mbar_wait(&S.bar_full[slotB], (rc / RING) & 1);
+        PROF_MARK(10)
         const unsigned eb = saddr(&S.ring[dy < 0 ? slotA : slotB][px * CP]);
         double ulo = 0.0, uhi = 0.0;
         if (WITH_F) {
@@ -424,7 +466,8 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
         const bool act_lo = lay_lo && rlo->nb > 0, act_hi = lay_hi && rhi->nb > 0;
         // group dz = 0 / +1 of the lower node: columns on layers m / m+1; group dz = -1 of the upper node: columns on layer m
         const int k0 = rhi->k[kk], k1 = rlo->k[9 + kk], k2 = rlo->k[18 + kk];
-        const bool on0 = act_hi && lact && k0 != 255, on1 = act_lo && lact && k1 != 255, on2 = act_lo && lact && k2 != 255;
+        const bool st = !(dbg & 32);
+        const bool on0 = st && act_hi && lact && k0 != 255, on1 = st && act_lo && lact && k1 != 255, on2 = st && act_lo && lact && k2 != 255;
         const unsigned q0 = (unsigned)rhi->base + 3u * k0 + jj, q1 = (unsigned)rlo->base + 3u * k1 + jj, q2 = (unsigned)rlo->base + 3u * k2 + jj;
         const int rs_lo = 3 * rlo->nb, rs_hi = 3 * rhi->nb;
         double v[9];   // v[i * 3 + g]
@@ -435,15 +478,20 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
             const int e0 = (g * 2 + 0) * 3 + i, e1 = (g * 2 + 1) * 3 + i;
             const unsigned w0 = par ? tab[1][e0 >> 1] : tab[0][e0 >> 1], w1 = par ? tab[1][e1 >> 1] : tab[0][e1 >> 1];
             const unsigned o0 = (e0 & 1) ? w0 >> 16 : w0 & 0xffffu, o1 = (e1 & 1) ? w1 >> 16 : w1 & 0xffffu;
-            v[i * 3 + g] = lds_pred(eb + o0, lact) + lds_pred(eb + o1, two);
+            v[i * 3 + g] = lds_pred(eb + o0, lact && !(dbg & 16)) + lds_pred(eb + o1, two && !(dbg & 16));
           }
+#if FEMX_MMA_PROF
+        if (v[0] + v[4] + v[8] == 1.2345e300) tprev = 0;
+#endif
+        PROF_MARK(11)
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           if (on0) vals[q0 + (unsigned)(i * rs_hi)] = v[i * 3 + 0];
           if (on1) vals[q1 + (unsigned)(i * rs_lo)] = v[i * 3 + 1];
           if (on2) vals[q2 + (unsigned)(i * rs_lo)] = v[i * 3 + 2];
         }
-        if (WITH_F) {
+        PROF_MARK(12)
+        if (WITH_F && !(dbg & 64)) {
           // f_r = sum_c K_rc u_c: lane products, butterfly-summed (fixed order); lanes 0-15 end up with the three sums of
           // the lower node, lanes 16-31 with those of the upper node
           double keep[3];
@@ -466,6 +514,7 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
           __syncwarp();
           if (wr && upper) S.fcarry[item][li] = act_hi ? mine : 0.0;
         }
+        PROF_MARK(13)
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&S.bar_empty[slotA]);
@@ -473,11 +522,14 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
           if (jn == 0) mbar_arrive(&S.bar_empty[slotA]);          // stands in for the node row below the tile
           if (jn == NYT - 1) mbar_arrive(&S.bar_empty[slotB]);    // ... and the one above
         }
+        PROF_MARK(14)
       }
     }
     cp_async_wait<0>();
+    PROF_FLUSH(8)
   } else {
     // ============================================================================================ MMA warps
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
     const int cx = wu;
     MmaLane L;
     L.m = lane >> 2; L.q = lane & 3;
@@ -491,36 +543,35 @@ hex_mma_kernel(DevHex hx, const double *__restrict__ u, double *__restrict__ val
 #pragma unroll
     for (int t = 0; t < 6; ++t) acc[t][0] = acc[t][1] = 0.0;
     double *gw = &S.gsc[wu][0][0];
+    PROF_DECL
     for (int it = 0; it < nsteps; ++it) {
       mbar_wait(&S.bar_lay[(it + 1) % LR], ((it + 1) / LR) & 1);
       if (it == 0) mbar_wait(&S.bar_lay[0], 0);
+      PROF_MARK(0)
       const double *xlo = &S.xlay[it % LR][0], *xhi = &S.xlay[(it + 1) % LR][0], *esc = &S.esc[it % LR][0];
       for (int cy0 = 0; cy0 < EYC; cy0 += 4) {
         __syncwarp();
-        geometry4(xlo, xhi, esc, gw, cx, cy0, lane);
+        if (!(dbg & 1)) geometry4(xlo, xhi, esc, gw, cx, cy0, lane);
         __syncwarp();
+        PROF_MARK(1)
 #pragma unroll
         for (int cq = 0; cq < 4; ++cq) {
           const int cy = cy0 + cq;
           if (cy < EYC) {
             const unsigned rc = (unsigned)it * EYC + cy;
-            const unsigned slot = rc % RING;
             const bool on = esc[cy * EXC + cx] != 0.0;
-            double *rcell = &S.ring[slot][cx * CP];
-            double *zcell = &S.zc[cx][cy][0];
             // cy0 is a multiple of 4: the parity of the cell's +y nodes is that of cq + 1
-            if (cq & 1)
-              mma_cell<0>(S, acc, L, gw + cq * GP, zcell, rcell, on, cy == 0, it > 0, rho, &S.bar_empty[slot], rc >= RING, (rc / RING - 1) & 1, &S.bar_full[slot], lane);
-            else
-              mma_cell<1>(S, acc, L, gw + cq * GP, zcell, rcell, on, cy == 0, it > 0, rho, &S.bar_empty[slot], rc >= RING, (rc / RING - 1) & 1, &S.bar_full[slot], lane);
+            if (cq & 1) mma_cell<0>(S, acc, L, gw + cq * GP, cx, rc, cy, on, it > 0, rho, lane, tprev, pacc, dbg);
+            else mma_cell<1>(S, acc, L, gw + cq * GP, cx, rc, cy, on, it > 0, rho, lane, tprev, pacc, dbg);
           }
         }
       }
     }
+    PROF_FLUSH(0)
   }
 }
 
-int launch_hex_mma(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+int FEMX_MMA_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
   const DevHex &hx = c->dhex;
   const int tiles = ((hx.NI + NXT - 1) / NXT) * ((hx.NJ + NYT - 1) / NYT);
   int nsm = 148;
@@ -544,9 +595,25 @@ int launch_hex_mma(femx_ctx *c, const double *d_u, double *d_vals, double *d_fin
   auto go = [&](auto kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ);
+    kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
   };
-  if (d_u) go(hex_mma_kernel<true>); else go(hex_mma_kernel<false>);
+  if (d_u) go(FEMX_MMA_KERNEL<true>); else go(FEMX_MMA_KERNEL<false>);
+#if FEMX_MMA_PROF
+  {
+    static const char *nm[24] = {"M wait layer", "M geometry", "M carry + z-in", "M operands + DMMA", "M wait slot", "M emit + z-out", "-", "-",
+                                 "G wait layer", "G prefetch", "G wait row", "G meta + loads", "G stores", "G f", "G arrive", "-",
+                                 "-", "-", "-", "-", "-", "-", "-", "-"};
+    unsigned long long h[24], z[24] = {};
+    cudaStreamSynchronize(c->stream);
+    cudaMemcpyFromSymbol(h, g_prof, sizeof(h));
+    cudaMemcpyToSymbol(g_prof, z, sizeof(z));
+    const double rows = (double)grid.x * grid.y * grid.z * (LZ + 1) * EYC;
+    fprintf(stderr, "femx hex_mma prof (cycles per warp per cell row; %.0f cell rows, LZ %d):\n ", rows, LZ);
+    for (int i = 0; i < 24; ++i)
+      if (nm[i][0] != '-') fprintf(stderr, " %s %.0f |", nm[i], (double)h[i] / rows / (i < 16 ? 8.0 : 4.0));
+    fprintf(stderr, "\n");
+  }
+#endif
   return 1;
 }
 
