@@ -41,6 +41,9 @@ namespace {
 #ifndef FEMX_MMA_PROF
 #define FEMX_MMA_PROF 0
 #endif
+#ifndef FEMX_MMA_NGW
+#define FEMX_MMA_NGW 8
+#endif
 #ifndef FEMX_MMA_KERNEL
 #define FEMX_MMA_KERNEL hex_mma_kernel
 #define FEMX_MMA_LAUNCH launch_hex_mma
@@ -49,7 +52,7 @@ constexpr int NXT = 7, EXC = NXT + 1;            // owned node columns, cell col
 constexpr int NYT = FEMX_MMA_NYT, EYC = NYT + 1; // owned node rows, cell rows
 constexpr int UX = NXT + 2, UY = NYT + 2, UL = UX * UY;   // node positions of a layer incl. halo
 constexpr int NP = NXT * NYT;
-constexpr int NMW = 8, NGW = 8, NT = 32 * (NMW + NGW);   // MMA and gather warps
+constexpr int NMW = 8, NGW = FEMX_MMA_NGW, NT = 32 * (NMW + NGW);   // MMA and gather warps
 constexpr int RING = 4;                          // cell rows in flight between the MMA and the gather warps
 constexpr int LR = 3, NR = 4;                    // node-layer ring, node-id ring
 constexpr int TP = 36, CP = 6 * TP, SP = 1729;   // doubles per tile / cell / ring slot (annealed against bank conflicts, tools/hex_mma_anneal.py)
@@ -58,6 +61,7 @@ constexpr int ZT = 12, ZC = 6 * ZT;              // z-carry entries per tile / p
 constexpr int XP = UX * 3 + 1;                   // doubles per row of the coordinate layer
 constexpr int PF_ROW = 6;                        // gather warps prefetch the next node layer when they reach this node row
 static_assert(EXC == NMW, "one MMA warp per cell column");
+static_assert(NGW == 8, "register split (setmaxnreg 160 / 96) and the prefetch protocol are validated for 8 gather warps only");
 static_assert(NYT > PF_ROW + 1 && EYC > RING, "tile too short for the prefetch point / the ring");
 
 // position of entry (row m, column n) of a tile inside its 36-entry block, by the parity P of the cell row's +y nodes
@@ -404,7 +408,7 @@ FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 
   if (wu >= NMW) {
     // ============================================================================================ gather warps
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");      // the MMA warps take the registers (geometry + accumulators + pending stores)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");      // the MMA warps take the registers (geometry + accumulators)      // the MMA warps take the registers (geometry + accumulators + pending stores)
     const int gw = wu - NMW, gt = tid - 32 * NMW;
     if (WITH_F && lane < 3)
       for (int item = gw; item < NP; item += NGW) S.fcarry[item][lane] = 0.0;   // read back by this warp only
