@@ -15,6 +15,7 @@ Every call goes through libfemx.so; nothing here computes on the CPU.
 from __future__ import annotations
 
 import ctypes as C
+import dataclasses
 
 import numpy as np
 
@@ -146,6 +147,14 @@ class Femx:
         coh = np.ascontiguousarray(m.cohprops)
         self._ck(self.L.femx_set_materials(self.h, len(enu), _dp(enu), len(coh), _dp(coh)))
         self._ck(self.L.femx_set_bcs(self.h, len(m.bcnode), _ip(m.bcnode), _dp(m.bcval)))
+        return self
+
+    def set_materials(self, mat: np.ndarray, cohprops: np.ndarray | None = None):
+        """mat(:, 1:2) = (E, nu) rows (src/m_global.F90:254-255); may be called again after build_plan."""
+        enu = np.ascontiguousarray(np.asarray(mat, float)[:, :2])
+        coh = np.ascontiguousarray(self.mesh.cohprops if cohprops is None else cohprops)
+        self._ck(self.L.femx_set_materials(self.h, len(enu), _dp(enu), len(coh), _dp(coh)))
+        self.mesh = dataclasses.replace(self.mesh, mat=np.asarray(mat, float), cohprops=coh)
         return self
 
     def build_plan(self):

@@ -21,6 +21,14 @@ int femx_create(femx_ctx **out, int device, const femx_opts *opts) {
     return FEMX_ERR_CUDA;
   }
   if (device < 0 || device >= ndev) { g_create_err = "device index out of range"; return FEMX_ERR_ARG; }
+  if (opts) {
+    const int av = opts->assembly_variant;
+    bool known = av == 0 || av == 1 || av == 9 || av == 11 || av == 12 || av == 20;
+#ifdef FEMX_DIAG
+    known = known || av == 13 || av == 21;
+#endif
+    if (!known) { g_create_err = "unknown assembly_variant (0, 1, 9, 11, 12, 20)"; return FEMX_ERR_ARG; }
+  }
   if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_err = cudaGetErrorString(e); return FEMX_ERR_CUDA; }
   femx_ctx *c = new femx_ctx;
   c->device = device;
@@ -93,6 +101,19 @@ int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *
   ARG(pdim == 2 || pdim == 3, "pdim must be 2 or 3");
   ARG(nels >= 0 && nlnds >= 0 && nnds >= nlnds, "bad sizes");
   ARG(etype && eptr && eind && emat && enlmat && coords && nl2g, "null mesh array");
+  // validate everything before the ctx is touched: a refused mesh leaves the previous mesh and plan intact
+  ARG(eptr[0] == 0, "eptr must start at 0");
+  for (int e = 0; e < nels; ++e) {
+    ARG(etype[e] >= FEMX_TRI && etype[e] <= FEMX_COH, "unknown element type");
+    ARG(eptr[e + 1] - eptr[e] == femx::type_nen(etype[e]), "eptr does not match the element types' node counts");
+    ARG(type_dim(etype[e]) == pdim, "element type does not match pdim");
+    for (int q = eptr[e]; q < eptr[e + 1]; ++q) ARG(eind[q] >= 1 && eind[q] <= nlnds, "element node id out of range (1-based local ids)");
+  }
+  for (int i = 0; i < nlnds; ++i) {
+    ARG(nl2g[i] >= 1 && nl2g[i] <= nnds, "nl2g out of range (1-based global ids)");
+    ARG(i == 0 || nl2g[i] > nl2g[i - 1], "nl2g must ascend (src/main.F90:57-63 numbering)");
+  }
+  c->has_plan = false;
   c->pdim = pdim; c->nels = nels; c->nlnds = nlnds; c->nnds = nnds;
   c->etype.assign(etype, etype + nels);
   c->eptr.assign(eptr, eptr + nels + 1);
@@ -100,10 +121,6 @@ int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *
   c->emat.assign(emat, emat + nels);
   c->enlmat.assign(enlmat, enlmat + nels);
   c->nl2g.assign(nl2g, nl2g + nlnds);
-  for (int i = 0; i < nlnds; ++i) {
-    ARG(nl2g[i] >= 1 && nl2g[i] <= nnds, "nl2g out of range (1-based global ids)");
-    ARG(i == 0 || nl2g[i] > nl2g[i - 1], "nl2g must ascend (src/main.F90:57-63 numbering)");
-  }
   c->coords.resize((size_t)nlnds * pdim);
   for (int i = 0; i < nlnds; ++i)
     for (int d = 0; d < pdim; ++d)
@@ -113,20 +130,69 @@ int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *
   return FEMX_OK;
 }
 
+// Everything the kernels derive from (E, nu): (lambda, mu) per material, and for a logical hex8 grid sqrt(mu) per cell and
+// rho = lambda / mu.  Runs in femx_build_plan and again when femx_set_materials is called afterwards, so that the fast
+// kernels never see scale factors of an older material table (they are re-validated too: one Poisson ratio, mu > 0).
+static int refresh_materials(femx_ctx *c) {
+  for (int e = 0; e < c->nels; ++e) {
+    if (c->etype[e] != FEMX_COH) ARG(c->emat[e] >= 1 && c->emat[e] <= c->nmts, "element material id out of range (femx_set_materials first)");
+    if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
+  }
+  int rc;
+  std::vector<double> lm(2 * (size_t)c->nmts);
+  for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
+  dev_release(c, c->dm.lam_mu); dev_release(c, c->dm.cohprops);
+  c->dm.lam_mu = nullptr; c->dm.cohprops = nullptr;
+  if ((rc = upload(c, &c->dm.lam_mu, lm))) return rc;
+  if ((rc = upload(c, &c->dm.cohprops, c->cohprops))) return rc;
+  std::vector<char> used(c->nmts, 0);
+  for (int e = 0; e < c->nels; ++e)
+    if (c->etype[e] != FEMX_COH) used[c->emat[e] - 1] = 1;
+  // both fast paths scale gradients by sqrt(mu): every used material needs mu > 0 and a finite lambda / mu
+  bool mu_ok = true;
+  for (int m = 0; m < c->nmts; ++m)
+    if (used[m] && (!(lm[2 * m + 1] > 0.0) || !std::isfinite(lm[2 * m] / lm[2 * m + 1]))) mu_ok = false;
+  c->mat_ok_simplex = mu_ok;
+  c->mat_ok_hex = false;
+  c->mat_why.clear();
+  if (c->hex.ok) {
+    femx::DevHex &hx = c->dhex;
+    double nu0 = 0.0;
+    bool have = false, one_nu = true;
+    for (int m = 0; m < c->nmts; ++m)
+      if (used[m]) {
+        if (!have) { nu0 = c->E_nu[2 * m + 1]; have = true; }
+        else if (c->E_nu[2 * m + 1] != nu0) one_nu = false;
+      }
+    if (!one_nu) c->mat_why = "elements with different Poisson ratios";
+    else if (!mu_ok) c->mat_why = "a material with mu <= 0";
+    else {
+      c->mat_ok_hex = true;
+      hx.rho = 2.0 * nu0 / (1.0 - 2.0 * nu0);   // lambda / mu
+      std::vector<double> smu(c->nmts);
+      for (int m = 0; m < c->nmts; ++m) smu[m] = std::sqrt(lm[2 * m + 1] > 0.0 ? lm[2 * m + 1] : 0.0);
+      std::vector<double> cm(c->hex.elem_at.size(), 0.0);
+      for (size_t q = 0; q < cm.size(); ++q)
+        if (c->hex.elem_at[q] >= 0) cm[q] = smu[c->emat[c->hex.elem_at[q]] - 1];
+      dev_release(c, hx.sqrt_mu); dev_release(c, hx.cellmu);
+      hx.sqrt_mu = nullptr; hx.cellmu = nullptr;
+      if ((rc = upload(c, &hx.sqrt_mu, smu))) return rc;
+      if ((rc = upload(c, &hx.cellmu, cm))) return rc;
+    }
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+
 int femx_set_materials(femx_ctx *c, int nmts, const double *E_nu, int ncoh, const double *cohprops) {
   if (!c) return FEMX_ERR_ARG;
   ARG(nmts >= 0 && ncoh >= 0, "bad counts");
   c->nmts = nmts; c->ncoh = ncoh;
   c->E_nu.assign(E_nu, E_nu + 2 * (size_t)nmts);
   c->cohprops.assign(cohprops, cohprops + 6 * (size_t)ncoh);
-  if (c->has_plan) {  // refresh device copies
-    std::vector<double> lm(2 * (size_t)nmts);
-    for (int m = 0; m < nmts; ++m) lame(E_nu[2 * m], E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
-    dev_release(c, c->dm.lam_mu); dev_release(c, c->dm.cohprops);
-    int rc;
-    if ((rc = upload(c, &c->dm.lam_mu, lm))) return rc;
-    if ((rc = upload(c, &c->dm.cohprops, c->cohprops))) return rc;
-    CK(cudaStreamSynchronize(c->stream));
+  if (c->has_plan) {   // a material change after the plan: re-validate and recompute every derived factor
+    int rc = refresh_materials(c);
+    if (rc) { c->has_plan = false; return rc; }
   }
   return FEMX_OK;
 }
@@ -190,23 +256,29 @@ int femx_build_plan(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;
   ARG(c->has_mesh, "femx_set_mesh first");
   CK(cudaSetDevice(c->device));
+  // a second plan on the same ctx: the previous plan's device arrays go first (hundreds of MB at 1 M hex8)
+  c->has_plan = false;
+  CK(cudaStreamSynchronize(c->stream));
+  for (void *q : c->plan_allocs) dev_release(c, q);
+  c->plan_allocs.clear();
+  for (double **q : {&c->d_ke, &c->d_fe, &c->d_sn, &c->d_u, &c->d_vals, &c->d_kstage, &c->d_vec[0], &c->d_vec[1], &c->d_vec[2], &c->d_vec[3]}) {
+    dev_release(c, *q);
+    *q = nullptr;
+  }
+  c->buf_n.clear();
+  c->dm = femx::DevMesh(); c->dhex = femx::DevHex(); c->loads = femx::DevLoads();
+  c->d_bc_diag = nullptr; c->d_bc_dof = nullptr; c->d_bc_val = nullptr;
+  const std::vector<void *> before = c->allocs;
   int rc = build_plan(c->pdim, c->nels, c->etype.data(), c->eptr.data(), c->eind.data(), c->enlmat.data(),
                       c->nlnds, c->nnds, &c->plan, &c->err);
   if (rc) return rc;
-  for (int e = 0; e < c->nels; ++e) {
+  for (int e = 0; e < c->nels; ++e)
     if (c->etype[e] != FEMX_COH) ARG(c->emat[e] >= 1 && c->emat[e] <= c->nmts, "element material id out of range (femx_set_materials first)");
-    if (c->enlmat[e] != 0) ARG(c->enlmat[e] >= 1 && c->enlmat[e] <= c->ncoh, "nlMat out of range");
-  }
   femx::Plan &P = c->plan;
   c->nl2g_identity = c->nlnds == c->nnds;
   for (int i = 0; i < c->nlnds && c->nl2g_identity; ++i) c->nl2g_identity = c->nl2g[i] == i + 1;
-  if (P.simplex) {   // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians and mu > 0
+  if (P.simplex) {   // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians (mu > 0: refresh_materials)
     const int pd = c->pdim;
-    for (int m = 0; m < c->nmts && P.simplex; ++m) {
-      double lam, mu;
-      lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lam, &mu);
-      if (!(mu > 0.0) || !std::isfinite(lam / mu)) P.simplex = false;
-    }
     for (int e = 0; e < c->nels && P.simplex; ++e) {
       const int *nd = &c->eind[c->eptr[e]];
       double d[3][3];
@@ -236,10 +308,7 @@ int femx_build_plan(femx_ctx *c) {
   c->nnz = (int64_t)c->pdim * c->pdim * P.nblk;
 #define UP(dst, src) if ((rc = upload(c, &dst, src))) return rc
   UP(dm.etype, c->etype); UP(dm.eptr, c->eptr); UP(dm.conn0, P.conn0); UP(dm.emat, c->emat); UP(dm.enlmat, c->enlmat);
-  UP(dm.nl2g, c->nl2g); UP(dm.coords, c->coords); UP(dm.cohprops, c->cohprops);
-  std::vector<double> lm(2 * (size_t)c->nmts);
-  for (int m = 0; m < c->nmts; ++m) lame(c->E_nu[2 * m], c->E_nu[2 * m + 1], &lm[2 * m], &lm[2 * m + 1]);
-  UP(dm.lam_mu, lm);
+  UP(dm.nl2g, c->nl2g); UP(dm.coords, c->coords);
   UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
   UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent); UP(dm.sx_inc, P.sx_inc); UP(dm.sx_mat, P.sx_mat); UP(dm.ri_nodes, P.ri_nodes); UP(dm.ri_info, P.ri_info);
   UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
@@ -264,23 +333,41 @@ int femx_build_plan(femx_ctx *c) {
   UP(c->d_cnode_ptr, P.cnode_ptr); UP(c->d_cnode_src, P.cnode_src);
   if ((rc = dev_alloc(c, &c->d_coh_ke, 64 * (int64_t)P.coh_elems.size()))) return rc;
   if ((rc = dev_alloc(c, &c->d_coh_fe, 8 * (int64_t)P.coh_elems.size()))) return rc;
-  // fused hex8 path (variant 2): only if the mesh provably is a logical grid of hex8
+  // fused hex8 tile kernels (variants 12, 20): only if the mesh provably is a logical grid of hex8
   c->hex = femx::HexPlan();
   if (c->opts.assembly_variant != 1 && c->opts.assembly_variant != 9 && c->opts.assembly_variant != 11) {
-    build_hex_plan(P, c->etype.data(), c->eptr.data(), c->emat.data(), c->E_nu.data(), c->nmts, &c->hex, &c->hex.why);
+    build_hex_plan(P, c->etype.data(), c->eptr.data(), &c->hex, &c->hex.why);
+    if (c->hex.ok) {
+      // the tile kernels scale gradients by rsqrt(detJ): a mirrored grid or an inverted element (which the reference and the
+      // general kernels assemble as is, src/m_local.F90:61-65) must not reach them
+      const double g = FEMX_G;
+      for (int e = 0; e < c->nels && c->hex.ok; ++e) {
+        const int *nd = &c->eind[c->eptr[e]];
+        for (int ip = 0; ip < 8 && c->hex.ok; ++ip) {
+          const double xi[3] = {(ip == 1 || ip == 2 || ip == 5 || ip == 6) ? g : -g, ((ip & 3) >= 2) ? g : -g, ip >= 4 ? g : -g};
+          double J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+          for (int b = 0; b < 8; ++b) {
+            const double sx = (b == 1 || b == 2 || b == 5 || b == 6) ? 1.0 : -1.0, sy = ((b & 3) >= 2) ? 1.0 : -1.0, sz = b >= 4 ? 1.0 : -1.0;
+            const double d[3] = {0.125 * sx * (1 + sy * xi[1]) * (1 + sz * xi[2]), 0.125 * sy * (1 + sx * xi[0]) * (1 + sz * xi[2]),
+                                 0.125 * sz * (1 + sx * xi[0]) * (1 + sy * xi[1])};
+            const double *X = &c->coords[(size_t)(nd[b] - 1) * 3];
+            for (int i = 0; i < 3; ++i)
+              for (int j = 0; j < 3; ++j) J[i][j] += d[i] * X[j];
+          }
+          const double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                             J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+          if (!(det > 0.0)) { c->hex.ok = false; c->hex.why = "an element with detJ <= 0 (inverted or mirrored numbering)"; }
+        }
+      }
+    }
     if (c->hex.ok) {
       femx::DevHex &hx = c->dhex;
-      hx.NI = c->hex.NI; hx.NJ = c->hex.NJ; hx.NK = c->hex.NK; hx.rho = c->hex.rho;
+      hx.NI = c->hex.NI; hx.NJ = c->hex.NJ; hx.NK = c->hex.NK;
       UP(hx.node_at, c->hex.node_at); UP(hx.elem_at, c->hex.elem_at); UP(hx.kmap, c->hex.kmap);
-      std::vector<double> c4((size_t)c->nlnds * 4, 0.0), smu(c->nmts);
+      std::vector<double> c4((size_t)c->nlnds * 4, 0.0);
       for (int i = 0; i < c->nlnds; ++i)
         for (int d = 0; d < 3; ++d) c4[(size_t)i * 4 + d] = c->coords[(size_t)i * 3 + d];
-      for (int m = 0; m < c->nmts; ++m) smu[m] = std::sqrt(lm[2 * m + 1]);
-      UP(hx.coords4, c4); UP(hx.sqrt_mu, smu);
-      std::vector<double> cm(c->hex.elem_at.size(), 0.0);
-      for (size_t q = 0; q < cm.size(); ++q)
-        if (c->hex.elem_at[q] >= 0) cm[q] = smu[c->emat[c->hex.elem_at[q]] - 1];
-      UP(hx.cellmu, cm);
+      UP(hx.coords4, c4);
       std::vector<double> px(c->hex.node_at.size() * 3, 0.0);
       std::vector<femx::HexRowMeta> pm(c->hex.node_at.size());
       for (size_t q = 0; q < pm.size(); ++q) {
@@ -296,18 +383,25 @@ int femx_build_plan(femx_ctx *c) {
         for (int t = 0; t < 27; ++t) mm.k[t] = c->hex.kmap[(size_t)r * 32 + t];
       }
       UP(hx.pos_x, px); UP(hx.pos_meta, pm);
-    } else if (c->opts.assembly_variant >= 2) {
+    } else if (c->opts.assembly_variant == 12 || c->opts.assembly_variant == 13 || c->opts.assembly_variant == 20 || c->opts.assembly_variant == 21) {
       c->err = "fused assembly variant requested but the mesh does not qualify: " + c->hex.why;
       return FEMX_ERR_UNSUPPORTED;
     }
   }
 #undef UP
+  if ((rc = refresh_materials(c))) return rc;
+  const int av = c->opts.assembly_variant;
+  if ((av == 12 || av == 13 || av == 20 || av == 21) && !c->mat_ok_hex) {
+    c->err = "fused assembly variant requested but the materials do not qualify: " + c->mat_why;
+    return FEMX_ERR_UNSUPPORTED;
+  }
   CK(cudaStreamSynchronize(c->stream));
+  rc = prepare_bcs(c);
+  for (void *q : c->allocs)
+    if (std::find(before.begin(), before.end(), q) == before.end()) c->plan_allocs.push_back(q);
+  if (rc) return rc;
   c->has_plan = true;
-  c->d_ke = c->d_fe = c->d_sn = c->d_u = c->d_vals = c->d_kstage = nullptr;
-  for (auto &v : c->d_vec) v = nullptr;
-  c->buf_n.clear();
-  return prepare_bcs(c);
+  return FEMX_OK;
 }
 
 int femx_pattern_size(femx_ctx *c, int64_t *nrows, int64_t *nnz) {

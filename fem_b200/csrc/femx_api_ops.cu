@@ -50,15 +50,16 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
   // auto (0): the 16-warp symmetric tile kernel with permuted gather lanes (12) for a logical hex8 grid, else the fused rows kernel, else two-pass
   const int av0 = c->opts.assembly_variant;
-  const bool fused = c->hex.ok && av0 != 1 && av0 != 9 && av0 != 11;
-  const bool simplex = !fused && av0 != 1 && av0 != 9 && rows_simplex_ok(c);   // pure tri3 / tet4 mesh
+  const bool fused = c->hex.ok && c->mat_ok_hex && av0 != 1 && av0 != 9 && av0 != 11;
+  if (!fused && (av0 == 12 || av0 == 13 || av0 == 20 || av0 == 21)) { c->err = "hex8 tile kernel: " + (c->hex.ok ? c->mat_why : c->hex.why); return FEMX_ERR_UNSUPPORTED; }
+  const bool simplex = !fused && av0 != 1 && av0 != 9 && c->mat_ok_simplex && rows_simplex_ok(c);   // pure tri3 / tet4 mesh
   const bool rows = !fused && !simplex && av0 != 1 && rows_fused_ok(c);
   if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
   if (av0 == 11 && !simplex) { c->err = "simplex rows kernel: needs a pure tri3 / tet4 mesh with at most 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
   const bool peer = c->peer.connected;
   // peer exchange: reserved[3] = 1 lets the assembly kernel store interface rows at their owner itself (variants 0, 5, 12, 9);
   // default is the push kernel behind the unchanged assembly kernel
-  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 5 || av0 == 12) : (rows || simplex));
+  const bool peer_fused = peer && c->opts.reserved[3] == 1 && (fused ? (av0 == 0 || av0 == 12) : (rows || simplex));
   c->peer.in_kernel = peer_fused;
   if (!fused && !rows && !simplex) {
     if ((rc = ensure(c, &c->d_ke, c->plan.ke_off[c->nels]))) return rc;
@@ -68,10 +69,12 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
     const int av = av0 == 0 ? 12 : av0;
-    c->launches += av == 20 ? launch_hex_mma(c, d_u, d_vals, d_fint) : av == 21 ? launch_hex_mma_prof(c, d_u, d_vals, d_fint) : av == 13 ? launch_hex_sym7(c, d_u, d_vals, d_fint) : av == 12 ? launch_hex_sym6(c, d_u, d_vals, d_fint) : av == 8 ? launch_hex_sym5(c, d_u, d_vals, d_fint) : av == 7 ? launch_hex_sym4(c, d_u, d_vals, d_fint)
-                   : av == 6 ? launch_hex_sym3(c, d_u, d_vals, d_fint) : av == 5 ? launch_hex_sym2(c, d_u, d_vals, d_fint)
-                   : av == 4 ? launch_hex_sym5(c, d_u, d_vals, d_fint)   /* the first 8-warp kernel lives on as variant 8 */
-                   : (av == 3 ? launch_hex_ws(c, d_u, d_vals, d_fint) : launch_hex_fused(c, d_u, d_vals, d_fint));
+#ifdef FEMX_DIAG
+    if (av == 13) c->launches += launch_hex_sym7(c, d_u, d_vals, d_fint);
+    else if (av == 21) c->launches += launch_hex_mma_prof(c, d_u, d_vals, d_fint);
+    else
+#endif
+    c->launches += av == 20 ? launch_hex_mma(c, d_u, d_vals, d_fint) : launch_hex_sym6(c, d_u, d_vals, d_fint);
   } else if (simplex) {
     c->launches += launch_rows_simplex(c, d_u, d_vals, d_fint);
   } else if (rows) {
@@ -245,20 +248,11 @@ static int residual_impl(femx_ctx *c, const double *jvals, const double *u_total
   c->launches += launch_cohesive_mesh(c, d_u, dt, c->d_coh_fe, nullptr);
   c->launches += launch_cohesive_force_gather(c, d_br);
   c->launches += launch_bc_force(c, dt, t_total, d_br);  // EnforceBCForce :439-455
-  cudaEvent_t evm = nullptr;
-  if (c->opts.reserved[2] & 32) { cudaEventCreate(&evm); cudaEventRecord(evm, c->stream); }
   if (jvals) {
     if (c->nlnds != c->nnds) CK(cudaMemsetAsync(d_r, 0, sizeof(double) * (size_t)nglob, c->stream));
     c->launches += launch_spmv_sub(c, d_j, d_du, d_br, d_r);  // VecScale(-1); MatMultAdd :225-226
   }
   if ((rc = end_timing(c))) return rc;
-  if (evm) {
-    cudaStreamSynchronize(c->stream);
-    float a = 0.f, b = 0.f;
-    cudaEventElapsedTime(&a, c->ev0, evm); cudaEventElapsedTime(&b, evm, c->ev1);
-    fprintf(stderr, "femx: residual force part %.4f ms, J du part %.4f ms\n", a, b);
-    cudaEventDestroy(evm);
-  }
   if ((rc = copy_back(c, r, d_r, nglob, where))) return rc;
   return finish_call(c, true);
 }

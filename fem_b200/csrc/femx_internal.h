@@ -68,7 +68,6 @@ struct Plan {
 // plan_hex.cpp: logical-grid proof + canonical 27-stencil positions for the fused hex8 kernel
 struct HexPlan {
   bool ok = false;
-  double rho = 0.0;                 // lambda / mu (one Poisson ratio per mesh)
   int NI = 0, NJ = 0, NK = 0;       // logical node-grid extents
   std::vector<int32_t> node_at;     // [NK][NJ][NI] local node id or -1
   std::vector<int32_t> elem_at;     // [NK][NJ][NI] local element id or -1 (cell spans i..i+1)
@@ -125,8 +124,7 @@ __device__ __forceinline__ double *peer_f(const PeerTab &pt, double *local, long
   return p;
 }
 
-int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,
-                   HexPlan *H, std::string *why);
+int build_hex_plan(const Plan &P, const int *etype, const int *eptr, HexPlan *H, std::string *why);
 
 int build_plan(int pdim, int nels, const int *etype, const int *eptr, const int *eind,
                const int *enlmat, int nlnds, int nnds, Plan *out, std::string *err);
@@ -186,6 +184,8 @@ struct femx_ctx {
   std::vector<double> coords, E_nu, cohprops, bcval;
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
+  bool mat_ok_simplex = false, mat_ok_hex = false;   // the CURRENT materials admit the simplex rows / hex8 tile kernels (mu > 0, one Poisson ratio)
+  std::string mat_why;                                // why not
   int own_nranks = 1, own_rank = 0;            // femx_set_ownership (PETSC_DECIDE row split of this rank)
   int64_t own_row_start = 0, own_row_end = -1;
   bool nl2g_identity = false;   // nl2g[i] == i + 1 for every local node (checked once in femx_build_plan)
@@ -216,6 +216,7 @@ struct femx_ctx {
   double *d_coh_ke = nullptr, *d_coh_fe = nullptr;
   femx::DevLoads loads;
   std::vector<void *> allocs;  // everything cudaMalloc'ed by the ctx
+  std::vector<void *> plan_allocs;   // ... of which the current plan's arrays (released by the next femx_build_plan)
   // peer-memory exchange (peer.cu)
   struct Peer {
     int nranks = 0, rank = 0;

@@ -179,7 +179,7 @@ __device__ unsigned long long g_prof[24];
 #define PROF_MARK(i) { const long long now_ = clock64(); pacc[(i) & 7] += now_ - tprev; tprev = now_; }
 #define PROF_FLUSH(base) if (lane == 0) { for (int i_ = 0; i_ < 8; ++i_) atomicAdd(&g_prof[(base) + i_], (unsigned long long)pacc[i_]); }
 #else
-#define PROF_DECL long long tprev = 0; long long pacc[1] = {0};
+#define PROF_DECL long long tprev = 0; long long pacc[1] = {0}; (void)tprev; (void)pacc;
 #define PROF_MARK(i)
 #define PROF_FLUSH(base)
 #endif

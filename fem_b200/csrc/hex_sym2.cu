@@ -385,46 +385,6 @@ __device__ __forceinline__ void put_diag(double *m, int ra, const double *k6) { 
     for (int j = 0; j < 3; ++j) m[ra * SA + i * SI + ra * 3 + j] = k6[sym_s(i < j ? i : j, i < j ? j : i)];
 }
 
-#if FEMX_SYM_TPC == 4
-// four threads per cell: one thread owns all 10 pairs of a face (78 accumulators), one 2 x 4 bottom x top blocks (72)
-__host__ __device__ constexpr int offdiag_p(int a, int b) { return a == 0 ? b - 1 : (a == 1 ? b + 1 : 5); }   // a < b, 0..5
-__device__ __forceinline__ void fma_face4(const double (&v)[3][4], double (&acc)[78]) {
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b = a + 1; b < 4; ++b)
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j) acc[offdiag_p(a, b) * 9 + i * 3 + j] = fma(v[i][a], v[j][b], acc[offdiag_p(a, b) * 9 + i * 3 + j]);
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-      for (int j = i; j < 3; ++j) acc[54 + a * 6 + sym_s(i, j)] = fma(v[i][a], v[j][a], acc[54 + a * 6 + sym_s(i, j)]);
-}
-__device__ __forceinline__ void load_bt4(const double *gp, int a0, double (&va)[3][2], double (&vb)[3][4]) {
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    const double2 a = *reinterpret_cast<const double2 *>(gp + i * 8 + a0);
-    const double2 b = *reinterpret_cast<const double2 *>(gp + i * 8 + 4);
-    const double2 c = *reinterpret_cast<const double2 *>(gp + i * 8 + 6);
-    va[i][0] = a.x; va[i][1] = a.y;
-    vb[i][0] = b.x; vb[i][1] = b.y; vb[i][2] = c.x; vb[i][3] = c.y;
-  }
-}
-__device__ __forceinline__ void fma_bt4(const double (&va)[3][2], const double (&vb)[3][4], double (&acc)[78]) {
-#pragma unroll
-  for (int a = 0; a < 2; ++a)
-#pragma unroll
-    for (int b = 0; b < 4; ++b)
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j) acc[(a * 4 + b) * 9 + i * 3 + j] = fma(va[i][a], vb[j][b], acc[(a * 4 + b) * 9 + i * 3 + j]);
-}
-#endif
 
 // ---------------------------------------------------------------------------------- gather phase
 // one CSR value: the <= 4 cell contributions in ascending cell order.  Loads of contributions a lane does not have are
@@ -458,8 +418,9 @@ __device__ __forceinline__ bool v_dummy(const double *p) { return p == nullptr; 
 
 template <bool WITH_F, bool PEER>   // PEER: rows another rank owns are stored into that rank's receive arena (peer.cu)
 __global__ void __launch_bounds__(NT, CTAS)
-FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg,
+FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg_in,
                 const PeerTab pt) {
+  const int dbg = FEMX_SYM_PROF ? dbg_in : 0;   // phase-skipping switches exist in the clock-accounting build only
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -483,9 +444,7 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   const int es = (w & (WPT - 1)) * 32 + lane;
   const int bt_a0 = ((type - 4) >> 1) * 2, bt_b0 = ((type - 4) & 1) * 2;
 #endif
-#if FEMX_SYM_TPC == 8
   const bool top = type >= 2, isy = (type & 1) != 0;
-#endif
 #if !FEMX_SYM_GPERM
   // gather-phase lane constants
   int kk, jj;
@@ -501,10 +460,6 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   }
 #endif
 
-  if (CTAS > 1 && (dbg >> 8) > 0) {   // diagnostic: start the second resident CTA of an SM (dbg >> 8) x 256 clocks late
-    const int lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-    if ((lin / 148) & 1) { const long long t0 = clock64(); while (clock64() - t0 < (long long)(dbg >> 8) * 256) { } }
-  }
   for (int t = tid; t < 3 * 32; t += NT) S.tab[t / 32][t % 32] = table_entry(t / 32, t % 32);
   if (WITH_F && tid < NP * 3) (&S.fcarry[0][0])[tid] = 0.0;
   fetch_nid(S, hx, T, T.l0 - 1, tid); fetch_nid(S, hx, T, T.l0, tid); fetch_nid(S, hx, T, T.l0 + 1, tid);
@@ -545,7 +500,6 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
     // ------------------------------------------------------------------ FMA phase
     const bool cell_on = S.esc[m & 3][es] != 0.0;
     const double *g = &S.a.geo[es * GS];
-#if FEMX_SYM_TPC == 8
     double acc[40];
     if (type < 4) {
       if (!top && it > 0) {
@@ -627,73 +581,6 @@ FEMX_SYM_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
           }
       }
     }
-#else
-    double acc[78];
-    if (type < 2) {
-      const bool topf = type == 1;
-      if (!topf && it > 0) {
-#pragma unroll
-        for (int q = 0; q < 39; ++q) { const double2 c = S.carry[0][q][es]; acc[2 * q] = c.x; acc[2 * q + 1] = c.y; }
-      } else {
-#pragma unroll
-        for (int q = 0; q < 78; ++q) acc[q] = 0.0;
-      }
-      const bool need = topf ? it + 1 < nsteps : it > 0;   // first finish / last start feed no owned row
-      if (cell_on && need && !(dbg & 2)) {
-        const double *gf = g + (topf ? 4 : 0);
-#pragma unroll 2
-        for (int ip = 0; ip < 8; ++ip) {
-          double v[3][4];
-          load_face_x(gf + ip * 24, v);
-          fma_face4(v, acc);
-        }
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < 78; ++q) acc[q] = 0.0;
-      if (cell_on && !(dbg & 2)) {
-        const int a0 = (type - 2) * 2;
-#pragma unroll 2
-        for (int ip = 0; ip < 8; ++ip) {
-          double va[3][2], vb[3][4];
-          load_bt4(g + ip * 24, a0, va, vb);
-          fma_bt4(va, vb, acc);
-        }
-      }
-    }
-    __syncthreads();              // everybody has left the gradient buffer
-    // ------------------------------------------------------------------ G' -> K, park in the scratch
-    {
-      double *sc = &S.a.scr[es * SS];
-      if (type == 0) {   // CCW face nodes 0, 1, 2, 3 = row-major 0, 1, 3, 2
-#pragma unroll
-        for (int p = 0; p < 6; ++p) to_k_block(&acc[p * 9], rho);
-#pragma unroll
-        for (int a = 0; a < 4; ++a) to_k_sym(&acc[54 + a * 6], rho + 1.0);
-        put_pair(sc + FACE_OFF, 0, 1, &acc[0]); put_pair(sc + FACE_OFF, 0, 3, &acc[9]); put_pair(sc + FACE_OFF, 0, 2, &acc[18]);
-        put_pair(sc + FACE_OFF, 1, 3, &acc[27]); put_pair(sc + FACE_OFF, 1, 2, &acc[36]); put_pair(sc + FACE_OFF, 3, 2, &acc[45]);
-        put_diag(sc + FACE_OFF, 0, &acc[54]); put_diag(sc + FACE_OFF, 1, &acc[60]); put_diag(sc + FACE_OFF, 3, &acc[66]); put_diag(sc + FACE_OFF, 2, &acc[72]);
-      } else if (type == 1) {   // park the raw top-face sums for the next layer's finisher (after the barrier: the finishers have loaded theirs)
-#pragma unroll
-        for (int q = 0; q < 39; ++q) S.carry[0][q][es] = make_double2(acc[2 * q], acc[2 * q + 1]);
-      } else {
-        const int a0 = (type - 2) * 2;
-#pragma unroll
-        for (int p = 0; p < 8; ++p) to_k_block(&acc[p * 9], rho);
-#pragma unroll
-        for (int a = 0; a < 2; ++a)
-#pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const int ra = (a0 + a) ^ ((a0 + a) >> 1), rb = b ^ (b >> 1);   // CCW -> row-major node index
-            double *dst = sc + BT_OFF + ra * SA + rb * 3;
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-#pragma unroll
-              for (int j = 0; j < 3; ++j) dst[i * SI + j] = acc[(a * 4 + b) * 9 + i * 3 + j];
-          }
-      }
-    }
-#endif
     PROF_MARK(5)
     __syncthreads();
     PROF_MARK(6)
@@ -839,13 +726,6 @@ int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
   dim3 grid((hx.NI + NX - 1) / NX, (hx.NJ + NY - 1) / NY, (hx.NK + LZ - 1) / LZ);
   const size_t smem = sizeof(Smem);
   static_assert(sizeof(Smem) <= (CTAS == 1 ? 232448 : 115712), "shared memory exceeds what the resident CTAs of an SM may opt into");
-  if (c->opts.reserved[2] & 32) {
-    int nb = -1;
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(FEMX_SYM_KERNEL<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, FEMX_SYM_KERNEL<true, false>, NT, smem);
-    fprintf(stderr, "femx: sym kernel smem %zu B, %d resident CTAs per SM, grid %d x %d x %d, LZ %d\n", smem, nb, grid.x, grid.y, grid.z, LZ);
-  }
   const PeerTab pt = c->peer.in_kernel ? peer_tab(c) : PeerTab{};
   const int dbg = c->opts.reserved[2];
   auto go = [&](auto kern) {
@@ -853,12 +733,10 @@ int FEMX_SYM_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, dbg, pt);
   };
-#if FEMX_SYM_TPC == 8 && FEMX_SYM_CTAS == 1
   if (pt.n > 0) {
     if (d_u) go(FEMX_SYM_KERNEL<true, true>); else go(FEMX_SYM_KERNEL<false, true>);
     return 1;
   }
-#endif
   if (d_u) go(FEMX_SYM_KERNEL<true, false>); else go(FEMX_SYM_KERNEL<false, false>);
 #if FEMX_SYM_PROF
   {

@@ -24,12 +24,6 @@ int launch_jacobian_overlay(femx_ctx *c, const double *d_kvals, double *d_jvals)
 int launch_cohesive_force_gather(femx_ctx *c, double *d_out);
 int launch_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b, const int64_t *ptr, const int64_t *idx,
                       int64_t nout, double *out);
-int launch_hex_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_ws(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_sym2(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_sym3(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_sym4(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
-int launch_hex_sym5(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym6(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym7(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_mma(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);

@@ -20,21 +20,12 @@ static const int kSx[8] = {0, 1, 1, 0, 0, 1, 1, 0};
 static const int kSy[8] = {0, 0, 1, 1, 0, 0, 1, 1};
 static const int kSz[8] = {0, 0, 0, 0, 1, 1, 1, 1};
 
-int build_hex_plan(const Plan &P, const int *etype, const int *eptr, const int *emat, const double *E_nu, int nmts,
-                   HexPlan *H, std::string *why) {
+int build_hex_plan(const Plan &P, const int *etype, const int *eptr, HexPlan *H, std::string *why) {
   H->ok = false;
   const int nels = P.nels, nn = P.nlnds;
   if (P.pdim != 3 || nels == 0) { *why = "not a 3-D mesh"; return 0; }
   for (int e = 0; e < nels; ++e)
     if (etype[e] != FEMX_HEX) { *why = "mesh holds non-hex8 elements"; return 0; }
-  // one Poisson ratio (lambda/mu) for all elements: E may vary, it is folded into the geometry factor
-  const double nu0 = E_nu[2 * (emat[0] - 1) + 1];
-  std::vector<char> used(nmts, 0);
-  for (int e = 0; e < nels; ++e) used[emat[e] - 1] = 1;
-  for (int m = 0; m < nmts; ++m)
-    if (used[m] && E_nu[2 * m + 1] != nu0) { *why = "elements with different Poisson ratios"; return 0; }
-  H->rho = 2.0 * nu0 / (1.0 - 2.0 * nu0);  // lambda / mu
-
   // breadth-first assignment of logical coordinates
   const int UNSET = INT32_MIN;
   std::vector<int32_t> ci(nn, UNSET), cj(nn, UNSET), ck(nn, UNSET);

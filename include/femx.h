@@ -61,15 +61,14 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh (12 for a logical hex8 grid, 11 for a pure tri3 / tet4
- * mesh, else 9, else 1),
- * 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather), 2 = fused node-row tile kernel,
- * 3 = its warp-specialised form, 5 = symmetric pair-block kernel on 16 warps (6, 7, 8: its measured tile / thread
- * variants, 4 = alias of 8), 12 = variant 5 with the gather lanes ordered by contribution count (13: the same with
- * per-phase clock accounting on stderr), 9 = fused rows kernel for any element mix, 11 = simplex rows kernel (tri3 / tet4 only) */
+/* assembly variants: 0 = best available for the mesh (12 for a logical hex8 grid, 11 for a pure
+ * tri3 / tet4 mesh, else 9, else 1); 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather; the cross-check);
+ * 9 = fused rows kernel for any element mix; 11 = simplex rows kernel (tri3 / tet4 only); 12 = symmetric pair-block hex8
+ * tile kernel; 20 = warp-specialised DMMA hex8 tile kernel.  Any other value is refused by femx_create (13 / 21, the
+ * clock-accounting builds of 12 / 20, exist only in a library built with `make DIAG=1`). */
 typedef struct {
   int quirks;            /* FEMX_Q_* bits                                   */
-  int assembly_variant;  /* 0 auto, 1 two-pass, 2..8, 12, 13 hex8 tile kernels, 9 fused rows, 11 simplex rows */
+  int assembly_variant;  /* 0 auto, 1 two-pass, 9 fused rows, 11 simplex rows, 12 / 20 hex8 tile kernels */
   int reserved[6];
 } femx_opts;
 

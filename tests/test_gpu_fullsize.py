@@ -24,24 +24,22 @@ def test_c2_hex100_cross_variant_and_rigid_modes():
     m = mg.jitter(mg.hex_cube(100, clamp=False))
     u = mg.displacement_field(m)
     out = {}
-    for var in (5, 3, 12, 13):
+    for var in (12, 20, 9):
         with api.Femx(assembly_variant=var) as f:
             f.set_mesh(m).build_plan()
             vals, fint = f.assemble_K_fint(u)
             assert f.nnz == 245438109 and len(vals) == f.nnz
-            if var == 5:
+            if var != 9:
                 _, f_tr = f.assemble_K_fint(np.tile([1.0, -2.0, 0.5], (m.nlnds, 1)))
                 assert np.abs(f_tr).max() <= 1e-10 * np.abs(vals).max()
             out[var] = (vals, fint)
-    # element-centric symmetric kernel vs node-row kernel: different summation trees, same matrix
-    scale = np.abs(out[3][0]).max()
-    assert np.abs(out[5][0] - out[3][0]).max() <= 1e-12 * scale
-    assert _rel(out[5][1], out[3][1]) <= 1e-12
-    assert np.isfinite(out[5][0]).all()
-    # variant 12 (permuted gather lanes): every matrix value sums the same contributions in the same order -> same bits
-    for var in (12, 13):
-        assert np.array_equal(out[var][0], out[5][0]), var
-        assert _rel(out[var][1], out[5][1]) <= 1e-12, var
+    # three independent algorithms (symmetric pair blocks with FMA, DMMA tiles with in-register y sums, per-row recompute in
+    # the general fused rows kernel): different summation trees, same matrix
+    scale = np.abs(out[9][0]).max()
+    for var in (12, 20):
+        assert np.abs(out[var][0] - out[9][0]).max() <= 1e-12 * scale, var
+        assert _rel(out[var][1], out[9][1]) <= 1e-12, var
+        assert np.isfinite(out[var][0]).all()
 
 
 def test_c3_tet94_rigid_modes_and_constant_stress():
