@@ -59,11 +59,14 @@ SIGNATURES = {
     "femx_set_loads": (C.c_int, [V, C.c_int, c_int_p, c_double_p, C.c_int, c_int_p, c_double_p]),
     "femx_form_rhs": (C.c_int, [V, C.c_double, C.c_double, C.c_double, V, C.c_int]),
     "femx_peer_arena_create": (C.c_int, [V, C.c_int64, C.c_int64, V]),
-    "femx_peer_connect": (C.c_int, [V, C.c_int, C.c_int, V, V, V, V, V, V, V]),
+    "femx_peer_connect": (C.c_int, [V, C.c_int, C.c_int, V, V, V, V, V, V, V, V]),
+    "femx_peer_connect_local": (C.c_int, [V, C.c_int, C.c_int, V, V, V, V, V, V, V, V]),
+    "femx_peer_set_merge": (C.c_int, [V, C.c_int64, V, V, V, C.c_int64, V, V, V]),
+    "femx_peer_merged": (C.c_int, [V, V, V]),
+    "femx_peer_complete": (C.c_int, [V]),
+    "femx_peer_last_error": (C.c_int, [V]),
     "femx_peer_recv": (C.c_int, [V, V, V]),
     "femx_peer_disconnect": (C.c_int, [V]),
-    "femx_nccl_unique_id": (C.c_int, [C.c_char_p]),
-    "femx_comm_init": (C.c_int, [V, C.c_char_p]),
     "femx_launch_count": (C.c_int64, [V]),
     "femx_last_kernel_ms": (C.c_double, [V]),
     "femx_version": (C.c_int, []),

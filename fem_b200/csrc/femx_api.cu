@@ -242,15 +242,6 @@ int femx_set_ownership(femx_ctx *c, int nranks, int rank, int64_t row_start, int
   c->own_nranks = nranks; c->own_rank = rank; c->own_row_start = row_start; c->own_row_end = row_end;
   return FEMX_OK;
 }
-// The library creates no NCCL communicator of its own: interface rows travel through femx_peer_* (peer memory over
-// NVLink, csrc/peer.cu) or through the host's MPI / NCCL (fem_b200/parallel.py keeps the NCCL all_to_all as fallback).
-int femx_nccl_unique_id(char id[128]) { memset(id, 0, 128); return FEMX_ERR_UNSUPPORTED; }
-int femx_comm_init(femx_ctx *c, const char id[128]) {
-  (void)id;
-  if (c) c->err = "no NCCL communicator inside the library: use femx_peer_* or exchange the value slices on the host side";
-  return FEMX_ERR_UNSUPPORTED;
-}
-
 // --------------------------------------------------------------------------- plan
 int femx_build_plan(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;

@@ -88,11 +88,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
   if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;
   if ((rc = finish_call(c, true))) return rc;
-  if (peer) {
-    int e = 0;
-    CK(cudaMemcpy(&e, c->peer.d_err, sizeof(int), cudaMemcpyDeviceToHost));
-    if (e) { c->err = "peer exchange: rank " + std::to_string(e - 1) + " did not reach the step barrier"; return FEMX_ERR_CUDA; }
-  }
+  if (peer && (rc = femx_peer_last_error(c))) return rc;
   return FEMX_OK;
 }
 

@@ -229,6 +229,15 @@ struct femx_ctx {
     unsigned long long step = 0;           // assemblies done; buffer parity = step & 1
     int *d_err = nullptr;
     bool connected = false;
+    bool local = false;                    // peers are ctxs of this process on the same device (femx_peer_connect_local): no IPC mapping
     bool in_kernel = false;                // this assembly's kernel stores the interface rows itself (PEER instantiation)
+    unsigned nbr_mask = 0;                 // ranks this one exchanges a non-empty slice with (either direction): the step barrier's scope
+    bool deferred = false;                 // assemblies signal but do not wait / merge; femx_peer_complete does (ranks driven in turn on one GPU)
+    bool pending = false;                  // ... and one is outstanding
+    double *pend_vals = nullptr, *pend_fint = nullptr;
+    // receiver add over the interface rows (femx_peer_set_merge)
+    int64_t n_merge = 0, n_fmerge = 0;
+    int64_t *d_mown = nullptr, *d_mptr = nullptr, *d_midx = nullptr, *d_frow = nullptr, *d_fptr = nullptr, *d_fidx = nullptr;
+    double *d_merged = nullptr;
   } peer;
 };

@@ -29,7 +29,7 @@ int launch_hex_sym7(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
 int launch_hex_mma(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_mma_prof(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 PeerTab peer_tab(const femx_ctx *c);          // peer.cu
-int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, const double *d_fint);
+int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_fint);   // push + step barrier + receiver add
 bool rows_fused_ok(const femx_ctx *c);
 int launch_rows_fused(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 bool rows_simplex_ok(const femx_ctx *c);     // rows_simplex.cu

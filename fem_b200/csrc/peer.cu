@@ -30,13 +30,19 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 
 struct FlagPtrs { unsigned long long *remote[kMaxPeers]; };
 
-// lane q: tell rank q that this rank's stores of assembly `step` are done, then wait for q's
-__device__ __forceinline__ void signal_wait(const FlagPtrs &fp, unsigned long long *mine, int n, int rank, unsigned long long step,
-                                            long long limit_clocks, int *err) {
+// lane q: tell NEIGHBOUR rank q (a rank this one exchanges a non-empty slice with, in either direction) that this rank's
+// stores of assembly `step` are done, then wait for q's.  Ranks that share no row are neither signalled nor awaited: a
+// step costs the slowest neighbour, not the slowest of all ranks.  wait = false: signal only (the caller waits later,
+// femx_peer_complete -- used when several ranks are driven one after another on one GPU).
+__device__ __forceinline__ void signal_wait(const FlagPtrs &fp, unsigned long long *mine, int n, int rank, unsigned nbr_mask, unsigned long long step,
+                                            long long limit_clocks, int *err, bool sig, bool wait) {
   const int q = threadIdx.x;
-  if (q >= n || q == rank) return;
-  __threadfence_system();
-  st_release_sys(fp.remote[q] + 8 * rank, step);
+  if (q >= n || q == rank || !((nbr_mask >> q) & 1u)) return;
+  if (sig) {
+    __threadfence_system();
+    st_release_sys(fp.remote[q] + 8 * rank, step);
+  }
+  if (!wait) return;
   const long long t0 = clock64();
   while (ld_acquire_sys(mine + 8 * q) < step) {
     if (clock64() - t0 > limit_clocks) { *err = 1 + q; break; }   // a dead peer must not hang the GPU
@@ -44,9 +50,9 @@ __device__ __forceinline__ void signal_wait(const FlagPtrs &fp, unsigned long lo
   }
 }
 
-__global__ void peer_signal_wait_kernel(FlagPtrs fp, unsigned long long *mine, int n, int rank, unsigned long long step,
-                                        long long limit_clocks, int *err) {
-  signal_wait(fp, mine, n, rank, step, limit_clocks, err);
+__global__ void peer_signal_wait_kernel(FlagPtrs fp, unsigned long long *mine, int n, int rank, unsigned nbr_mask, unsigned long long step,
+                                        long long limit_clocks, int *err, bool sig, bool wait) {
+  signal_wait(fp, mine, n, rank, nbr_mask, step, limit_clocks, err, sig, wait);
 }
 
 // Push form (works behind every assembly variant): the kernel wrote all of its rows into the local arrays; copy the
@@ -54,7 +60,8 @@ __global__ void peer_signal_wait_kernel(FlagPtrs fp, unsigned long long *mine, i
 // to finish runs the step barrier.  fint is indexed by global row, the wire format by local dof (pdim * node + i).
 __global__ void __launch_bounds__(256)
 peer_push_kernel(PeerTab pt, const double *__restrict__ vals, const double *__restrict__ fint, const int32_t *__restrict__ nl2g, int pdim,
-                 FlagPtrs fp, unsigned long long *mine, unsigned long long step, long long limit_clocks, int *err, unsigned int *ticket) {
+                 FlagPtrs fp, unsigned long long *mine, unsigned nbr_mask, unsigned long long step, long long limit_clocks, int *err, unsigned int *ticket,
+                 bool wait) {
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
   for (int q = 0; q < pt.n; ++q) {
     if (q == pt.rank) continue;
@@ -79,7 +86,28 @@ peer_push_kernel(PeerTab pt, const double *__restrict__ vals, const double *__re
   __syncthreads();
   if (!last) return;
   if (threadIdx.x == 0) *ticket = 0;
-  signal_wait(fp, mine, pt.n, pt.rank, step, limit_clocks, err);
+  signal_wait(fp, mine, pt.n, pt.rank, nbr_mask, step, limit_clocks, err, true, wait);
+}
+
+// Receiver add (the part of MatAssemblyEnd that sums the stash into the owned rows, src/main.F90:167-168), interface rows
+// only: entry s of the merged interface rows = this rank's own value (slot own[s] of the local CSR, -1 = the rank has no
+// such entry) + the received values idx[ptr[s]..ptr[s+1]) in list order = (source rank, sender position): deterministic.
+__global__ void peer_merge_kernel(const double *__restrict__ vals, const double *__restrict__ recv, const int64_t *__restrict__ own,
+                                  const int64_t *__restrict__ ptr, const int64_t *__restrict__ idx, int64_t n, double *__restrict__ out) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  double v = own[s] >= 0 ? vals[own[s]] : 0.0;
+  for (int64_t q = ptr[s]; q < ptr[s + 1]; ++q) v += recv[idx[q]];
+  out[s] = v;
+}
+// owned internal-force entries: fint[row[s]] += received entries in (source rank, position) order
+__global__ void peer_merge_f_kernel(double *__restrict__ fint, const double *__restrict__ recv_f, const int64_t *__restrict__ row,
+                                    const int64_t *__restrict__ ptr, const int64_t *__restrict__ idx, int64_t n) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  double v = fint[row[s]];
+  for (int64_t q = ptr[s]; q < ptr[s + 1]; ++q) v += recv_f[idx[q]];
+  fint[row[s]] = v;
 }
 
 int64_t buffer_doubles(int64_t nv, int64_t nf) { return nv + nf; }
@@ -105,26 +133,46 @@ PeerTab peer_tab(const femx_ctx *c) {
   return t;
 }
 
+static int launch_peer_merge(femx_ctx *c, const double *d_vals, double *d_fint) {
+  auto &P = c->peer;
+  int n = 0;
+  const int par = (int)((P.step - 1) & 1);   // the buffer the assembly that just ran filled
+  const double *buf = reinterpret_cast<const double *>(P.arena + kFlagBytes) + par * buffer_doubles(P.nv, P.nf);
+  if (P.n_merge > 0) {
+    peer_merge_kernel<<<(unsigned)((P.n_merge + 255) / 256), 256, 0, c->stream>>>(d_vals, buf, P.d_mown, P.d_mptr, P.d_midx, P.n_merge, P.d_merged);
+    ++n;
+  }
+  if (P.n_fmerge > 0 && d_fint) {
+    peer_merge_f_kernel<<<(unsigned)((P.n_fmerge + 255) / 256), 256, 0, c->stream>>>(d_fint, buf + P.nv, P.d_frow, P.d_fptr, P.d_fidx, P.n_fmerge);
+    ++n;
+  }
+  return n;
+}
+
 // fused = the assembly kernel already stored the interface rows at their owners (PEER instantiations)
-int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, const double *d_fint) {
+int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_fint) {
   auto &P = c->peer;
   FlagPtrs fp{};
   for (int q = 0; q < P.nranks; ++q) fp.remote[q] = reinterpret_cast<unsigned long long *>(P.remote[q]);
   unsigned long long *mine = reinterpret_cast<unsigned long long *>(P.arena);
   const long long limit = 20000000000ll;   // ~10 s
+  const bool wait = !P.deferred;
+  int n = 1;
   if (fused) {
     ++P.step;
-    peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, mine, P.nranks, P.rank, P.step, limit, P.d_err);
-    return 1;
+    peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, mine, P.nranks, P.rank, P.nbr_mask, P.step, limit, P.d_err, true, wait);
+  } else {
+    const PeerTab pt = peer_tab(c);   // destinations of the current step's buffer
+    ++P.step;
+    int64_t nv = 0;
+    for (int q = 0; q < P.nranks; ++q) if (q != P.rank) nv += P.vb[q + 1] - P.vb[q];
+    int grid = (int)std::min<int64_t>(296, std::max<int64_t>(1, (nv + 255) / 256 / 8));
+    peer_push_kernel<<<grid, 256, 0, c->stream>>>(pt, d_vals, d_fint, c->dm.nl2g, c->pdim, fp, mine, P.nbr_mask, P.step, limit, P.d_err,
+                                                  reinterpret_cast<unsigned int *>(P.d_err + 1), wait);
   }
-  const PeerTab pt = peer_tab(c);   // destinations of the current step's buffer
-  ++P.step;
-  int64_t n = 0;
-  for (int q = 0; q < P.nranks; ++q) if (q != P.rank) n += P.vb[q + 1] - P.vb[q];
-  int grid = (int)std::min<int64_t>(296, std::max<int64_t>(1, (n + 255) / 256 / 8));
-  peer_push_kernel<<<grid, 256, 0, c->stream>>>(pt, d_vals, d_fint, c->dm.nl2g, c->pdim, fp, mine, P.step, limit, P.d_err,
-                                                reinterpret_cast<unsigned int *>(P.d_err + 1));
-  return 1;
+  if (wait) n += launch_peer_merge(c, d_vals, d_fint);
+  else { P.pending = true; P.pend_vals = const_cast<double *>(d_vals); P.pend_fint = d_fint; }
+  return n;
 }
 
 }  // namespace femx
@@ -154,19 +202,19 @@ int femx_peer_arena_create(femx_ctx *c, int64_t n_recv_vals, int64_t n_recv_f, c
   return FEMX_OK;
 }
 
-int femx_peer_connect(femx_ctx *c, int nranks, int rank, const char *handles, const int64_t *recv_vals, const int64_t *recv_f,
-                      const int64_t *val_bounds, const int64_t *val_dst, const int64_t *f_bounds, const int64_t *f_dst) {
-  if (!c) return FEMX_ERR_ARG;
+static int peer_connect_common(femx_ctx *c, int nranks, int rank, const int64_t *recv_vals, const int64_t *recv_f, const int64_t *val_bounds,
+                               const int64_t *val_dst, const int64_t *f_bounds, const int64_t *f_dst, const int64_t *recv_from) {
   ARG(c->has_plan, "femx_build_plan first");
   ARG(c->peer.arena, "femx_peer_arena_create first");
+  ARG(!c->peer.connected, "already connected (femx_peer_disconnect first)");
   ARG(nranks >= 2 && nranks <= kMaxPeers && rank >= 0 && rank < nranks, "peer exchange handles 2..8 ranks of one node");
-  ARG(handles && recv_vals && recv_f && val_bounds && val_dst && f_bounds && f_dst, "NULL argument");
+  ARG(recv_vals && recv_f && val_bounds && val_dst && f_bounds && f_dst && recv_from, "NULL argument");
   ARG(c->own_row_end < 0 || (c->own_nranks == nranks && c->own_rank == rank), "femx_set_ownership named another rank / rank count");
   ARG(val_bounds[0] == 0 && val_bounds[nranks] == c->nnz, "val_bounds must span the local values");
   ARG(f_bounds[0] == 0 && f_bounds[nranks] == (int64_t)c->pdim * c->nlnds, "f_bounds must span the local dofs");
-  CK(cudaSetDevice(c->device));
   auto &P = c->peer;
   P.nranks = nranks; P.rank = rank;
+  P.nbr_mask = 0;
   for (int q = 0; q <= nranks; ++q) { P.vb[q] = val_bounds[q]; P.fb[q] = f_bounds[q]; }
   for (int q = 0; q < nranks; ++q) {
     ARG(val_bounds[q] <= val_bounds[q + 1] && f_bounds[q] <= f_bounds[q + 1], "bounds must ascend");
@@ -175,15 +223,128 @@ int femx_peer_connect(femx_ctx *c, int nranks, int rank, const char *handles, co
     if (q == rank) continue;
     ARG(val_dst[q] >= 0 && val_dst[q] + (val_bounds[q + 1] - val_bounds[q]) <= recv_vals[q], "value slice does not fit the peer's arena");
     ARG(f_dst[q] >= 0 && f_dst[q] + (f_bounds[q + 1] - f_bounds[q]) <= recv_f[q], "force slice does not fit the peer's arena");
+    // neighbours: a non-empty slice in either direction (the relation is symmetric: q computes the same from its side)
+    if (val_bounds[q + 1] > val_bounds[q] || f_bounds[q + 1] > f_bounds[q] || recv_from[q] > 0) P.nbr_mask |= 1u << q;
+  }
+  return FEMX_OK;
+}
+
+int femx_peer_connect(femx_ctx *c, int nranks, int rank, const char *handles, const int64_t *recv_vals, const int64_t *recv_f,
+                      const int64_t *val_bounds, const int64_t *val_dst, const int64_t *f_bounds, const int64_t *f_dst,
+                      const int64_t *recv_from) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(handles, "NULL argument");
+  int rc = peer_connect_common(c, nranks, rank, recv_vals, recv_f, val_bounds, val_dst, f_bounds, f_dst, recv_from);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device));
+  auto &P = c->peer;
+  for (int q = 0; q < nranks; ++q) {
+    if (q == rank) continue;
     cudaIpcMemHandle_t h;
     memcpy(&h, handles + 64 * (size_t)q, 64);
     void *p = nullptr;
     CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     P.remote[q] = (char *)p;
   }
-  P.step = 0;
+  // the step counter is NOT reset: the arenas' flag words keep the steps of earlier connections, and every rank has run
+  // the same number of (collective) assemblies
+  P.local = false;
   P.connected = true;
   return FEMX_OK;
+}
+
+// Ranks that are ctxs of ONE process on ONE device (tests on a single GPU; a host that drives several partitions per
+// GPU): the peers' arenas are plain device pointers.  Such ranks run one after another on the device, so a kernel must
+// never wait for a peer that has not been launched yet: assemblies only push and signal (deferred = 1), and
+// femx_peer_complete -- called on every rank after all of them have assembled -- checks the flags and runs the receiver add.
+int femx_peer_connect_local(femx_ctx *c, int nranks, int rank, femx_ctx *const *peers, const int64_t *recv_vals, const int64_t *recv_f,
+                            const int64_t *val_bounds, const int64_t *val_dst, const int64_t *f_bounds, const int64_t *f_dst,
+                            const int64_t *recv_from) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(peers, "NULL argument");
+  int rc = peer_connect_common(c, nranks, rank, recv_vals, recv_f, val_bounds, val_dst, f_bounds, f_dst, recv_from);
+  if (rc) return rc;
+  auto &P = c->peer;
+  for (int q = 0; q < nranks; ++q) {
+    if (q == rank) continue;
+    ARG(peers[q] && peers[q]->peer.arena && peers[q]->device == c->device, "local peers must be ctxs with an arena on the same device");
+    ARG(peers[q]->peer.nv == recv_vals[q] && peers[q]->peer.nf == recv_f[q], "peer arena capacity mismatch");
+    P.remote[q] = peers[q]->peer.arena;
+  }
+  P.local = true;
+  P.deferred = true;
+  P.connected = true;
+  return FEMX_OK;
+}
+
+int femx_peer_set_merge(femx_ctx *c, int64_t n, const int64_t *own_slot, const int64_t *ptr, const int64_t *idx, int64_t nf,
+                        const int64_t *f_row, const int64_t *f_ptr, const int64_t *f_idx) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->peer.arena, "femx_peer_arena_create first");
+  ARG(n >= 0 && nf >= 0 && (n == 0 || (own_slot && ptr && idx)) && (nf == 0 || (f_row && f_ptr && f_idx)), "bad merge lists");
+  CK(cudaSetDevice(c->device));
+  auto &P = c->peer;
+  for (int64_t s = 0; s < n; ++s) ARG(own_slot[s] >= -1 && own_slot[s] < c->nnz && ptr[s] <= ptr[s + 1], "merge list: bad own slot / ptr");
+  for (int64_t q = 0; q < (n ? ptr[n] : 0); ++q) ARG(idx[q] >= 0 && idx[q] < P.nv, "merge list: received index outside the arena");
+  for (int64_t s = 0; s < nf; ++s) ARG(f_row[s] >= 0 && f_row[s] < (int64_t)c->pdim * c->nnds && f_ptr[s] <= f_ptr[s + 1], "force merge list: bad row / ptr");
+  for (int64_t q = 0; q < (nf ? f_ptr[nf] : 0); ++q) ARG(f_idx[q] >= 0 && f_idx[q] < P.nf, "force merge list: received index outside the arena");
+  for (void *q : {(void *)P.d_mown, (void *)P.d_mptr, (void *)P.d_midx, (void *)P.d_frow, (void *)P.d_fptr, (void *)P.d_fidx, (void *)P.d_merged}) dev_release(c, q);
+  P.d_mown = P.d_mptr = P.d_midx = P.d_frow = P.d_fptr = P.d_fidx = nullptr; P.d_merged = nullptr;
+  P.n_merge = n; P.n_fmerge = nf;
+  int rc;
+  if (n > 0) {
+    if ((rc = upload(c, &P.d_mown, std::vector<int64_t>(own_slot, own_slot + n))) || (rc = upload(c, &P.d_mptr, std::vector<int64_t>(ptr, ptr + n + 1))) ||
+        (rc = upload(c, &P.d_midx, std::vector<int64_t>(idx, idx + ptr[n]))) || (rc = dev_alloc(c, &P.d_merged, n)))
+      return rc;
+  }
+  if (nf > 0) {
+    if ((rc = upload(c, &P.d_frow, std::vector<int64_t>(f_row, f_row + nf))) || (rc = upload(c, &P.d_fptr, std::vector<int64_t>(f_ptr, f_ptr + nf + 1))) ||
+        (rc = upload(c, &P.d_fidx, std::vector<int64_t>(f_idx, f_idx + f_ptr[nf]))))
+      return rc;
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+
+int femx_peer_merged(femx_ctx *c, const double **merged, int64_t *n) {
+  if (!c) return FEMX_ERR_ARG;
+  if (merged) *merged = c->peer.d_merged;
+  if (n) *n = c->peer.n_merge;
+  return FEMX_OK;
+}
+
+static int peer_check_error(femx_ctx *c) {
+  int e = 0;
+  CK(cudaMemcpy(&e, c->peer.d_err, sizeof(int), cudaMemcpyDeviceToHost));
+  if (e) {
+    CK(cudaMemset(c->peer.d_err, 0, sizeof(int)));   // reported once, not sticky
+    c->err = "peer exchange: rank " + std::to_string(e - 1) + " did not reach the step barrier";
+    return FEMX_ERR_CUDA;
+  }
+  return FEMX_OK;
+}
+
+int femx_peer_complete(femx_ctx *c) {
+  if (!c) return FEMX_ERR_ARG;
+  auto &P = c->peer;
+  ARG(P.connected && P.deferred, "femx_peer_complete belongs to deferred (local) peer connections");
+  ARG(P.pending, "no assembly is outstanding");
+  CK(cudaSetDevice(c->device));
+  FlagPtrs fp{};
+  for (int q = 0; q < P.nranks; ++q) fp.remote[q] = reinterpret_cast<unsigned long long *>(P.remote[q]);
+  // every peer has already signalled (its assembly ran before this call): a short limit turns a protocol error into a message
+  peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, reinterpret_cast<unsigned long long *>(P.arena), P.nranks, P.rank, P.nbr_mask, P.step, 2000000ll,
+                                                   P.d_err, false, true);
+  c->launches += 1 + launch_peer_merge(c, P.pend_vals, P.pend_fint);
+  P.pending = false;
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  return peer_check_error(c);
+}
+
+int femx_peer_last_error(femx_ctx *c) {   // used by the assemble path
+  if (!c) return FEMX_ERR_ARG;
+  return peer_check_error(c);
 }
 
 int femx_peer_recv(femx_ctx *c, const double **vals_recv, const double **f_recv) {
@@ -203,8 +364,9 @@ int femx_peer_disconnect(femx_ctx *c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   for (int q = 0; q < kMaxPeers; ++q)
-    if (P.remote[q]) { cudaIpcCloseMemHandle(P.remote[q]); P.remote[q] = nullptr; }
+    if (P.remote[q]) { if (!P.local) cudaIpcCloseMemHandle(P.remote[q]); P.remote[q] = nullptr; }
   P.connected = false;   // the arena stays until femx_destroy: peers may still have it mapped
+  P.deferred = false; P.pending = false;
   return FEMX_OK;
 }
 

@@ -41,103 +41,160 @@ class ExchangePlan:
     send_hi: np.ndarray
     send_rows: list             # per destination: global rows / cols of the slice (setup only)
     send_cols: list
+    send_frows: list = None     # per destination: global rows of the internal-force entries of the slice
+    f_bounds: np.ndarray = None # [nranks+1] local dofs (pdim*node + i) by owner
     recv_counts: np.ndarray = None
-    coo_i: np.ndarray = None    # COO of the rank's output (own slice first, then per source rank)
+    recv_fcounts: np.ndarray = None
+    coo_i: np.ndarray = None    # COO of what the rank receives (source-rank order)
     coo_j: np.ndarray = None
-    # merged owned CSR
-    rowptr: np.ndarray = None   # [row_end-row_start+1]
-    colidx: np.ndarray = None
-    merge_ptr: np.ndarray = None
-    merge_idx: np.ndarray = None
+    # receiver add over the interface rows (rows of this rank that receive contributions)
+    if_rows: np.ndarray = None  # global rows, ascending
+    if_rowptr: np.ndarray = None
+    if_colidx: np.ndarray = None
+    m_own: np.ndarray = None    # per merged entry: local value slot of this rank's own contribution, -1 = none
+    m_ptr: np.ndarray = None
+    m_idx: np.ndarray = None    # positions in the receive arena, (source rank, sender position) order
+    f_row: np.ndarray = None    # owned global rows that receive internal-force entries
+    f_ptr: np.ndarray = None
+    f_idx: np.ndarray = None
 
 
-def plan_sends(rowptr: np.ndarray, colidx: np.ndarray, nrows: int, nranks: int, rank: int) -> ExchangePlan:
+def _ranges(starts: np.ndarray, lens: np.ndarray) -> np.ndarray:
+    """concatenate(arange(s, s + l) for s, l in zip(starts, lens)) without a Python loop"""
+    lens = np.asarray(lens, np.int64)
+    tot = int(lens.sum())
+    if tot == 0:
+        return np.zeros(0, np.int64)
+    off = np.concatenate([[0], np.cumsum(lens)[:-1]])
+    return np.repeat(np.asarray(starts, np.int64) - off, lens) + np.arange(tot, dtype=np.int64)
+
+
+def plan_sends(rowptr: np.ndarray, colidx: np.ndarray, nrows: int, nranks: int, rank: int, nl2g=None, pdim: int = 0) -> ExchangePlan:
     """Split the rank-local CSR (global row numbering, rows of absent nodes empty) by row owner."""
     bounds = np.array([petsc_ownership(nrows, nranks, r)[0] for r in range(nranks)] + [nrows], dtype=np.int64)
     lo = rowptr[bounds[:-1]].astype(np.int64)
     hi = rowptr[bounds[1:]].astype(np.int64)
-    rows_of = lambda r0, r1: np.repeat(np.arange(r0, r1, dtype=np.int64), np.diff(rowptr[r0:r1 + 1]))
     send_rows, send_cols = [], []
     for q in range(nranks):
-        if q == rank:
+        if q == rank or hi[q] == lo[q]:
             send_rows.append(np.zeros(0, np.int64)); send_cols.append(np.zeros(0, np.int64))
         else:
-            send_rows.append(rows_of(bounds[q], bounds[q + 1]))
+            r0, r1 = int(bounds[q]), int(bounds[q + 1])
+            send_rows.append(np.repeat(np.arange(r0, r1, dtype=np.int64), np.diff(rowptr[r0:r1 + 1])))
             send_cols.append(colidx[lo[q]:hi[q]].astype(np.int64))
-    return ExchangePlan(nranks=nranks, rank=rank, row_start=int(bounds[rank]), row_end=int(bounds[rank + 1]),
-                        own_lo=int(lo[rank]), own_hi=int(hi[rank]), send_lo=lo, send_hi=hi,
-                        send_rows=send_rows, send_cols=send_cols)
+    ep = ExchangePlan(nranks=nranks, rank=rank, row_start=int(bounds[rank]), row_end=int(bounds[rank + 1]),
+                      own_lo=int(lo[rank]), own_hi=int(hi[rank]), send_lo=lo, send_hi=hi,
+                      send_rows=send_rows, send_cols=send_cols)
+    if nl2g is not None:      # internal-force entries travel by local dof, pdim * node + i: the sender names the global rows
+        gdof = (pdim * (np.asarray(nl2g, np.int64) - 1)[:, None] + np.arange(pdim)[None, :]).reshape(-1)
+        assert np.all(np.diff(gdof) > 0), "local nodes must ascend in global id"
+        ep.f_bounds = np.searchsorted(gdof, bounds).astype(np.int64)
+        ep.send_frows = [gdof[ep.f_bounds[q]:ep.f_bounds[q + 1]] if q != rank else np.zeros(0, np.int64) for q in range(nranks)]
+    return ep
 
 
 def finish_plan(ep: ExchangePlan, rowptr: np.ndarray, colidx: np.ndarray, recv_rows: list, recv_cols: list,
-                with_merge: bool = True) -> ExchangePlan:
-    """After the one-time (row, col) exchange: COO lists and the merged owned CSR."""
+                recv_frows: list | None = None) -> ExchangePlan:
+    """After the one-time (row, col) exchange: COO lists of the received part and the receiver-add lists over the interface
+    rows -- O(interface) setup and O(interface) work per assembly (csrc/peer.cu: peer_merge_kernel)."""
     r0, r1 = ep.row_start, ep.row_end
     ep.recv_counts = np.array([len(x) for x in recv_rows], dtype=np.int64)
     for x in recv_rows:
         assert np.all((np.asarray(x) >= r0) & (np.asarray(x) < r1)), "received a row this rank does not own"
-    if not with_merge:          # COO lists of the received part only (the own part is the local CSR slice)
-        ep.coo_i = np.concatenate([np.asarray(x, np.int64) for x in recv_rows]) if recv_rows else np.zeros(0, np.int64)
-        ep.coo_j = np.concatenate([np.asarray(x, np.int64) for x in recv_cols]) if recv_cols else np.zeros(0, np.int64)
-        return ep
-    own_rows = np.repeat(np.arange(r0, r1, dtype=np.int64), np.diff(rowptr[r0:r1 + 1]))
-    own_cols = colidx[ep.own_lo:ep.own_hi].astype(np.int64)
-    ep.coo_i = np.concatenate([own_rows] + [np.asarray(x, np.int64) for x in recv_rows])
-    ep.coo_j = np.concatenate([own_cols] + [np.asarray(x, np.int64) for x in recv_cols])
-    # union pattern; stable sort keeps (own, source rank, sender position) order inside each nonzero
-    ncols = int(ep.coo_j.max()) + 1 if len(ep.coo_j) else 1
-    key = (ep.coo_i - r0) * ncols + ep.coo_j
-    order = np.argsort(key, kind="stable")
-    ks = key[order]
+    ep.coo_i = np.concatenate([np.asarray(x, np.int64) for x in recv_rows]) if recv_rows else np.zeros(0, np.int64)
+    ep.coo_j = np.concatenate([np.asarray(x, np.int64) for x in recv_cols]) if recv_cols else np.zeros(0, np.int64)
+    nrecv = len(ep.coo_i)
+    ep.if_rows = np.unique(ep.coo_i)
+    # this rank's own entries of those rows
+    st = rowptr[ep.if_rows].astype(np.int64)
+    ln = (rowptr[ep.if_rows + 1] - rowptr[ep.if_rows]).astype(np.int64)
+    own_slots = _ranges(st, ln)
+    own_rows = np.repeat(ep.if_rows, ln)
+    own_cols = colidx[own_slots].astype(np.int64)
+    ncols = int(max(ep.coo_j.max() if nrecv else 0, own_cols.max() if len(own_cols) else 0)) + 1
+    key = np.concatenate([own_rows * ncols + own_cols, ep.coo_i * ncols + ep.coo_j])
+    src = np.concatenate([-1 - own_slots, np.arange(nrecv, dtype=np.int64)])      # own: -1 - slot; received: arena position
+    order = np.argsort(key, kind="stable")      # inside a nonzero: own first, then (source rank, sender position)
+    ks, ss = key[order], src[order]
     first = np.ones(len(ks), bool)
     first[1:] = ks[1:] != ks[:-1]
     starts = np.nonzero(first)[0]
-    ep.merge_ptr = np.concatenate([starts, [len(ks)]]).astype(np.int64)
-    ep.merge_idx = order.astype(np.int64)
-    urow = (ks[starts] // ncols).astype(np.int64)
-    ep.colidx = (ks[starts] % ncols).astype(np.int32)
-    ep.rowptr = np.zeros(r1 - r0 + 1, np.int64)
-    np.add.at(ep.rowptr, urow + 1, 1)
-    np.cumsum(ep.rowptr, out=ep.rowptr)
+    nmer = len(starts)
+    has_own = ss[starts] < 0 if nmer else np.zeros(0, bool)
+    ep.m_own = np.where(has_own, -1 - ss[starts], -1).astype(np.int64) if nmer else np.zeros(0, np.int64)
+    counts = np.diff(np.concatenate([starts, [len(ks)]])) - has_own.astype(np.int64) if nmer else np.zeros(0, np.int64)
+    ep.m_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    ep.m_idx = ss[ss >= 0].astype(np.int64)      # sorted order keeps groups contiguous; own entries drop out
+    urow = ks[starts] // ncols if nmer else np.zeros(0, np.int64)
+    ep.if_colidx = (ks[starts] % ncols).astype(np.int32) if nmer else np.zeros(0, np.int32)
+    ep.if_rowptr = np.concatenate([[0], np.cumsum(np.bincount(np.searchsorted(ep.if_rows, urow), minlength=len(ep.if_rows)))]).astype(np.int64)
+    # internal-force entries
+    if recv_frows is not None:
+        ep.recv_fcounts = np.array([len(x) for x in recv_frows], dtype=np.int64)
+        fr = np.concatenate([np.asarray(x, np.int64) for x in recv_frows]) if recv_frows else np.zeros(0, np.int64)
+        assert np.all((fr >= r0) & (fr < r1)), "received a force entry this rank does not own"
+        fo = np.argsort(fr, kind="stable")
+        frs = fr[fo]
+        ff = np.ones(len(frs), bool)
+        ff[1:] = frs[1:] != frs[:-1]
+        fs = np.nonzero(ff)[0]
+        ep.f_row = frs[fs].astype(np.int64)
+        ep.f_ptr = np.concatenate([fs, [len(frs)]]).astype(np.int64)
+        ep.f_idx = fo.astype(np.int64)
     return ep
 
 
+def owned_csr(ep: ExchangePlan, rowptr: np.ndarray, colidx: np.ndarray, vals_local: np.ndarray, merged: np.ndarray):
+    """Host view of the rank's owned rows after an assembly: the local CSR slice, with the interface rows replaced by their
+    merged form (union pattern).  Used by the parity tests; a PETSc host passes the two pieces to MatSetValuesCOO instead
+    (own slice with the interface rows' i set to -1, which COO ignores, plus the merged rows)."""
+    r0, r1 = ep.row_start, ep.row_end
+    is_if = np.zeros(r1 - r0, bool)
+    is_if[ep.if_rows - r0] = True
+    own_len = np.diff(rowptr[r0:r1 + 1]).astype(np.int64)
+    if_len = np.zeros(r1 - r0, np.int64)
+    if_len[ep.if_rows - r0] = np.diff(ep.if_rowptr)
+    lens = np.where(is_if, if_len, own_len)
+    rp = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    ci = np.empty(rp[-1], np.int32)
+    va = np.empty(rp[-1])
+    keep = ~is_if
+    dst = _ranges(rp[:-1][keep], lens[keep])
+    srcs = _ranges(rowptr[r0:r1][keep], lens[keep])
+    ci[dst] = colidx[srcs]; va[dst] = vals_local[srcs]
+    dst = _ranges(rp[:-1][is_if], lens[is_if])
+    ci[dst] = ep.if_colidx; va[dst] = merged
+    return rp, ci, va
+
+
 def exchange_lists(ep: ExchangePlan, dist, device="cpu"):
-    """One-time exchange of the (row, col) lists with torch.distributed (gloo or NCCL)."""
+    """One-time exchange of the (row, col) lists and of the force rows with torch.distributed (gloo or NCCL).
+    Returns (recv_rows, recv_cols, recv_frows), each a list by source rank."""
     import torch
     P = ep.nranks
-    counts = torch.tensor([len(x) for x in ep.send_rows], dtype=torch.int64, device=device)
-    rcounts = torch.empty(P, dtype=torch.int64, device=device)
-    dist.all_to_all_single(rcounts, counts)
-    rc = rcounts.cpu().tolist()
-    sc = counts.cpu().tolist()
-    out = []
-    for lists in (ep.send_rows, ep.send_cols):
-        send = torch.from_numpy(np.concatenate(lists)).to(device)
+
+    def a2a(lists):
+        counts = torch.tensor([len(x) for x in lists], dtype=torch.int64, device=device)
+        rcounts = torch.empty(P, dtype=torch.int64, device=device)
+        dist.all_to_all_single(rcounts, counts)
+        rc, sc = rcounts.cpu().tolist(), counts.cpu().tolist()
+        send = torch.from_numpy(np.concatenate(lists).astype(np.int64)).to(device)
         recv = torch.empty(int(sum(rc)), dtype=torch.int64, device=device)
         dist.all_to_all_single(recv, send, output_split_sizes=rc, input_split_sizes=sc)
-        out.append(np.split(recv.cpu().numpy(), np.cumsum(rc)[:-1]))
-    return out[0], out[1]
+        return np.split(recv.cpu().numpy(), np.cumsum(rc)[:-1])
+
+    return a2a(ep.send_rows), a2a(ep.send_cols), a2a(ep.send_frows)
 
 
-def peer_layout(ep: ExchangePlan, recv_rows: list, nl2g: np.ndarray, pdim: int, nrows: int, nnz: int):
-    """Index side of the peer-memory exchange (csrc/peer.cu): where each source rank's slice lands in this
-    rank's receive arena, and which local ranges go to which owner.  Returns a dict of int64 arrays:
-      recv_voff / recv_foff [P+1]  start of source s's values / force entries in the arena (source-rank order),
-      f_rows[s]                    global rows of the force entries source s sends (its local rows in my range,
-                                   ascending = the unique rows of its matrix list, every row has a diagonal),
-      val_bounds / f_bounds [P+1]  local value offsets / local dofs (pdim*node + i) by owner."""
-    P = ep.nranks
-    f_rows = [np.unique(np.asarray(r, np.int64)) for r in recv_rows]
-    recv_voff = np.concatenate([[0], np.cumsum([len(r) for r in recv_rows])]).astype(np.int64)
-    recv_foff = np.concatenate([[0], np.cumsum([len(r) for r in f_rows])]).astype(np.int64)
+def peer_layout(ep: ExchangePlan, nnz: int):
+    """Index side of the peer-memory exchange (csrc/peer.cu): where each source rank's slice lands in this rank's
+    receive arena (source-rank order), and which local ranges go to which owner."""
+    recv_voff = np.concatenate([[0], np.cumsum(ep.recv_counts)]).astype(np.int64)
+    recv_foff = np.concatenate([[0], np.cumsum(ep.recv_fcounts)]).astype(np.int64)
     val_bounds = np.concatenate([ep.send_lo, [nnz]]).astype(np.int64)
     assert np.array_equal(ep.send_hi, val_bounds[1:]), "local rows must ascend with their owner"
-    bounds = np.array([petsc_ownership(nrows, P, r)[0] for r in range(P)] + [nrows], dtype=np.int64)
-    gdof = (pdim * (np.asarray(nl2g, np.int64) - 1)[:, None] + np.arange(pdim)[None, :]).reshape(-1)
-    assert np.all(np.diff(gdof) > 0), "local nodes must ascend in global id"
-    f_bounds = np.searchsorted(gdof, bounds).astype(np.int64)
-    return dict(recv_voff=recv_voff, recv_foff=recv_foff, f_rows=f_rows, val_bounds=val_bounds, f_bounds=f_bounds)
+    return dict(recv_voff=recv_voff, recv_foff=recv_foff, val_bounds=val_bounds, f_bounds=ep.f_bounds,
+                recv_from=(ep.recv_counts + ep.recv_fcounts).astype(np.int64))
 
 
 def exchange_offsets(lay: dict, dist, nranks: int, device="cpu"):
@@ -162,31 +219,44 @@ class _DevArray:
         self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f8", "data": (int(ptr), False), "version": 3, "strides": None}
 
 
+def _i64(a):
+    return np.ascontiguousarray(a, np.int64)
+
+
+def _set_merge(fx, ep: ExchangePlan):
+    """hand the receiver-add lists to the library (interface rows only)"""
+    args = [_i64(ep.m_own), _i64(ep.m_ptr), _i64(ep.m_idx), _i64(ep.f_row), _i64(ep.f_ptr), _i64(ep.f_idx)]
+    p = [a.ctypes.data for a in args]
+    fx._ck(fx.L.femx_peer_set_merge(fx.h, len(ep.m_own), p[0], p[1], p[2], len(ep.f_row), p[3], p[4], p[5]))
+
+
 class DistributedAssembly:
     """Per-rank driver: femx context on the local mesh + the exchange plan.
 
-    `vals_local` lives in a torch tensor so that torch.distributed (NCCL) can send slices of it;
-    femx writes into it through its raw device pointer.
+    peer = True (default on GPUs of one node): interface rows travel through femx's peer-memory arenas, the step barrier
+    among neighbours and the receiver add run inside femx_assemble_* (csrc/peer.cu).  peer = False: the value slices go
+    through torch.distributed all_to_all (NCCL; gloo in the CPU tests) after the call and merged_host() adds on the host.
+    `vals_local` lives in a torch tensor; femx writes into it through its raw device pointer.
     """
 
-    def __init__(self, fx, dist, device, with_merge=True, peer=False):
+    def __init__(self, fx, dist, device, peer=False):
         import torch
         self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
-        rowptr, colidx = fx.pattern()
+        self.rowptr, self.colidx = fx.pattern()
         nranks, rank = dist.get_world_size(), dist.get_rank()
-        ep = plan_sends(rowptr, colidx, fx.nrows, nranks, rank)
-        rr, rcs = exchange_lists(ep, dist, device)
-        self.ep = finish_plan(ep, rowptr, colidx, rr, rcs, with_merge)
+        m = fx.mesh
+        ep = plan_sends(self.rowptr, self.colidx, fx.nrows, nranks, rank, m.nl2g, m.pdim)
+        rr, rcs, rf = exchange_lists(ep, dist, device)
+        self.ep = finish_plan(ep, self.rowptr, self.colidx, rr, rcs, rf)
         self.vals_local = torch.empty(fx.nnz, dtype=torch.float64, device=device)
         self.recv = torch.empty(int(self.ep.recv_counts.sum()), dtype=torch.float64, device=device)
         self.send_splits = [int(h - l) if q != rank else 0 for q, (l, h) in enumerate(zip(ep.send_lo, ep.send_hi))]
         self.recv_splits = [int(x) for x in self.ep.recv_counts]
         self.n_own = self.ep.own_hi - self.ep.own_lo
-        self._merge_dev = None
         self.peer = False
         if peer:                 # all ranks or none: a rank whose IPC mapping fails takes everybody back to NCCL
             try:
-                self._connect_peers(rr)
+                self._connect_peers()
                 good = 1
             except Exception as e:   # noqa: BLE001
                 import sys
@@ -198,14 +268,11 @@ class DistributedAssembly:
                 self.fx._ck(self.fx.L.femx_peer_disconnect(self.fx.h))
             self.peer = bool(int(t.item()))
 
-    def _connect_peers(self, recv_rows):
-        """Peer-memory mode: the assembly kernel stores interface rows into the owner's arena (csrc/peer.cu);
-        exchange() then only looks up where the last assembly's receive buffer is."""
+    def _connect_peers(self):
         import ctypes as C
         torch, fx, dist, ep = self.torch, self.fx, self.dist, self.ep
         P = ep.nranks
-        m = fx.mesh
-        self.lay = lay = peer_layout(ep, recv_rows, m.nl2g, m.pdim, fx.nrows, fx.nnz)
+        self.lay = lay = peer_layout(ep, fx.nnz)
         val_dst, f_dst, caps = exchange_offsets(lay, dist, P, self.device)
         handle = (C.c_char * 64)()
         fx._ck(fx.L.femx_peer_arena_create(fx.h, int(caps[ep.rank, 0]), int(caps[ep.rank, 1]), C.addressof(handle)))
@@ -213,10 +280,9 @@ class DistributedAssembly:
         alls = [torch.empty_like(mine) for _ in range(P)]
         dist.all_gather(alls, mine)
         handles = b"".join(bytes(t.cpu().numpy().tobytes()) for t in alls)
-        i64 = lambda a: np.ascontiguousarray(a, np.int64)
-        args = [i64(caps[:, 0]), i64(caps[:, 1]), i64(lay["val_bounds"]), i64(val_dst), i64(lay["f_bounds"]), i64(f_dst)]
+        args = [_i64(caps[:, 0]), _i64(caps[:, 1]), _i64(lay["val_bounds"]), _i64(val_dst), _i64(lay["f_bounds"]), _i64(f_dst), _i64(lay["recv_from"])]
         fx._ck(fx.L.femx_peer_connect(fx.h, P, ep.rank, handles, *[a.ctypes.data for a in args]))
-        self._peer_keep = args
+        _set_merge(fx, ep)
         self.n_recv_f = int(caps[ep.rank, 1])
 
     def peer_received(self):
@@ -229,18 +295,14 @@ class DistributedAssembly:
                              else self.torch.empty(0, dtype=self.torch.float64, device=self.device))
         return as_t(pv, n), as_t(pf, self.n_recv_f)
 
-    def owned_fint(self, d_f):
-        """Internal force of the owned rows after a peer-mode assembly: this rank's partial plus the entries
-        each source rank stored into the arena, added in source-rank order (deterministic)."""
-        torch, ep = self.torch, self.ep
-        out = d_f[ep.row_start:ep.row_end].clone()
-        fr = self.peer_received()[1]
-        for s, rows in enumerate(self.lay["f_rows"]):
-            if len(rows):
-                o = int(self.lay["recv_foff"][s])
-                idx = torch.from_numpy(rows - ep.row_start).to(self.device)
-                out.index_add_(0, idx, fr[o:o + len(rows)])
-        return out
+    def merged(self):
+        """Merged interface-row values of the last peer-mode assembly (device tensor view, union pattern ep.if_*)."""
+        import ctypes as C
+        p, n = C.c_void_p(), C.c_int64()
+        self.fx._ck(self.fx.L.femx_peer_merged(self.fx.h, C.byref(p), C.byref(n)))
+        if n.value == 0:
+            return self.torch.empty(0, dtype=self.torch.float64, device=self.device)
+        return self.torch.as_tensor(_DevArray(p.value, n.value), device=self.device)
 
     def close(self):
         if self.peer:
@@ -249,33 +311,95 @@ class DistributedAssembly:
             self.peer = False
 
     def exchange(self):
-        """Ship the interface-row values (contiguous slices of vals_local, no pack kernel);
-        returns (own slice view, received values ordered by source rank)."""
+        """NCCL / gloo path: ship the interface-row values (contiguous slices of vals_local, no pack kernel); returns the
+        received values ordered by source rank.  In peer mode the kernel has already delivered and merged them."""
         ep = self.ep
-        if self.peer:            # the kernel already delivered the slices; the step barrier ran inside the assemble call
+        if self.peer:
             self.recv = self.peer_received()[0]
-            return self.vals_local[ep.own_lo:ep.own_hi], self.recv
+            return self.recv
         ins = [self.vals_local[int(ep.send_lo[q]):int(ep.send_hi[q])] if q != ep.rank else self.vals_local[:0]
                for q in range(ep.nranks)]
         offs = np.concatenate([[0], np.cumsum(self.recv_splits)])
         outs = [self.recv[int(offs[q]):int(offs[q + 1])] for q in range(ep.nranks)]
         self.dist.all_to_all(outs, ins)
-        return self.vals_local[ep.own_lo:ep.own_hi], self.recv
+        return self.recv
 
-    def merged(self):
-        """Owned rows as CSR values (union pattern), summed in (own, source rank) order on the device."""
-        import ctypes as C
-        torch, ep, fx = self.torch, self.ep, self.fx
-        if self._merge_dev is None:
-            self._merge_dev = (torch.from_numpy(ep.merge_ptr).to(self.device), torch.from_numpy(ep.merge_idx).to(self.device),
-                               torch.empty(len(ep.colidx), dtype=torch.float64, device=self.device))
-        ptr, idx, out = self._merge_dev
-        own = self.vals_local[ep.own_lo:ep.own_hi]
-        torch.cuda.synchronize()
-        fx._ck(fx.L.femx_gather_sum(fx.h, C.c_void_p(own.data_ptr()), self.n_own, C.c_void_p(self.recv.data_ptr()),
-                                    C.c_void_p(ptr.data_ptr()), C.c_void_p(idx.data_ptr()), len(ep.colidx),
-                                    C.c_void_p(out.data_ptr())))
+    def merged_host(self, vals_local: np.ndarray, recv: np.ndarray) -> np.ndarray:
+        """The receiver add on the host, same lists and order as peer_merge_kernel (NCCL / gloo path, CPU tests)."""
+        ep = self.ep
+        out = np.where(ep.m_own >= 0, vals_local[np.maximum(ep.m_own, 0)], 0.0)
+        cnt = np.diff(ep.m_ptr)
+        for k in range(int(cnt.max()) if len(cnt) else 0):          # k-th received contribution of every entry, in list order
+            sel = np.nonzero(cnt > k)[0]
+            out[sel] = out[sel] + recv[ep.m_idx[ep.m_ptr[sel] + k]]
         return out
+
+    def owned_csr(self, vals_local: np.ndarray, merged: np.ndarray):
+        return owned_csr(self.ep, self.rowptr, self.colidx, vals_local, merged)
+
+
+class LocalRanks:
+    """N ranks as N femx contexts of THIS process on ONE device (femx_peer_connect_local): the whole multi-rank data
+    path -- per-owner value ranges, arena layout, remote stores, step flags, receiver add -- on a single GPU.  The ranks'
+    kernels run one after another, so assemblies push and signal only and femx_peer_complete finishes every rank once all
+    have assembled (a kernel that waited for a peer not yet launched would never finish)."""
+
+    def __init__(self, fxs: list):
+        import ctypes as C
+        self.fxs, P = fxs, len(fxs)
+        self.P = P
+        pats = [fx.pattern() for fx in fxs]
+        eps = [plan_sends(pats[r][0], pats[r][1], fxs[r].nrows, P, r, fxs[r].mesh.nl2g, fxs[r].mesh.pdim) for r in range(P)]
+        self.eps = [finish_plan(eps[r], pats[r][0], pats[r][1], [eps[s].send_rows[r] for s in range(P)], [eps[s].send_cols[r] for s in range(P)],
+                                [eps[s].send_frows[r] for s in range(P)]) for r in range(P)]
+        self.pats = pats
+        lays = [peer_layout(self.eps[r], fxs[r].nnz) for r in range(P)]
+        caps = np.array([[int(l["recv_voff"][-1]), int(l["recv_foff"][-1])] for l in lays], np.int64)
+        for r, fx in enumerate(fxs):
+            handle = (C.c_char * 64)()
+            fx._ck(fx.L.femx_peer_arena_create(fx.h, int(caps[r, 0]), int(caps[r, 1]), C.addressof(handle)))
+        ptrs = (C.c_void_p * P)(*[fx.h for fx in fxs])
+        for r, fx in enumerate(fxs):
+            val_dst = _i64([lays[q]["recv_voff"][r] for q in range(P)])      # where my slice starts in rank q's arena
+            f_dst = _i64([lays[q]["recv_foff"][r] for q in range(P)])
+            args = [_i64(caps[:, 0]), _i64(caps[:, 1]), _i64(lays[r]["val_bounds"]), val_dst, _i64(lays[r]["f_bounds"]), f_dst, _i64(lays[r]["recv_from"])]
+            fx._ck(fx.L.femx_peer_connect_local(fx.h, P, r, C.addressof(ptrs), *[a.ctypes.data for a in args]))
+            _set_merge(fx, self.eps[r])
+
+    def assemble_K_fint(self, us: list):
+        """One collective assembly.  Returns per rank (rowptr, colidx, vals) of the owned rows (host) and the global internal
+        force vector summed over the ranks' owned entries."""
+        import ctypes as C
+        from . import api
+        P = self.P
+        bufs = []
+        for r, fx in enumerate(self.fxs):
+            d_u = api.DeviceBuffer(fx, us[r].nbytes).upload(np.ascontiguousarray(us[r]))
+            d_v = api.DeviceBuffer(fx, 8 * fx.nnz)
+            d_f = api.DeviceBuffer(fx, 8 * fx.nrows)
+            fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_v.ptr, d_f.ptr, api.DEVICE))      # kernel + push + signal
+            bufs.append((d_u, d_v, d_f))
+        out, f_tot = [], np.zeros(self.fxs[0].nrows)
+        for r, fx in enumerate(self.fxs):
+            fx._ck(fx.L.femx_peer_complete(fx.h))                                              # flags + receiver add
+        for r, fx in enumerate(self.fxs):
+            ep = self.eps[r]
+            d_u, d_v, d_f = bufs[r]
+            p, n = C.c_void_p(), C.c_int64()
+            fx._ck(fx.L.femx_peer_merged(fx.h, C.byref(p), C.byref(n)))
+            merged = np.empty(n.value)
+            if n.value:
+                fx._ck(fx.L.femx_memcpy(fx.h, C.c_void_p(merged.ctypes.data), p, merged.nbytes, api.HOST, api.DEVICE))
+            out.append(owned_csr(ep, self.pats[r][0], self.pats[r][1], d_v.download(), merged))
+            f = d_f.download()
+            f_tot[ep.row_start:ep.row_end] = f[ep.row_start:ep.row_end]
+            for b in bufs[r]:
+                b.free()
+        return out, f_tot
+
+    def close(self):
+        for fx in self.fxs:
+            fx._ck(fx.L.femx_peer_disconnect(fx.h))
 
 
 # --------------------------------------------------------------------------- nodal stress across ranks

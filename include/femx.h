@@ -186,28 +186,42 @@ int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b,
  * are the contiguous local value range [val_bounds[q], val_bounds[q+1]) and the internal-force entries (numbered
  * pdim*local_node + i) the range [f_bounds[q], f_bounds[q+1]).  After femx_peer_connect, femx_assemble_K /
  * femx_assemble_K_fint push those ranges into rank q's receive arena over NVLink (remote stores of a kernel behind
- * the assembly kernel; with opts.reserved[3] = 1 and variants 0, 5, 12, 9 the assembly kernel stores them there itself
+ * the assembly kernel; with opts.reserved[3] = 1 and variants 0, 12, 9, 11 the assembly kernel stores them there itself
  * and the non-owned ranges of the local arrays are not written), at val_dst[q] / f_dst[q] doubles from the start of
- * q's value / force receive area, and the call ends with a device-side step barrier among the ranks: at return the
- * rank's own slice of `vals` (and the owned rows of `fint`) plus everything its peers sent are complete.
- * Assemblies are collective: every rank calls them the same number of times.  The arena is double-buffered on the
- * call parity.
+ * q's value / force receive area.  The call then runs a device-side step barrier among NEIGHBOURS (ranks that exchange
+ * a non-empty slice in either direction; recv_from[q] = doubles this rank receives from q) and the receiver add
+ * (femx_peer_set_merge): at return the rank's own slice of `vals`, everything its peers sent, the merged interface
+ * rows and the owned rows of `fint` are complete.  Assemblies are collective: every rank calls them the same number of
+ * times.  The arena is double-buffered on the call parity.
  *   femx_peer_arena_create  allocates the arena for n_recv_vals + n_recv_f doubles (per buffer) and returns its
  *                           cudaIpcMemHandle (64 bytes) for the caller to all-gather among the ranks;
  *   femx_peer_connect       handles = nranks x 64 bytes, recv_vals / recv_f = every rank's arena capacities;
+ *   femx_peer_connect_local the same for ranks that are ctxs of ONE process on ONE device (peers[q] instead of
+ *                           handles).  Kernels of such ranks run one after another, so none may wait for a peer:
+ *                           assemblies push and signal only, and femx_peer_complete -- called on every rank once all
+ *                           have assembled -- checks the flags (they are set by then) and runs the receiver add;
+ *   femx_peer_set_merge     the receiver add, interface rows only: merged[s] = vals[own_slot[s]] (own_slot -1: none)
+ *                           + sum of the received values idx[ptr[s] .. ptr[s+1]) in list order = (source rank, sender
+ *                           position); fint[f_row[s]] += received force entries f_idx[f_ptr[s] .. f_ptr[s+1]).
+ *                           O(interface) work per assembly; replaces the add inside MatAssemblyEnd;
+ *   femx_peer_merged        device pointer / length of the merged interface-row values of the last assembly;
  *   femx_peer_recv          device pointers to what the LAST assembly received (source-rank order, as laid out by
  *                           the caller's val_dst / f_dst);
  *   femx_peer_disconnect    unmaps the peers' arenas (call on every rank before any rank destroys its ctx). */
 int femx_peer_arena_create(femx_ctx *ctx, int64_t n_recv_vals, int64_t n_recv_f, char handle[64]);
 int femx_peer_connect(femx_ctx *ctx, int nranks, int rank, const char *handles, const int64_t *recv_vals,
                       const int64_t *recv_f, const int64_t *val_bounds, const int64_t *val_dst,
-                      const int64_t *f_bounds, const int64_t *f_dst);
+                      const int64_t *f_bounds, const int64_t *f_dst, const int64_t *recv_from);
+int femx_peer_connect_local(femx_ctx *ctx, int nranks, int rank, femx_ctx *const *peers, const int64_t *recv_vals,
+                            const int64_t *recv_f, const int64_t *val_bounds, const int64_t *val_dst,
+                            const int64_t *f_bounds, const int64_t *f_dst, const int64_t *recv_from);
+int femx_peer_set_merge(femx_ctx *ctx, int64_t n, const int64_t *own_slot, const int64_t *ptr, const int64_t *idx,
+                        int64_t nf, const int64_t *f_row, const int64_t *f_ptr, const int64_t *f_idx);
+int femx_peer_merged(femx_ctx *ctx, const double **merged, int64_t *n);
+int femx_peer_complete(femx_ctx *ctx);
+int femx_peer_last_error(femx_ctx *ctx);   /* reports (and clears) a step-barrier timeout */
 int femx_peer_recv(femx_ctx *ctx, const double **vals_recv, const double **f_recv);
 int femx_peer_disconnect(femx_ctx *ctx);
-/* Reserved: the library creates no NCCL communicator of its own (both return FEMX_ERR_UNSUPPORTED); the exchange is
- * femx_peer_* above or the host's MPI / NCCL on the contiguous value slices. */
-int femx_nccl_unique_id(char id[128]);
-int femx_comm_init(femx_ctx *ctx, const char id[128]);
 
 /* ---- instrumentation -------------------------------------------------------------- */
 /* kernels launched by this ctx since creation (bench.py "gpu_launches") */

@@ -32,9 +32,9 @@ def _worker(rank, world, port, kind, out):
         loc = fm.localize(g, epart, rank)
         om = orc.Mesh(loc)
         rowptr, colidx, vals = orc.assemble_K(om).export(om.ndof)
-        ep = par.plan_sends(rowptr, colidx, om.ndof, world, rank)
-        rr, rc = par.exchange_lists(ep, dist)
-        ep = par.finish_plan(ep, rowptr, colidx, rr, rc)
+        ep = par.plan_sends(rowptr, colidx, om.ndof, world, rank, loc.nl2g, loc.pdim)
+        rr, rc, rf = par.exchange_lists(ep, dist)
+        ep = par.finish_plan(ep, rowptr, colidx, rr, rc, rf)
         # value exchange: contiguous slices of the local value array
         v = torch.from_numpy(vals)
         ins = [v[int(ep.send_lo[q]):int(ep.send_hi[q])] if q != rank else v[:0] for q in range(world)]
@@ -48,22 +48,26 @@ def _worker(rank, world, port, kind, out):
             reqs.append(dist.irecv(outs[q], q))
         for r in reqs:
             r.wait()
-        src = np.concatenate([vals[ep.own_lo:ep.own_hi]] + [o.numpy() for o in outs])
-        merged = np.array([src[ep.merge_idx[a:b]].sum() for a, b in zip(ep.merge_ptr[:-1], ep.merge_ptr[1:])])
+        recv = np.concatenate([o.numpy() for o in outs])
+        # the receiver add over the interface rows, list order = (own, source rank, sender position) -- what peer_merge_kernel does
+        merged = np.array([(vals[ep.m_own[s]] if ep.m_own[s] >= 0 else 0.0) + recv[ep.m_idx[a:b]].sum()
+                           for s, (a, b) in enumerate(zip(ep.m_ptr[:-1], ep.m_ptr[1:]))])
+        assert len(ep.if_rows) < (ep.row_end - ep.row_start), "the receiver add touches interface rows only"
+        rp_o, ci_o, va_o = par.owned_csr(ep, rowptr, colidx, vals, merged)
         # oracle: 1-rank global assembly restricted to the owned rows
         og = orc.Mesh(g)
         rp_g, ci_g, va_g = orc.assemble_K(og).export(og.ndof)
         r0, r1 = ep.row_start, ep.row_end
         assert (r0, r1) == fm.petsc_ownership(og.ndof, world, rank)
-        assert np.array_equal(ep.rowptr, rp_g[r0:r1 + 1] - rp_g[r0]), "owned-row pattern (rowptr)"
-        assert np.array_equal(ep.colidx, ci_g[rp_g[r0]:rp_g[r1]]), "owned-row pattern (colidx)"
+        assert np.array_equal(rp_o, rp_g[r0:r1 + 1] - rp_g[r0]), "owned-row pattern (rowptr)"
+        assert np.array_equal(ci_o, ci_g[rp_g[r0]:rp_g[r1]]), "owned-row pattern (colidx)"
         ref = va_g[rp_g[r0]:rp_g[r1]]
-        assert np.all(np.abs(merged - ref) <= 1e-12 * np.maximum(np.abs(ref), np.abs(va_g).max()))
-        # COO form: every (i, j) owned, duplicates only on interface rows
-        assert len(ep.coo_i) == (ep.own_hi - ep.own_lo) + int(ep.recv_counts.sum())
+        assert np.all(np.abs(va_o - ref) <= 1e-12 * np.maximum(np.abs(ref), np.abs(va_g).max()))
+        # COO form of the received part: every (i, j) owned
+        assert len(ep.coo_i) == int(ep.recv_counts.sum())
         # peer-memory layout (csrc/peer.cu): every sender's slice must land where the receiver's source-rank-ordered
         # lists expect it, for the matrix values and for the internal force (wire format: local dof order)
-        lay = par.peer_layout(ep, rr, loc.nl2g, loc.pdim, om.ndof, len(vals))
+        lay = par.peer_layout(ep, len(vals))
         val_dst, f_dst, caps = par.exchange_offsets(lay, dist, world)
         assert caps[rank, 0] == ep.recv_counts.sum() and np.array_equal(np.diff(lay["recv_voff"]), ep.recv_counts)
         u = mg.displacement_field(loc)
@@ -92,11 +96,11 @@ def _worker(rank, world, port, kind, out):
             arena_f[fo:fo + fn] = b[4 + vn:4 + vn + fn]
         for r in reqs:
             r.wait()
-        assert np.array_equal(arena_v, np.concatenate([o.numpy() for o in outs])), "arena = source-rank-ordered receive list"
-        f_own = f_loc[r0:r1].copy()
-        for s_, rows in enumerate(lay["f_rows"]):
-            o = int(lay["recv_foff"][s_])
-            np.add.at(f_own, rows - r0, arena_f[o:o + len(rows)])
+        assert np.array_equal(arena_v, recv), "arena = source-rank-ordered receive list"
+        f_own = f_loc.copy()
+        for s_, (a, b) in enumerate(zip(ep.f_ptr[:-1], ep.f_ptr[1:])):     # peer_merge_f_kernel
+            f_own[ep.f_row[s_]] += arena_f[ep.f_idx[a:b]].sum()
+        f_own = f_own[r0:r1]
         ug = mg.displacement_field(g)
         f_ref = orc.fint(og, ug.reshape(-1))[r0:r1]
         assert np.all(np.abs(f_own - f_ref) <= 1e-12 * max(np.abs(f_ref).max(), 1e-300)), "owned internal force"

@@ -43,19 +43,23 @@ def main():
         torch.cuda.synchronize()
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, C.c_void_p(d_u.data_ptr()), C.c_void_p(da.vals_local.data_ptr()),
                                          C.c_void_p(d_f.data_ptr()), api.DEVICE))
-        da.exchange()
-        merged = da.merged().cpu().numpy()
-        if peer:                                   # owned rows: own partial + what the peers stored into the arena
-            own = da.owned_fint(d_f)
-            d_f.zero_()
-            d_f[da.ep.row_start:da.ep.row_end] = own
-        dist.all_reduce(d_f)                       # residual: plain sum of the ranks' partial vectors
+        recv = da.exchange()
+        vl = da.vals_local.cpu().numpy()
+        if peer:                                   # the receiver add ran inside the assemble call (interface rows only)
+            merged = da.merged().cpu().numpy()
+            d_f2 = torch.zeros_like(d_f)
+            d_f2[da.ep.row_start:da.ep.row_end] = d_f[da.ep.row_start:da.ep.row_end]     # owned rows: own partial + received, added by femx
+            d_f = d_f2
+        else:
+            merged = da.merged_host(vl, recv.cpu().numpy())
+        rp_o, ci_o, va_o = da.owned_csr(vl, merged)
+        dist.all_reduce(d_f)                       # residual: the ranks' owned entries (peer) / partial vectors (NCCL) sum to the global vector
         og = orc.Mesh(g)
         rp, ci, va = orc.assemble_K(og).export(og.ndof)
         r0, r1 = da.ep.row_start, da.ep.row_end
         ref = va[rp[r0]:rp[r1]]
-        good = (np.array_equal(da.ep.rowptr, rp[r0:r1 + 1] - rp[r0]) and np.array_equal(da.ep.colidx, ci[rp[r0]:rp[r1]])
-                and np.all(np.abs(merged - ref) <= 1e-12 * np.maximum(np.abs(ref), np.abs(va).max())))
+        good = (np.array_equal(rp_o, rp[r0:r1 + 1] - rp[r0]) and np.array_equal(ci_o, ci[rp[r0]:rp[r1]])
+                and np.all(np.abs(va_o - ref) <= 1e-12 * np.maximum(np.abs(ref), np.abs(va).max())))
         ug = np.zeros((g.nnds, g.pdim)); ug[loc.nl2g - 1] = u
         f_ref = orc.fint(og, mg.displacement_field(g).reshape(-1))
         f = d_f.cpu().numpy()
@@ -69,7 +73,7 @@ def main():
             sgood = np.all(np.abs(s_loc - want) <= 1e-10 * np.maximum(np.abs(want), np.abs(s_ref).max())) and np.array_equal(s_loc, s_loc2)
             print(f"[rank {rank}] {name} nodal stress over {world} ranks {'OK' if sgood else 'MISMATCH'}", flush=True)
             good = good and bool(sgood)
-        print(f"[rank {rank}] {name} {('nccl', 'peer-push', 'peer-fused')[peer]} #{rep}: owned rows [{r0},{r1}) nnz {len(merged)} recv {int(da.ep.recv_counts.sum())} "
+        print(f"[rank {rank}] {name} {('nccl', 'peer-push', 'peer-fused')[peer]} #{rep}: owned rows [{r0},{r1}) nnz {len(va_o)} interface nnz {len(merged)} recv {int(da.ep.recv_counts.sum())} "
               f"{'OK' if good else 'MISMATCH'}", flush=True)
         ok = ok and bool(good)
     da.close(); fx.close()
