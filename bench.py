@@ -9,6 +9,10 @@ elements are not congruent.  A step = one femx_assemble_K_fint call: every CSR v
 the internal force f = sum_e Ke u_e are (re)computed from coordinates and u.  `value` is
 device-timed with inputs resident in HBM; `e2e` goes through the same C-ABI call with pinned
 HOST buffers (u H2D, K values + f D2H inside the timed region).
+N > 1 (weak scaling): the (Px n) x (Py n) x (Pz n) cube in Px x Py x Pz blocks of n^3 elements, one per GPU -- 2x1x1,
+2x2x1, 2x2x2; N = 8 is BASELINE configs[4] (200^3, three interface faces per rank) -- node numbering contiguous per
+block, rows owned by the PETSC_DECIDE split.  The step then includes femx's interface exchange: remote stores into the
+owners' arenas over NVLink, the step barrier among neighbours and the receiver add over the interface rows.
 """
 import argparse
 import json
@@ -24,8 +28,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BYTES_PER_EL = {"hex8": 2074.0}
-KERNEL_NAME = {0: "hex_sym6_kernel", 1: "elem_rows_kernel + gather_rows_kernel", 2: "hex_fused_kernel", 3: "hex_ws_kernel",
-               4: "hex_sym5_kernel", 5: "hex_sym2_kernel", 6: "hex_sym3_kernel", 7: "hex_sym4_kernel", 8: "hex_sym5_kernel", 12: "hex_sym6_kernel", 13: "hex_sym7_kernel"}   # conn 32 + mat 4 + coords 24.73 + u 24.73 + K 1963.5 + R 24.73
+KERNEL_NAME = {0: "hex_sym6_kernel", 1: "elem_rows_kernel + gather_rows_kernel", 9: "fused_rows_kernel", 12: "hex_sym6_kernel", 20: "hex_mma_kernel"}
+# conn 32 + mat 4 + coords 24.73 + u 24.73 + K 1963.5 + R 24.73
 
 
 def algorithmic_bytes(m, nnz):
@@ -63,14 +67,95 @@ class ClockSampler(threading.Thread):
 
 
 def build_workload(n, nranks, rank):
-    from fem_b200 import mesh as fm, meshgen as mg
+    from fem_b200 import meshgen as mg
     if nranks == 1:
         m = mg.jitter(mg.hex_cube(n, clamp=False))
     else:
-        # weak scaling: a column of nranks cubes, one n^3 block per rank (z-slabs); each rank
-        # assembles the rows of its own elements (SURVEY.md 8e partitioning by element)
-        m = mg.hex_block(n, n, n, z0=rank * n, nz_total=n * nranks)
+        # weak scaling: one n^3 block of the (Px n) x (Py n) x (Pz n) cube per rank; each rank assembles the rows of its own
+        # elements (partition by element, rows by the PETSC_DECIDE split)
+        m = mg.hex_block_rank(n, mg.block_grid(nranks), rank)
     return m, mg.displacement_field(m)
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this rank's host threads (and therefore its pinned buffers' first touch) to the CPUs NVML names as local to the
+    GPU: eight ranks copying 2 GB each through one socket is what made the round-1 e2e collapse at N = 8."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        if cpus & allowed:
+            os.sched_setaffinity(0, cpus & allowed)
+            return len(cpus & allowed)
+    except Exception:
+        pass
+    return 0
+
+
+def other_configs(args, api, mg):
+    """N = 1 only: the BASELINE configurations that are not the headline, each with device ms (median of 5), elements/s,
+    algorithmic GB/s and its fraction of the measured HBM rate (SURVEY.md 8(d) bytes per element)."""
+    out = []
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0))
+    except Exception:
+        peak = 6650.0
+
+    def timed(fx, call, reps=5):
+        ms = []
+        for _ in range(reps + 1):
+            call()
+            ms.append(fx.last_kernel_ms)
+        return float(np.median(ms[1:]))
+
+    def add(name, nels, ms, bpe, **kw):
+        gbs = nels * bpe / (ms * 1e-3) / 1e9
+        out.append(dict(config=name, ms=ms, elements_per_s=nels / (ms * 1e-3), algorithmic_bytes_per_element=bpe, algorithmic_GBps=gbs,
+                        frac=gbs / peak, **kw))
+
+    # hex8 100^3 through the other kernels: the DMMA tile kernel and the general fused rows kernel (what an off-grid hex8 mesh gets)
+    m = mg.jitter(mg.hex_cube(args.n, clamp=False))
+    u = mg.displacement_field(m)
+    for var, nm in ((20, "hex_mma_kernel (variant 20)"), (9, "fused_rows_kernel (variant 9: any hex8 mesh)")):
+        with api.Femx(assembly_variant=var) as fx:
+            fx.set_mesh(m).build_plan()
+            d_u = fx.device_buffer(u.nbytes).upload(u); d_v = fx.device_buffer(8 * fx.nnz); d_f = fx.device_buffer(8 * fx.nrows)
+            ms = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_v.ptr, d_f.ptr, api.DEVICE)))
+            add(f"C2 hex8 {args.n}^3 K + f_int, {nm}", m.nels, ms, 2074.0)
+            if var == 9:
+                d_s = fx.device_buffer(8 * 6 * m.nlnds)
+                ms = timed(fx, lambda: fx._ck(fx.L.femx_stress(fx.h, d_u.ptr, d_s.ptr, api.ROW_MAJOR, api.DEVICE)))
+                add(f"C2 hex8 {args.n}^3 nodal-averaged stress", m.nels, ms, 32 + 4 + 2 * 24.73 + 48 * m.nlnds / m.nels)
+    m = mg.tet_cube(94)
+    u = mg.displacement_field(m)
+    with api.Femx() as fx:
+        fx.set_mesh(m).build_plan()
+        d_u = fx.device_buffer(u.nbytes).upload(u); d_v = fx.device_buffer(8 * fx.nnz); d_f = fx.device_buffer(8 * fx.nrows)
+        d_s = fx.device_buffer(8 * 6 * m.nlnds)
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_v.ptr, d_f.ptr, api.DEVICE)))
+        add("C3 tet4 94^3x6 K + f_int (rows_simplex_kernel)", m.nels, ms, 215.0)
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_stress(fx.h, d_u.ptr, d_s.ptr, api.ROW_MAJOR, api.DEVICE)))
+        add("C3 tet4 94^3x6 nodal-averaged stress", m.nels, ms, 36.5)
+    m = mg.cohesive_strip(1000, 1000)
+    nn = m.nlnds
+    u = np.zeros((nn, 2)); u[nn // 2:, 1] = 1e-3
+    with api.Femx(quirks=api.Q_UEL) as fx:
+        fx.set_mesh(m).build_plan()
+        d_u = fx.device_buffer(u.nbytes).upload(u); d_k = fx.device_buffer(8 * fx.nnz); d_j = fx.device_buffer(8 * fx.nnz)
+        d_f = fx.device_buffer(8 * fx.nrows); d_r = fx.device_buffer(8 * fx.nrows)
+        d_du = fx.device_buffer(8 * fx.nrows).upload(np.zeros(fx.nrows)); d_fe = fx.device_buffer(8 * fx.nrows).upload(np.zeros(fx.nrows))
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, d_k.ptr, d_f.ptr, api.DEVICE)))
+        add("C4 quad4 2x1000^2 + 1000 coh K + f_int (fused_rows_kernel)", m.nels, ms, 356.0)
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_jacobian(fx.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE)))
+        add("C4 femx_jacobian (copy K, cohesive overlay, BC diagonal)", m.nels, ms, 16.0 * fx.nnz / m.nels)
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_jacobian_update(fx.h, d_k.ptr, d_u.ptr, float(m.dt), d_j.ptr, api.DEVICE)))
+        add("C4 femx_jacobian_update (cohesive blocks + BC diagonal only)", m.nels, ms, 0.0)
+        ms = timed(fx, lambda: fx._ck(fx.L.femx_residual(fx.h, d_j.ptr, d_u.ptr, d_du.ptr, d_fe.ptr, float(m.dt), float(m.t), d_r.ptr, api.DEVICE)))
+        add("C4 femx_residual (cohesive forces, BC rows, J du - f)", m.nels, ms, (12.0 * fx.nnz + 24.0 * fx.nrows) / m.nels)
+    return out
 
 
 def cpu_sample(n_cpu, threads):
@@ -130,30 +215,30 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=56, help="edge of the bounded CPU sample cube")
     ap.add_argument("--impl", default="femx")
     ap.add_argument("--variant", type=int, default=0)
-    ap.add_argument("--tile", type=int, default=0)
     ap.add_argument("--lz", type=int, default=0)
-    ap.add_argument("--dbg", type=int, default=0, help="diagnostic: skip parts of the fused kernel (results invalid)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-other", action="store_true", help="skip the other_configs array (C3 / C4 / other hex8 kernels; N = 1 only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
-    import torch
-    import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    numa_cpus = bind_to_gpu_numa_node(local_rank) if world > 1 else 0
+    import torch
+    import torch.distributed as dist
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (femx has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    from fem_b200 import api
+    import ctypes as C
+    from fem_b200 import api, meshgen as mg
     m, u = build_workload(args.n, world, rank)
-    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, tile=args.tile, lz=args.lz, dbg=args.dbg,
-                  peer_in_kernel=args.exchange == "peer-fused")
+    fx = api.Femx(device=local_rank, quirks=api.Q_REFERENCE, assembly_variant=args.variant, lz=args.lz, peer_in_kernel=args.exchange == "peer-fused")
     t0 = time.time()
     fx.set_mesh(m).build_plan()
     plan_s = time.time() - t0
@@ -163,10 +248,8 @@ def main():
     d_f = fx.device_buffer(8 * nrows)
     da = None
     if world > 1:
-        # interface rows go to their PETSc owners over NCCL every step (fem_b200/parallel.py)
-        import ctypes as C
         from fem_b200 import parallel as par
-        da = par.DistributedAssembly(fx, dist, torch.device("cuda", local_rank), with_merge=False, peer=args.exchange != "nccl")
+        da = par.DistributedAssembly(fx, dist, torch.device("cuda", local_rank), peer=args.exchange != "nccl")
         vals_ptr = C.c_void_p(da.vals_local.data_ptr())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     else:
@@ -174,9 +257,10 @@ def main():
         vals_ptr = d_vals.ptr
 
     def step_device():
+        # peer mode: kernel + remote stores + neighbour barrier + receiver add (interface rows) are all inside this call
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, vals_ptr, d_f.ptr, api.DEVICE))
         ms = fx.last_kernel_ms
-        if da is not None and not da.peer:   # peer mode: the kernel stored the interface rows into the owners' arenas
+        if da is not None and not da.peer:
             ev0.record()
             da.exchange()
             ev1.record()
@@ -203,15 +287,37 @@ def main():
     wall_ms = 1e3 * (time.perf_counter() - w0)
     launches = fx.launches - l0
 
-    # e2e: pinned host buffers through the same C-ABI call
+    # e2e: pinned host buffers through the C ABI.  N = 1: one femx_assemble_K_fint(FEMX_HOST) call per step.  N > 1: the rank's
+    # OWNED part travels -- u in, then the owned value slice, the merged interface rows and the owned internal force out.
     e2e = None
     if not args.no_e2e:
         hu = fx.pinned(u.size); hu.array[:] = u.reshape(-1)
-        hv = fx.pinned(nnz); hf = fx.pinned(nrows)
+        if da is None:
+            hv = fx.pinned(nnz); hf = fx.pinned(nrows)
 
-        def step_host():
-            fx._ck(fx.L.femx_assemble_K_fint(fx.h, hu.ptr, hv.ptr, hf.ptr, api.HOST))
+            def step_host():
+                fx._ck(fx.L.femx_assemble_K_fint(fx.h, hu.ptr, hv.ptr, hf.ptr, api.HOST))
+            d2h = 8 * nnz + 8 * nrows
+        else:
+            ep = da.ep
+            n_own, n_mer, n_f = ep.own_hi - ep.own_lo, len(ep.m_own), ep.row_end - ep.row_start
+            hv = fx.pinned(n_own + n_mer); hf = fx.pinned(n_f)
+            own_src = C.c_void_p(da.vals_local.data_ptr() + 8 * ep.own_lo)
+            f_src = C.c_void_p(d_f.ptr.value + 8 * ep.row_start)
+            hv_mer = C.c_void_p(hv.ptr.value + 8 * n_own)
 
+            def step_host():
+                fx._ck(fx.L.femx_memcpy(fx.h, d_u.ptr, hu.ptr, u.nbytes, api.DEVICE, api.HOST))
+                fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, vals_ptr, d_f.ptr, api.DEVICE))
+                if not da.peer:
+                    da.exchange()
+                fx._ck(fx.L.femx_memcpy(fx.h, hv.ptr, own_src, 8 * n_own, api.HOST, api.DEVICE))
+                if da.peer and n_mer:
+                    p, nn_ = C.c_void_p(), C.c_int64()
+                    fx._ck(fx.L.femx_peer_merged(fx.h, C.byref(p), C.byref(nn_)))
+                    fx._ck(fx.L.femx_memcpy(fx.h, hv_mer, p, 8 * n_mer, api.HOST, api.DEVICE))
+                fx._ck(fx.L.femx_memcpy(fx.h, hf.ptr, f_src, 8 * n_f, api.HOST, api.DEVICE))
+            d2h = 8 * (n_own + n_mer + n_f)
         step_host()
         barrier()
         e0 = time.perf_counter()
@@ -220,17 +326,37 @@ def main():
             step_host()
         barrier()
         e2e_ms = 1e3 * (time.perf_counter() - e0) / ke
-        # parity spot check of what came back (size-independent properties; tests/ hold the oracle parity)
+        # spot check of what came back (size-independent; tests/ hold the oracle parity)
         assert np.isfinite(hv.array[:1000]).all() and np.isfinite(hf.array).all()
-        e2e = {"ms": e2e_ms, "h2d": int(u.nbytes), "d2h": int(8 * nnz + 8 * nrows)}
+        e2e = {"ms": e2e_ms, "h2d": int(u.nbytes), "d2h": int(d2h)}
         hu.free(); hv.free(); hf.free()
     sampler.stop_flag = True
     sampler.join(timeout=2)
+
+    # in-bench correctness check (N = 1): the timed kernel against the general fused rows kernel, an independent algorithm
+    check = None
+    if world == 1 and args.variant != 9:
+        a = torch.as_tensor(par_dev(vals_ptr.value, nnz), device="cuda")
+        fa = torch.as_tensor(par_dev(d_f.ptr.value, nrows), device="cuda")
+        with api.Femx(device=local_rank, assembly_variant=9) as f9:
+            f9.set_mesh(m).build_plan()
+            d_v9 = f9.device_buffer(8 * nnz); d_f9 = f9.device_buffer(8 * nrows); d_u9 = f9.device_buffer(u.nbytes).upload(u)
+            f9._ck(f9.L.femx_assemble_K_fint(f9.h, d_u9.ptr, d_v9.ptr, d_f9.ptr, api.DEVICE))
+            b = torch.as_tensor(par_dev(d_v9.ptr.value, nnz), device="cuda")
+            fb = torch.as_tensor(par_dev(d_f9.ptr.value, nrows), device="cuda")
+            check = {"K_max_diff_vs_general_kernel_rel": float(((a - b).abs().max() / b.abs().max()).item()),
+                     "f_max_diff_vs_general_kernel_rel": float(((fa - fb).abs().max() / fb.abs().max()).item()),
+                     "sum_K": float(a.sum().item()), "sum_f": float(fa.sum().item())}
+            del b, fb
+        del a, fa
 
     t = torch.tensor([dev_ms, wall_ms, e2e["ms"] if e2e else 0.0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, wall_ms, e2e_ms = (float(x) for x in t.tolist())
+    io = torch.tensor([float(e2e["h2d"]) if e2e else 0.0, float(e2e["d2h"]) if e2e else 0.0], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(io)             # bytes of all ranks per step
     nels_total = m.nels * world          # every rank holds an n^3 block
     if rank == 0:
         ms_step = dev_ms / args.steps
@@ -245,26 +371,34 @@ def main():
         achieved = alg / (ms_step * 1e-3) / 1e9
         traffic, pipes = None, None
         try:   # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel from the committed ncu capture
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
             if args.n == 100:
                 ent = tj.get(KERNEL_NAME.get(args.variant, "?"), {})
                 traffic = ent.get("traffic_bytes_per_launch")
                 if "lsu_data_pipe_pct_of_peak" in ent:   # what actually bounds the kernel (committed ncu capture, not measured live)
-                    pipes = {k: ent[k] for k in ("lsu_data_pipe_pct_of_peak", "fp64_pipe_pct_of_peak", "dram_pct_of_peak")}
+                    pipes = {k: ent[k] for k in ("lsu_data_pipe_pct_of_peak", "fp64_pipe_pct_of_peak", "dram_pct_of_peak") if k in ent}
+                    pipes["source"] = ent.get("source", "profiles/")
         except Exception:
             pass
+        if world > 1:
+            grid = mg.block_grid(world)
+            par_txt = (f"{grid[0]}x{grid[1]}x{grid[2]} blocks of {args.n}^3 elements (N = 8: BASELINE configs[4]), node numbering contiguous per block, "
+                       "PETSC_DECIDE row split, interface rows "
+                       + ((("stored by the assembly kernel" if args.exchange == "peer-fused" else "pushed by femx's peer kernel")
+                           + " into the owner's arena over NVLink + device-side step barrier among neighbours + receiver add over the "
+                             "interface rows, all inside the timed step")
+                          if da.peer else "sent with NCCL all_to_all after the kernel (receiver add on the host, not timed)")
+                       + f" ({int(da.ep.recv_counts.sum()) * 8} B received, {len(da.ep.m_own)} merged values on rank 0 per step)")
+        else:
+            par_txt = "1 GPU"
         line = {"metric": "elements/sec (Ke+f_int assembly)", "value": value, "unit": "elements/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"hex8 cube {args.n}^3 per GPU, jittered, K + f_int (BASELINE configs[1])",
                            "elements_per_gpu": m.nels, "dof_per_gpu": int(m.pdim * m.nlnds), "nnz_per_gpu": int(nnz),
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
-                           "parallelism": (f"z-slab element partition x{world}, PETSc row split, interface rows "
-                                           + ((("stored by the assembly kernel" if args.exchange == "peer-fused" else "pushed by femx's peer kernel")
-                                               + " into the owner's arena over NVLink + device-side step barrier")
-                                              if da.peer else "sent with NCCL all_to_all after the kernel")
-                                           + f" ({int(da.ep.recv_counts.sum()) * 8} B received on rank 0 per step)") if world > 1 else "1 GPU",
-                           "variant": args.variant, "tile": args.tile, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
+                           "parallelism": par_txt,
+                           "variant": args.variant, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
                 "gpu_launches": int(launches),
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -272,9 +406,13 @@ def main():
                              "frac_of_8TBs_nominal": achieved / 8000.0, "bytes_per_element": alg / m.nels, "algorithmic_bytes_per_launch": alg,
                              "kernel": KERNEL_NAME.get(args.variant, "?") + " (one launch per step)", "traffic": traffic,
                              "ncu_pipe_utilisation": pipes}}
+        if check:
+            line["check"] = check
         if e2e:
-            line["e2e"] = {"value": nels_total / (e2e_ms * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": e2e["h2d"],
-                           "d2h_bytes_per_step": e2e["d2h"], "ms_per_step": e2e_ms}
+            h2d_all, d2h_all = (float(x) for x in io.tolist())
+            line["e2e"] = {"value": nels_total / (e2e_ms * 1e-3), "unit": "elements/s", "h2d_bytes_per_step": int(h2d_all),
+                           "d2h_bytes_per_step": int(d2h_all), "ms_per_step": e2e_ms,
+                           "d2h_GBps_per_gpu": d2h_all / world / (e2e_ms * 1e-3) / 1e9, "numa_cpus_bound": numa_cpus}
         if world == 1 and not args.no_cpu:
             from oracle import pyoracle as orc
             orc.build()
@@ -282,13 +420,24 @@ def main():
             line["cpu_baseline"] = {"value": ne / sec, "unit": "elements/s", "cores": 1, "kind": "port",
                                     "sample": f"hex8 cube {args.cpu_n}^3 ({ne} elements) in {sec:.2f} s, oracle/ CPU "
                                               "restatement of src/main.F90:157-166; reference (Fortran+PETSc) not buildable here"}
-        print(json.dumps(line))
     if da is not None:
         da.close()
     fx.close()
+    if rank == 0:
+        if world == 1 and not args.no_other:
+            try:
+                line["other_configs"] = other_configs(args, api, mg)
+            except Exception as e:   # noqa: BLE001  -- the headline line must not depend on the side measurements
+                line["other_configs"] = [{"error": repr(e)}]
+        print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def par_dev(ptr, n):
+    from fem_b200.parallel import _DevArray
+    return _DevArray(ptr, n)
 
 
 if __name__ == "__main__":

@@ -214,3 +214,56 @@ def slab_partition(m: Mesh, nparts: int) -> np.ndarray:
     axis for the structured generators).  Stand-in for METIS_PartMeshNodal
     (src/m_io.F90:137): the hot path only consumes `epart`."""
     return (np.arange(m.nels, dtype=np.int64) * nparts // max(m.nels, 1)).astype(np.int32)
+
+
+def block_grid(nranks: int):
+    """(Px, Py, Pz) of the block partition bench.py uses at N ranks: 2x1x1, 2x2x1, 2x2x2 (BASELINE configs[4] is the last)."""
+    return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[nranks]
+
+
+def hex_block_rank(n: int, grid, rank: int, E=3.0e10, nu=0.25, jittered=True) -> Mesh:
+    """Rank-local mesh of block `rank` of a (Px n) x (Py n) x (Pz n) hex8 cube cut into Px x Py x Pz blocks of n^3 elements
+    (BASELINE configs[4] at grid (2, 2, 2), n = 100), built without ever forming the global mesh.  Global node numbering is
+    contiguous per block: a node on a shared face belongs to the lower block, blocks are numbered x-fastest,
+    nodes inside a block lexicographically.  Local ids ascend with the global id (src/main.F90:57-63), elements are in
+    lexicographic order, node order of an element as ShapeFuncdHex (src/m_elems.F90:574-579).  Interior nodes of the WHOLE
+    cube are jittered by a hash of the global id, so the pieces of different ranks agree on shared nodes."""
+    Px, Py, Pz = grid
+    bx, by, bz = rank % Px, (rank // Px) % Py, rank // (Px * Py)
+    n1 = n + 1
+    own_len = lambda b: n1 if b == 0 else n                     # owned node positions of a block along one axis
+    counts = np.array([[[own_len(x) * own_len(y) * own_len(z) for x in range(Px)] for y in range(Py)] for z in range(Pz)], np.int64)
+    offs = np.concatenate([[0], np.cumsum(counts.reshape(-1))])     # block order: x fastest
+    i = np.arange(n1)
+
+    def axis(b):        # owner block coordinate and position inside the owner's owned range, per lattice position
+        ob = np.where((i == 0) & (b > 0), b - 1, b)
+        pos = np.where((i == 0) & (b > 0), n, i)                # position in the owner's lattice
+        pos = np.where(ob == 0, pos, pos - 1)                   # owned range starts at lattice position 1 unless the block is first
+        return ob, pos
+
+    obx, px = axis(bx); oby, py = axis(by); obz, pz = axis(bz)
+    OBX, OBY, OBZ = np.meshgrid(obx, oby, obz, indexing="ij")   # [i, j, k]
+    PX, PY, PZ = np.meshgrid(px, py, pz, indexing="ij")
+    lx = np.where(OBX == 0, n1, n); ly = np.where(OBY == 0, n1, n)
+    gid = offs[(OBZ * Py + OBY) * Px + OBX] + (PZ * ly + PY) * lx + PX + 1      # 1-based global node id, [i, j, k]
+    gflat = gid.transpose(2, 1, 0).reshape(-1)                  # lattice order: i fastest
+    order = np.argsort(gflat, kind="stable")
+    nl2g = gflat[order]
+    local_of = np.empty(len(order), np.int64)
+    local_of[order] = np.arange(1, len(order) + 1)
+    X, Y, Z = np.meshgrid(bx * n + i, by * n + i, bz * n + i, indexing="ij")
+    coords = np.stack([X.transpose(2, 1, 0).reshape(-1), Y.transpose(2, 1, 0).reshape(-1), Z.transpose(2, 1, 0).reshape(-1)], 1).astype(float)
+    lid = lambda a, b, c: local_of[(c * n1 + b) * n1 + a]
+    e = np.arange(n)
+    EI, EJ, EK = np.meshgrid(e, e, e, indexing="ij")
+    EI, EJ, EK = (a.transpose(2, 1, 0).reshape(-1) for a in (EI, EJ, EK))
+    conn = np.stack([lid(EI, EJ, EK), lid(EI + 1, EJ, EK), lid(EI + 1, EJ + 1, EK), lid(EI, EJ + 1, EK),
+                     lid(EI, EJ, EK + 1), lid(EI + 1, EJ, EK + 1), lid(EI + 1, EJ + 1, EK + 1), lid(EI, EJ + 1, EK + 1)], 1)
+    from .mesh import from_uniform
+    m = from_uniform(3, HEX, conn, coords[order], E=E, nu=nu)
+    import dataclasses
+    m = dataclasses.replace(m, nl2g=nl2g.astype(np.int32), nnds=int(offs[-1]), bcnode=np.zeros((0, 4), np.int32), bcval=np.zeros((0, 3))).normalized()
+    if jittered:
+        m = jitter(m, lo=(0, 0, 0), hi=(Px * n, Py * n, Pz * n))
+    return m

@@ -660,7 +660,8 @@ void orc_stress(const orc_mesh *M, const double *uu, int quirks, double *stress_
 
 // CPU baseline: the assembly loop of src/main.F90:157-166 plus f = sum Ke u_e, per thread on
 // a contiguous element range into its own matrix (one "MPI rank" per thread; the interface
-// merge is not timed, which favours the CPU).
+// merge is not timed, which favours the CPU).  Every thread's matrix gets the reference's row
+// preallocation (src/main.F90:153) on the rows its elements touch, set up before the clock starts.
 double orc_time_assembly(const orc_mesh *M, int prealloc, const double *u_local, int nthreads,
                          int64_t *nnz_out) {
   if (nthreads < 1) nthreads = 1;
@@ -668,8 +669,17 @@ double orc_time_assembly(const orc_mesh *M, int prealloc, const double *u_local,
   std::vector<std::vector<double>> fs(nthreads);
   const int64_t n = (int64_t)M->pdim * M->nnds;
   for (int t = 0; t < nthreads; ++t) {
-    mats[t] = orc_csr_create(n, nthreads == 1 ? prealloc : 0);
+    mats[t] = orc_csr_create(n, 0);
     fs[t].assign(n, 0.0);
+    if (prealloc > 0) {
+      const int e0 = (int)((int64_t)M->nels * t / nthreads), e1 = (int)((int64_t)M->nels * (t + 1) / nthreads);
+      for (int e = e0; e < e1; ++e)
+        for (int q = M->eptr[e]; q < M->eptr[e + 1]; ++q) {
+          const int64_t g = (int64_t)M->pdim * (M->nl2g[M->eind[q] - 1] - 1);
+          for (int d = 0; d < M->pdim; ++d)
+            if (mats[t]->cols[g + d].capacity() < (size_t)prealloc) { mats[t]->cols[g + d].reserve(prealloc); mats[t]->vals[g + d].reserve(prealloc); }
+        }
+    }
   }
   auto work = [&](int t) {
     const int e0 = (int)((int64_t)M->nels * t / nthreads), e1 = (int)((int64_t)M->nels * (t + 1) / nthreads);
