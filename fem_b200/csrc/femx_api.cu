@@ -331,25 +331,14 @@ int femx_build_plan(femx_ctx *c) {
     if (c->hex.ok) {
       // the tile kernels scale gradients by rsqrt(detJ): a mirrored grid or an inverted element (which the reference and the
       // general kernels assemble as is, src/m_local.F90:61-65) must not reach them
-      const double g = FEMX_G;
-      for (int e = 0; e < c->nels && c->hex.ok; ++e) {
-        const int *nd = &c->eind[c->eptr[e]];
-        for (int ip = 0; ip < 8 && c->hex.ok; ++ip) {
-          const double xi[3] = {(ip == 1 || ip == 2 || ip == 5 || ip == 6) ? g : -g, ((ip & 3) >= 2) ? g : -g, ip >= 4 ? g : -g};
-          double J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
-          for (int b = 0; b < 8; ++b) {
-            const double sx = (b == 1 || b == 2 || b == 5 || b == 6) ? 1.0 : -1.0, sy = ((b & 3) >= 2) ? 1.0 : -1.0, sz = b >= 4 ? 1.0 : -1.0;
-            const double d[3] = {0.125 * sx * (1 + sy * xi[1]) * (1 + sz * xi[2]), 0.125 * sy * (1 + sx * xi[0]) * (1 + sz * xi[2]),
-                                 0.125 * sz * (1 + sx * xi[0]) * (1 + sy * xi[1])};
-            const double *X = &c->coords[(size_t)(nd[b] - 1) * 3];
-            for (int i = 0; i < 3; ++i)
-              for (int j = 0; j < 3; ++j) J[i][j] += d[i] * X[j];
-          }
-          const double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
-                             J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
-          if (!(det > 0.0)) { c->hex.ok = false; c->hex.why = "an element with detJ <= 0 (inverted or mirrored numbering)"; }
-        }
-      }
+      int *d_bad = nullptr, bad = 0;
+      if ((rc = dev_alloc(c, &d_bad, 1))) return rc;
+      CK(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+      c->launches += launch_hex_detj(c, d_bad);
+      CK(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      dev_release(c, d_bad);
+      if (bad) { c->hex.ok = false; c->hex.why = "an element with detJ <= 0 (inverted or mirrored numbering)"; }
     }
     if (c->hex.ok) {
       femx::DevHex &hx = c->dhex;

@@ -222,6 +222,13 @@ struct femx_ctx {
     int nranks = 0, rank = 0;
     char *arena = nullptr;                 // [flags 1 KB | buffer 0: vals, f | buffer 1: vals, f]
     int64_t nv = 0, nf = 0;                // receive capacity (doubles) per buffer
+    int64_t nu = 0;                        // ghost-displacement receive area (doubles per buffer, indexed by local dof): pdim * nlnds
+    int64_t rnu[femx::kMaxPeers] = {};     // peers' nu
+    unsigned long long ustep = 0;          // femx_scatter_u calls done; u-area parity = ustep & 1
+    int64_t *d_sptr = nullptr, *d_srow = nullptr;   // femx_peer_set_scatter: per peer the owned global rows whose u it needs
+    int64_t udst[femx::kMaxPeers] = {};    // first local dof (in the peer's numbering) of the block this rank sends it
+    int64_t n_scatter = 0;
+    bool upending = false; double *pend_ulocal = nullptr; const double *pend_uowned = nullptr;
     char *remote[femx::kMaxPeers] = {};    // peers' arenas mapped with cudaIpcOpenMemHandle
     int64_t rnv[femx::kMaxPeers] = {}, rnf[femx::kMaxPeers] = {};   // peers' capacities (their buffer layout)
     int64_t vb[femx::kMaxPeers + 1] = {}, fb[femx::kMaxPeers + 1] = {};

@@ -270,6 +270,22 @@ __global__ void colidx_kernel(DevMesh dm, int32_t *__restrict__ colidx) {
     for (int j = 0; j < PD; ++j) colidx[PD * PD * b0 + (int64_t)i * PD * nb + PD * k + j] = gcol + j;
 }
 
+// plan-time check for the hex8 tile kernels: number of (element, integration point) pairs with detJ <= 0
+__global__ void hex_detj_kernel(DevMesh dm, int *__restrict__ bad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= dm.nels * 8) return;
+  const int e = t >> 3, ip = t & 7;
+  double X[8][3];
+  const int32_t *nd = dm.conn0 + dm.eptr[e];
+#pragma unroll
+  for (int b = 0; b < 8; ++b)
+#pragma unroll
+    for (int d = 0; d < 3; ++d) X[b][d] = dm.coords[(size_t)nd[b] * 3 + d];
+  double g[8][3];
+  const double wdet = phys_grad<FEMX_HEX>(X, ip, g);
+  if (!(wdet > 0.0)) atomicAdd(bad, 1);
+}
+
 __global__ void apply_kbc_kernel(int n, const int64_t *__restrict__ diag, double *__restrict__ vals) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) vals[diag[i]] = kPenalty;  // MatSetValue(j, j, 1e30, INSERT), src/m_global.F90:296
@@ -565,6 +581,13 @@ int launch_colidx(femx_ctx *c, int32_t *d_colidx) {
   if (!g) return 0;
   if (c->pdim == 2) colidx_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
   else colidx_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
+  return 1;
+}
+
+int launch_hex_detj(femx_ctx *c, int *d_bad) {
+  const int n = c->nels * 8;
+  if (!n) return 0;
+  hex_detj_kernel<<<nblocks(n, 128), 128, 0, c->stream>>>(c->dm, d_bad);
   return 1;
 }
 

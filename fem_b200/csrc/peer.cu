@@ -110,6 +110,42 @@ __global__ void peer_merge_f_kernel(double *__restrict__ fint, const double *__r
   fint[row[s]] = v;
 }
 
+// GetVec_U across ranks (src/m_global.F90:549-564: VecScatter global -> ghosted local): every owner stores the displacement
+// entries its peers hold as ghosts straight into their u areas (indexed by the peer's local dof), then signals.
+struct ScatterDst { double *u[kMaxPeers]; };
+__global__ void __launch_bounds__(256)
+peer_scatter_push_kernel(int nranks, int rank, const int64_t *__restrict__ sptr, const int64_t *__restrict__ srow, const double *__restrict__ u_owned,
+                         long long row_start, ScatterDst dst, FlagPtrs fp, unsigned long long *mine, unsigned nbr_mask, unsigned long long step,
+                         long long limit_clocks, int *err, unsigned int *ticket, bool wait) {
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  for (int q = 0; q < nranks; ++q) {
+    if (q == rank || !dst.u[q]) continue;
+    const long long n = sptr[q + 1] - sptr[q];
+    const int64_t *rows = srow + sptr[q];
+    for (long long i = tid; i < n; i += nth) dst.u[q][i] = u_owned[rows[i] - row_start];
+  }
+  __shared__ bool last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  if (threadIdx.x == 0) *ticket = 0;
+  signal_wait(fp, mine, nranks, rank, nbr_mask, step, limit_clocks, err, true, wait);
+}
+// the rank's own dofs from its slice of the global vector, the ghosts from the u area the owners filled
+__global__ void peer_scatter_local_kernel(double *__restrict__ u_local, const double *__restrict__ u_owned, const double *__restrict__ uarea,
+                                          const int32_t *__restrict__ nl2g, int pdim, long long n, long long own_lo, long long own_hi, long long row_start) {
+  const long long ld = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (ld >= n) return;
+  if (ld >= own_lo && ld < own_hi) {
+    const long long node = ld / pdim;
+    u_local[ld] = u_owned[(long long)pdim * (nl2g[node] - 1) + (ld - node * pdim) - row_start];
+  } else {
+    u_local[ld] = uarea[ld];
+  }
+}
+
 int64_t buffer_doubles(int64_t nv, int64_t nf) { return nv + nf; }
 
 }  // namespace
@@ -179,15 +215,19 @@ int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_
 
 extern "C" {
 
+static int launch_scatter_local(femx_ctx *c, const double *d_uown, double *d_uloc);
+
 int femx_peer_arena_create(femx_ctx *c, int64_t n_recv_vals, int64_t n_recv_f, char handle[64]) {
   if (!c) return FEMX_ERR_ARG;
   ARG(n_recv_vals >= 0 && n_recv_f >= 0 && handle, "bad arguments");
   ARG(!c->peer.arena, "the receive arena exists already");
+  ARG(c->has_mesh, "femx_set_mesh first");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
   CK(cudaSetDevice(c->device));
   auto &P = c->peer;
   P.nv = n_recv_vals; P.nf = n_recv_f;
-  const size_t bytes = (size_t)kFlagBytes + 2 * sizeof(double) * (size_t)buffer_doubles(P.nv, P.nf);
+  P.nu = (int64_t)c->pdim * c->nlnds;      // ghost displacements (femx_scatter_u) land at their local dof
+  const size_t bytes = (size_t)kFlagBytes + 2 * sizeof(double) * (size_t)(buffer_doubles(P.nv, P.nf) + P.nu);
   void *p = nullptr;
   CK(cudaMalloc(&p, bytes));
   P.arena = (char *)p;
@@ -328,9 +368,19 @@ int femx_peer_complete(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;
   auto &P = c->peer;
   ARG(P.connected && P.deferred, "femx_peer_complete belongs to deferred (local) peer connections");
-  ARG(P.pending, "no assembly is outstanding");
+  ARG(P.pending || P.upending, "no assembly / scatter is outstanding");
   CK(cudaSetDevice(c->device));
   FlagPtrs fp{};
+  if (P.upending) {
+    peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, reinterpret_cast<unsigned long long *>(P.arena + 512), P.nranks, P.rank, P.nbr_mask, P.ustep, 2000000ll,
+                                                     P.d_err, false, true);
+    c->launches += 1 + launch_scatter_local(c, P.pend_uowned, P.pend_ulocal);
+    P.upending = false;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    int rc = peer_check_error(c);
+    if (rc || !P.pending) return rc;
+  }
   for (int q = 0; q < P.nranks; ++q) fp.remote[q] = reinterpret_cast<unsigned long long *>(P.remote[q]);
   // every peer has already signalled (its assembly ran before this call): a short limit turns a protocol error into a message
   peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, reinterpret_cast<unsigned long long *>(P.arena), P.nranks, P.rank, P.nbr_mask, P.step, 2000000ll,
@@ -345,6 +395,94 @@ int femx_peer_complete(femx_ctx *c) {
 int femx_peer_last_error(femx_ctx *c) {   // used by the assemble path
   if (!c) return FEMX_ERR_ARG;
   return peer_check_error(c);
+}
+
+int femx_peer_set_scatter(femx_ctx *c, const int64_t *send_ptr, const int64_t *send_rows, const int64_t *u_dst, const int64_t *recv_u) {
+  if (!c) return FEMX_ERR_ARG;
+  auto &P = c->peer;
+  ARG(P.connected, "femx_peer_connect first");
+  ARG(send_ptr && u_dst && recv_u && send_ptr[0] == 0, "bad scatter lists");
+  ARG(c->own_row_end >= c->own_row_start && c->own_row_end >= 0, "femx_set_ownership first");
+  CK(cudaSetDevice(c->device));
+  const int64_t n = send_ptr[P.nranks];
+  ARG(n == 0 || send_rows, "bad scatter lists");
+  for (int q = 0; q < P.nranks; ++q) {
+    ARG(send_ptr[q] <= send_ptr[q + 1], "scatter ptr must ascend");
+    ARG(q == P.rank || u_dst[q] + (send_ptr[q + 1] - send_ptr[q]) <= recv_u[q], "ghost block does not fit the peer's u area");
+    P.udst[q] = u_dst[q]; P.rnu[q] = recv_u[q];
+    if (q != P.rank && send_ptr[q + 1] > send_ptr[q]) P.nbr_mask |= 1u << q;
+  }
+  for (int64_t i = 0; i < n; ++i) ARG(send_rows[i] >= c->own_row_start && send_rows[i] < c->own_row_end, "scatter row outside the owned range");
+  // ghosts of mine: their owners are neighbours too (they will signal me)
+  for (int q = 0; q < P.nranks; ++q)
+    if (q != P.rank && P.fb[q + 1] > P.fb[q]) P.nbr_mask |= 1u << q;
+  dev_release(c, P.d_sptr); dev_release(c, P.d_srow);
+  P.d_sptr = P.d_srow = nullptr;
+  int rc;
+  if ((rc = upload(c, &P.d_sptr, std::vector<int64_t>(send_ptr, send_ptr + P.nranks + 1)))) return rc;
+  if ((rc = upload(c, &P.d_srow, std::vector<int64_t>(send_rows, send_rows + n)))) return rc;
+  P.n_scatter = n;
+  CK(cudaStreamSynchronize(c->stream));
+  return FEMX_OK;
+}
+
+static const double *my_uarea(const femx_ctx *c, int par) {
+  const auto &P = c->peer;
+  return reinterpret_cast<const double *>(P.arena + kFlagBytes) + 2 * buffer_doubles(P.nv, P.nf) + par * P.nu;
+}
+
+static int launch_scatter_local(femx_ctx *c, const double *d_uown, double *d_uloc) {
+  auto &P = c->peer;
+  const long long n = (long long)c->pdim * c->nlnds;
+  if (!n) return 0;
+  const int par = (int)((P.ustep - 1) & 1);
+  peer_scatter_local_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_uloc, d_uown, my_uarea(c, par), c->dm.nl2g, c->pdim, n, P.fb[P.rank],
+                                                                                P.fb[P.rank + 1], c->own_row_start);
+  return 1;
+}
+
+// GetVec_U (src/m_global.F90:549-564; scatter built at src/main.F90:183-190): u_owned = this rank's slice [row_start, row_end)
+// of the global solution vector, u_local [pdim * nlnds] = the ghosted local vector every kernel reads.
+int femx_scatter_u(femx_ctx *c, const double *u_owned, double *u_local, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  auto &P = c->peer;
+  ARG(P.connected && P.d_sptr, "femx_peer_connect / femx_peer_set_scatter first");
+  ARG(u_owned && u_local, "NULL argument");
+  ARG(!P.upending, "a deferred femx_scatter_u is outstanding (femx_peer_complete)");
+  CK(cudaSetDevice(c->device));
+  const int64_t nown = c->own_row_end - c->own_row_start, nloc = (int64_t)c->pdim * c->nlnds;
+  View uo(c, u_owned, sizeof(double) * (size_t)nown, where, true, false);
+  View ul(c, u_local, sizeof(double) * (size_t)nloc, where, false, true);
+  if (uo.rc || ul.rc) return uo.rc | ul.rc;
+  int rc;
+  if ((rc = begin_timing(c))) return rc;
+  const int par = (int)(P.ustep & 1);
+  ++P.ustep;
+  ScatterDst dst{};
+  FlagPtrs fp{};
+  for (int q = 0; q < P.nranks; ++q) {
+    if (q == P.rank || !P.remote[q]) continue;
+    // the flag words of the u exchange sit behind those of the assembly exchange (512 bytes further)
+    fp.remote[q] = reinterpret_cast<unsigned long long *>(P.remote[q] + 512);
+    dst.u[q] = reinterpret_cast<double *>(P.remote[q] + kFlagBytes) + 2 * buffer_doubles(P.rnv[q], P.rnf[q]) + par * P.rnu[q] + P.udst[q];
+  }
+  const int grid = (int)std::min<int64_t>(296, std::max<int64_t>(1, (P.n_scatter + 255) / 256 / 4));
+  const bool wait = !P.deferred;
+  peer_scatter_push_kernel<<<grid, 256, 0, c->stream>>>(P.nranks, P.rank, P.d_sptr, P.d_srow, uo.as<double>(), c->own_row_start, dst, fp,
+                                                        reinterpret_cast<unsigned long long *>(P.arena + 512), P.nbr_mask, P.ustep, 20000000000ll, P.d_err,
+                                                        reinterpret_cast<unsigned int *>(P.d_err + 1), wait);
+  c->launches += 1;
+  if (wait) {
+    c->launches += launch_scatter_local(c, uo.as<double>(), ul.as<double>());
+    if ((rc = end_timing(c))) return rc;
+    if ((rc = ul.finish())) return rc;
+    if ((rc = finish_call(c, true))) return rc;
+    return peer_check_error(c);
+  }
+  ARG(where == FEMX_DEVICE, "deferred (local) peers: femx_scatter_u works on device buffers");
+  P.upending = true; P.pend_uowned = u_owned; P.pend_ulocal = u_local;
+  if ((rc = end_timing(c))) return rc;
+  return finish_call(c, true);
 }
 
 int femx_peer_recv(femx_ctx *c, const double **vals_recv, const double **f_recv) {

@@ -230,6 +230,15 @@ def _set_merge(fx, ep: ExchangePlan):
     fx._ck(fx.L.femx_peer_set_merge(fx.h, len(ep.m_own), p[0], p[1], p[2], len(ep.f_row), p[3], p[4], p[5]))
 
 
+def _set_scatter(fx, ep: ExchangePlan, recv_frows: list, u_dst, recv_u):
+    """reverse exchange (GetVec_U): the owned rows whose displacement each peer holds as a ghost are the rows it sends force
+    entries for; they land at that peer's local dofs f_bounds_peer[my rank] + i"""
+    ptr = np.concatenate([[0], np.cumsum([len(x) for x in recv_frows])]).astype(np.int64)
+    rows = _i64(np.concatenate([np.asarray(x, np.int64) for x in recv_frows])) if len(recv_frows) else np.zeros(0, np.int64)
+    a = [_i64(ptr), rows, _i64(u_dst), _i64(recv_u)]
+    fx._ck(fx.L.femx_peer_set_scatter(fx.h, *[x.ctypes.data for x in a]))
+
+
 class DistributedAssembly:
     """Per-rank driver: femx context on the local mesh + the exchange plan.
 
@@ -247,7 +256,9 @@ class DistributedAssembly:
         m = fx.mesh
         ep = plan_sends(self.rowptr, self.colidx, fx.nrows, nranks, rank, m.nl2g, m.pdim)
         rr, rcs, rf = exchange_lists(ep, dist, device)
+        self._recv_frows = rf
         self.ep = finish_plan(ep, self.rowptr, self.colidx, rr, rcs, rf)
+        fx._ck(fx.L.femx_set_ownership(fx.h, nranks, rank, ep.row_start, ep.row_end))
         self.vals_local = torch.empty(fx.nnz, dtype=torch.float64, device=device)
         self.recv = torch.empty(int(self.ep.recv_counts.sum()), dtype=torch.float64, device=device)
         self.send_splits = [int(h - l) if q != rank else 0 for q, (l, h) in enumerate(zip(ep.send_lo, ep.send_hi))]
@@ -284,6 +295,19 @@ class DistributedAssembly:
         fx._ck(fx.L.femx_peer_connect(fx.h, P, ep.rank, handles, *[a.ctypes.data for a in args]))
         _set_merge(fx, ep)
         self.n_recv_f = int(caps[ep.rank, 1])
+        # GetVec_U: every rank tells its peers where (in its local dof numbering) the block they own starts, and its pdim * nlnds
+        mine = torch.tensor(np.stack([lay["f_bounds"][:-1], np.full(P, fx.mesh.pdim * fx.mesh.nlnds)], 1).reshape(-1), dtype=torch.int64, device=self.device)
+        theirs = torch.empty_like(mine)
+        dist.all_to_all_single(theirs, mine)
+        theirs = theirs.cpu().numpy().reshape(P, 2)
+        _set_scatter(fx, ep, self._recv_frows, theirs[:, 0], theirs[:, 1])
+
+    def scatter_u(self, u_owned, u_local):
+        """GetVec_U (src/m_global.F90:549-564): u_owned = this rank's slice of the global vector (device tensor),
+        u_local = the ghosted local vector [pdim * nlnds] (device tensor, filled)."""
+        import ctypes as C
+        self.fx._ck(self.fx.L.femx_scatter_u(self.fx.h, C.c_void_p(u_owned.data_ptr()), C.c_void_p(u_local.data_ptr()), 1))
+        return u_local
 
     def peer_received(self):
         """(values, force entries) the last assembly received, as torch views of the arena."""
@@ -363,8 +387,30 @@ class LocalRanks:
             val_dst = _i64([lays[q]["recv_voff"][r] for q in range(P)])      # where my slice starts in rank q's arena
             f_dst = _i64([lays[q]["recv_foff"][r] for q in range(P)])
             args = [_i64(caps[:, 0]), _i64(caps[:, 1]), _i64(lays[r]["val_bounds"]), val_dst, _i64(lays[r]["f_bounds"]), f_dst, _i64(lays[r]["recv_from"])]
+            fx._ck(fx.L.femx_set_ownership(fx.h, P, r, self.eps[r].row_start, self.eps[r].row_end))
             fx._ck(fx.L.femx_peer_connect_local(fx.h, P, r, C.addressof(ptrs), *[a.ctypes.data for a in args]))
             _set_merge(fx, self.eps[r])
+            _set_scatter(fx, self.eps[r], [eps[s].send_frows[r] for s in range(P)], [lays[q]["f_bounds"][r] for q in range(P)],
+                         [fxs[q].mesh.pdim * fxs[q].mesh.nlnds for q in range(P)])
+
+    def scatter_u(self, u_global: np.ndarray):
+        """GetVec_U on every rank: each gets its slice of the global vector and returns its ghosted local vector (host)."""
+        from . import api
+        bufs = []
+        for r, fx in enumerate(self.fxs):
+            ep = self.eps[r]
+            d_o = api.DeviceBuffer(fx, max(8, 8 * (ep.row_end - ep.row_start))).upload(np.ascontiguousarray(u_global[ep.row_start:ep.row_end]))
+            d_l = api.DeviceBuffer(fx, 8 * fx.mesh.pdim * fx.mesh.nlnds)
+            fx._ck(fx.L.femx_scatter_u(fx.h, d_o.ptr, d_l.ptr, api.DEVICE))        # push + signal
+            bufs.append((d_o, d_l))
+        out = []
+        for r, fx in enumerate(self.fxs):
+            fx._ck(fx.L.femx_peer_complete(fx.h))                                  # flags + local gather
+        for r, fx in enumerate(self.fxs):
+            out.append(bufs[r][1].download().reshape(-1, fx.mesh.pdim))
+            for b in bufs[r]:
+                b.free()
+        return out
 
     def assemble_K_fint(self, us: list):
         """One collective assembly.  Returns per rank (rowptr, colidx, vals) of the owned rows (host) and the global internal

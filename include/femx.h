@@ -220,6 +220,16 @@ int femx_peer_set_merge(femx_ctx *ctx, int64_t n, const int64_t *own_slot, const
 int femx_peer_merged(femx_ctx *ctx, const double **merged, int64_t *n);
 int femx_peer_complete(femx_ctx *ctx);
 int femx_peer_last_error(femx_ctx *ctx);   /* reports (and clears) a step-barrier timeout */
+/* GetVec_U across ranks (src/m_global.F90:549-564; scatter of src/main.F90:183-190), the reverse of the force exchange:
+ * femx_peer_set_scatter names, per peer q, the owned global rows send_rows[send_ptr[q] .. send_ptr[q+1]) whose
+ * displacement q holds as a ghost (= the rows q sends force entries for, the transpose of f_bounds), u_dst[q] = the
+ * first local dof of that block in q's numbering, recv_u[q] = pdim * nlnds of rank q.  femx_scatter_u then turns this
+ * rank's slice u_owned [row_end - row_start] of the global vector into the ghosted local vector u_local [pdim * nlnds]
+ * every kernel reads: owners store into the peers' u areas over NVLink, neighbours' step barrier, local gather.
+ * Deferred (local) peers: push + signal only, femx_peer_complete finishes (device buffers only). */
+int femx_peer_set_scatter(femx_ctx *ctx, const int64_t *send_ptr, const int64_t *send_rows, const int64_t *u_dst,
+                          const int64_t *recv_u);
+int femx_scatter_u(femx_ctx *ctx, const double *u_owned, double *u_local, int where);
 int femx_peer_recv(femx_ctx *ctx, const double **vals_recv, const double **f_recv);
 int femx_peer_disconnect(femx_ctx *ctx);
 

@@ -66,6 +66,10 @@ def test_local_ranks_exchange_on_one_gpu(orc, world, kind, variant):
                 assert _close(va, va_g[rp_g[r0]:rp_g[r1]], np.abs(va_g).max()), (r, rep)
                 assert len(lr.eps[r].if_rows) < (r1 - r0)      # the receiver add touches interface rows only
             assert _close(f_tot, f_ref, np.abs(f_ref).max()), rep
+            # GetVec_U (R17): owners push the ghost displacements; every rank's local vector must be the global one gathered
+            ugl = ug.reshape(-1) + rep
+            for r, ul in enumerate(lr.scatter_u(ugl)):
+                assert np.array_equal(ul, ugl.reshape(-1, g.pdim)[locs[r].nl2g - 1]), (r, rep)
         lr.close()
     finally:
         for fx in fxs:

@@ -64,6 +64,11 @@ def main():
         f_ref = orc.fint(og, mg.displacement_field(g).reshape(-1))
         f = d_f.cpu().numpy()
         good = good and np.all(np.abs(f - f_ref) <= 1e-12 * np.maximum(np.abs(f_ref), np.abs(f_ref).max()))
+        if peer == 1:                              # GetVec_U through the arenas: owned slice of the global vector -> ghosted local vector
+            ug_all = torch.from_numpy(mg.displacement_field(g).reshape(-1) + rep).to(dev)
+            ul = da.scatter_u(ug_all[da.ep.row_start:da.ep.row_end].contiguous(), torch.empty(loc.pdim * loc.nlnds, dtype=torch.float64, device=dev))
+            want_u = ug_all.cpu().numpy().reshape(-1, g.pdim)[loc.nl2g - 1].reshape(-1)
+            good = good and np.array_equal(ul.cpu().numpy(), want_u)
         if rep == 0 and peer == 0:                 # nodal stress across ranks (femx_stress_partial + DistributedStress)
             ds = par.DistributedStress(fx, dist, dev)
             s_loc = ds.stress(C.c_void_p(d_u.data_ptr())).cpu().numpy()
