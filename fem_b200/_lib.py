@@ -40,6 +40,11 @@ SIGNATURES = {
     "femx_build_plan": (C.c_int, [V]),
     "femx_pattern_size": (C.c_int, [V, c_i64_p, c_i64_p]),
     "femx_get_pattern": (C.c_int, [V, V, V, C.c_int]),
+    "femx_get_coo": (C.c_int, [V, V, V, C.c_int]),
+    "femx_mpiaij_sizes": (C.c_int, [V, C.c_int64, C.c_int64, V, V, V]),
+    "femx_get_pattern_mpiaij": (C.c_int, [V, C.c_int64, C.c_int64, V, V, V, V, V]),
+    "femx_set_stream": (C.c_int, [V, V]),
+    "femx_set_async": (C.c_int, [V, C.c_int]),
     "femx_get_slot_map": (C.c_int, [V, c_i64_p, c_u16_p]),
     "femx_element_ke": (C.c_int, [V, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p]),
     "femx_element_stress": (C.c_int, [V, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p]),

@@ -135,6 +135,11 @@ void nodal_stress_tables(double *qua16, double *hex64) {
 int begin_timing(femx_ctx *c) { CK(cudaEventRecord(c->ev0, c->stream)); return FEMX_OK; }
 int end_timing(femx_ctx *c) { CK(cudaEventRecord(c->ev1, c->stream)); return FEMX_OK; }
 int finish_call(femx_ctx *c, bool timed) {
+  if (c->async) {                       // femx_set_async: the caller orders later work on the stream / calls femx_synchronize
+    c->ms_pending = timed;
+    CK(cudaPeekAtLastError());
+    return FEMX_OK;
+  }
   CK(cudaStreamSynchronize(c->stream));
   CK(cudaGetLastError());
   if (timed) {

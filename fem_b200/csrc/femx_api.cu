@@ -33,7 +33,7 @@ int femx_create(femx_ctx **out, int device, const femx_opts *opts) {
   femx_ctx *c = new femx_ctx;
   c->device = device;
   if (opts) c->opts = *opts;
-  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess || (c->stream = c->own_stream, false) ||
       cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
     g_create_err = "stream/event creation failed";
     delete c;
@@ -55,7 +55,7 @@ int femx_destroy(femx_ctx *c) {
   for (void *p : c->allocs) cudaFree(p);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
-  cudaStreamDestroy(c->stream);
+  cudaStreamDestroy(c->own_stream);
   delete c;
   return FEMX_OK;
 }
@@ -88,6 +88,31 @@ int femx_memcpy(femx_ctx *c, void *dst, const void *src, int64_t bytes, int dw, 
 int femx_synchronize(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  if (c->ms_pending) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->last_ms = ms;
+    c->ms_pending = false;
+  }
+  if (c->peer.connected && c->peer.d_err && !c->peer.deferred) return femx_peer_last_error(c);
+  return FEMX_OK;
+}
+// Threading / streams: by default every call runs on the ctx's own stream and returns synchronised.
+// femx_set_stream puts the ctx on the caller's CUDA stream (a cudaStream_t passed as void *; NULL = back to its own), so
+// that femx work is ordered with the caller's own kernels / PETSc's; femx_set_async(1) makes calls on FEMX_DEVICE buffers
+// return as soon as the work is enqueued -- the host overlaps femx_jacobian with anything else and calls femx_synchronize
+// (or synchronises its stream) before it reads results or timings.  Host-buffer calls stay usable: their D2H copies are
+// enqueued too and complete at femx_synchronize.
+int femx_set_stream(femx_ctx *c, void *cuda_stream) {
+  if (!c) return FEMX_ERR_ARG;
+  CK(cudaStreamSynchronize(c->stream));
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+  return FEMX_OK;
+}
+int femx_set_async(femx_ctx *c, int on) {
+  if (!c) return FEMX_ERR_ARG;
+  if (!on) CK(cudaStreamSynchronize(c->stream));
+  c->async = on != 0;
   return FEMX_OK;
 }
 int64_t femx_launch_count(const femx_ctx *c) { return c ? c->launches : 0; }
@@ -417,6 +442,87 @@ int femx_get_pattern(femx_ctx *c, int64_t *rowptr, int32_t *colidx, int where) {
     CK(cudaGetLastError());
   }
   return FEMX_OK;
+}
+
+// ---- PETSc hand-off: the index arrays of MatSetPreallocationCOO and the MPIAIJ split of the owned rows
+int femx_get_coo(femx_ctx *c, int32_t *coo_i, int32_t *coo_j, int where) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && coo_i && coo_j, "femx_build_plan first / NULL argument");
+  ARG((int64_t)c->pdim * c->nnds < 2147483647ll, "global dofs exceed 32-bit PetscInt");
+  CK(cudaSetDevice(c->device));
+  View vi(c, coo_i, sizeof(int32_t) * (size_t)c->nnz, where, false, true), vj(c, coo_j, sizeof(int32_t) * (size_t)c->nnz, where, false, true);
+  if (vi.rc || vj.rc) return vi.rc | vj.rc;
+  c->launches += launch_coo(c, vi.as<int32_t>(), vj.as<int32_t>());
+  int rc;
+  if ((rc = vi.finish()) || (rc = vj.finish())) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  return FEMX_OK;
+}
+
+// rows [row_start, row_end) of the rank-local pattern in MPIAIJ form: the diagonal block (columns inside the range, local
+// column numbers) and the off-diagonal block compacted through garray (ascending global columns) -- Mat_MPIAIJ's A / B / garray
+static int mpiaij_walk(femx_ctx *c, int64_t row_start, int64_t row_end, int64_t *d_rowptr, int32_t *d_col, int64_t *o_rowptr, int32_t *o_col,
+                       std::vector<int32_t> *garray, int64_t *nd_out, int64_t *no_out) {
+  const int pd = c->pdim;
+  ARG(row_start >= 0 && row_end >= row_start && row_end <= (int64_t)pd * c->nnds, "bad row range");
+  const femx::Plan &P = c->plan;
+  std::vector<int32_t> &ga = *garray;
+  const bool fill = d_col != nullptr;
+  if (!fill) {   // first pass: collect the off-diagonal columns
+    ga.clear();
+    for (int r = 0; r < c->nlnds; ++r) {
+      const int64_t g0 = (int64_t)pd * (c->nl2g[r] - 1);
+      if (g0 + pd <= row_start || g0 >= row_end) continue;
+      for (int64_t b = P.bptr[r]; b < P.bptr[r + 1]; ++b) {
+        const int64_t c0 = (int64_t)pd * (c->nl2g[P.bcol[b]] - 1);
+        for (int j = 0; j < pd; ++j)
+          if (c0 + j < row_start || c0 + j >= row_end) ga.push_back((int32_t)(c0 + j));
+      }
+    }
+    std::sort(ga.begin(), ga.end());
+    ga.erase(std::unique(ga.begin(), ga.end()), ga.end());
+  }
+  int64_t nd = 0, no = 0;
+  int r = (int)(std::lower_bound(c->nl2g.begin(), c->nl2g.end(), (int32_t)(row_start / pd + 1)) - c->nl2g.begin());
+  for (int64_t g = row_start; g < row_end; ++g) {
+    if (fill) { d_rowptr[g - row_start] = nd; o_rowptr[g - row_start] = no; }
+    const int32_t node = (int32_t)(g / pd + 1);
+    while (r < c->nlnds && c->nl2g[r] < node) ++r;
+    if (r >= c->nlnds || c->nl2g[r] != node) continue;      // a row of a node this rank does not hold: empty
+    for (int64_t b = P.bptr[r]; b < P.bptr[r + 1]; ++b) {
+      const int64_t c0 = (int64_t)pd * (c->nl2g[P.bcol[b]] - 1);
+      for (int j = 0; j < pd; ++j) {
+        const int64_t col = c0 + j;
+        if (col >= row_start && col < row_end) { if (fill) d_col[nd] = (int32_t)(col - row_start); ++nd; }
+        else { if (fill) o_col[no] = (int32_t)(std::lower_bound(ga.begin(), ga.end(), (int32_t)col) - ga.begin()); ++no; }
+      }
+    }
+  }
+  if (fill) { d_rowptr[row_end - row_start] = nd; o_rowptr[row_end - row_start] = no; }
+  if (nd_out) *nd_out = nd;
+  if (no_out) *no_out = no;
+  return FEMX_OK;
+}
+
+int femx_mpiaij_sizes(femx_ctx *c, int64_t row_start, int64_t row_end, int64_t *nnz_diag, int64_t *nnz_offdiag, int64_t *n_garray) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan, "femx_build_plan first");
+  std::vector<int32_t> ga;
+  int rc = mpiaij_walk(c, row_start, row_end, nullptr, nullptr, nullptr, nullptr, &ga, nnz_diag, nnz_offdiag);
+  if (n_garray) *n_garray = (int64_t)ga.size();
+  return rc;
+}
+
+int femx_get_pattern_mpiaij(femx_ctx *c, int64_t row_start, int64_t row_end, int64_t *d_rowptr, int32_t *d_col, int64_t *o_rowptr, int32_t *o_col,
+                            int32_t *garray) {
+  if (!c) return FEMX_ERR_ARG;
+  ARG(c->has_plan && d_rowptr && d_col && o_rowptr && o_col && garray, "femx_build_plan first / NULL argument");
+  std::vector<int32_t> ga;
+  int rc = mpiaij_walk(c, row_start, row_end, nullptr, nullptr, nullptr, nullptr, &ga, nullptr, nullptr);
+  if (rc) return rc;
+  memcpy(garray, ga.data(), sizeof(int32_t) * ga.size());
+  return mpiaij_walk(c, row_start, row_end, d_rowptr, d_col, o_rowptr, o_col, &ga, nullptr, nullptr);
 }
 
 int femx_get_slot_map(femx_ctx *c, int64_t *offsets, uint16_t *blockpos) {

@@ -88,7 +88,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
   if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;
   if ((rc = finish_call(c, true))) return rc;
-  if (peer && (rc = femx_peer_last_error(c))) return rc;
+  if (peer && !c->async && (rc = femx_peer_last_error(c))) return rc;
   return FEMX_OK;
 }
 

@@ -174,6 +174,9 @@ struct femx_ctx {
   int device = 0;
   femx_opts opts{};
   cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;   // the stream femx_create made (femx_set_stream may substitute the caller's)
+  bool async = false;                 // femx_set_async: calls return without synchronising the stream
+  bool ms_pending = false;            // ... the last call's event pair has not been read yet
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   std::string err;
   int64_t launches = 0;

@@ -286,6 +286,28 @@ __global__ void hex_detj_kernel(DevMesh dm, int *__restrict__ bad) {
   if (!(wdet > 0.0)) atomicAdd(bad, 1);
 }
 
+// COO (i, j) of every value in femx_get_pattern order: the arrays MatSetPreallocationCOO takes
+template <int PD>
+__global__ void coo_kernel(DevMesh dm, int32_t *__restrict__ coo_i, int32_t *__restrict__ coo_j) {
+  const int64_t blk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nblk = dm.bptr[dm.nlnds];
+  if (blk >= nblk) return;
+  int lo = 0, hi = dm.nlnds;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (dm.bptr[mid] <= blk) lo = mid; else hi = mid;
+  }
+  const int64_t b0 = dm.bptr[lo];
+  const int nb = (int)(dm.bptr[lo + 1] - b0), k = (int)(blk - b0);
+  const int grow = PD * (dm.nl2g[lo] - 1), gcol = PD * (dm.nl2g[dm.bcol[blk]] - 1);
+  for (int i = 0; i < PD; ++i)
+    for (int j = 0; j < PD; ++j) {
+      const int64_t s = PD * PD * b0 + (int64_t)i * PD * nb + PD * k + j;
+      coo_i[s] = grow + i;
+      coo_j[s] = gcol + j;
+    }
+}
+
 __global__ void apply_kbc_kernel(int n, const int64_t *__restrict__ diag, double *__restrict__ vals) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) vals[diag[i]] = kPenalty;  // MatSetValue(j, j, 1e30, INSERT), src/m_global.F90:296
@@ -581,6 +603,14 @@ int launch_colidx(femx_ctx *c, int32_t *d_colidx) {
   if (!g) return 0;
   if (c->pdim == 2) colidx_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
   else colidx_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_colidx);
+  return 1;
+}
+
+int launch_coo(femx_ctx *c, int32_t *d_i, int32_t *d_j) {
+  const int bs = 256, g = nblocks(c->plan.nblk, bs);
+  if (!g) return 0;
+  if (c->pdim == 2) coo_kernel<2><<<g, bs, 0, c->stream>>>(c->dm, d_i, d_j);
+  else coo_kernel<3><<<g, bs, 0, c->stream>>>(c->dm, d_i, d_j);
   return 1;
 }
 

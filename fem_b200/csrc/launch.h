@@ -13,6 +13,7 @@ int launch_element_stress(femx_ctx *c, int type, int n, const double *d_x, const
                           double *d_sig, double *d_sn);
 int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_out, int col_major, int average);
 int launch_colidx(femx_ctx *c, int32_t *d_colidx);
+int launch_coo(femx_ctx *c, int32_t *d_i, int32_t *d_j);
 int launch_hex_detj(femx_ctx *c, int *d_bad);   // hex8 meshes: counts (element, integration point) pairs with detJ <= 0
 int launch_apply_kbc(femx_ctx *c, double *d_vals);
 int launch_bc_force(femx_ctx *c, double dt, double t_total, double *d_out);

@@ -164,12 +164,53 @@ module femx
       character(kind=c_char), intent(out) :: handle(64)
     end function
     integer(c_int) function femx_peer_connect(ctx, nranks, rank, handles, recv_vals, recv_f, val_bounds, val_dst, &
-                                              f_bounds, f_dst) bind(C, name="femx_peer_connect")
+                                              f_bounds, f_dst, recv_from) bind(C, name="femx_peer_connect")
       import :: c_ptr, c_int, c_int64_t, c_char
       type(c_ptr), value :: ctx
       integer(c_int), value :: nranks, rank
       character(kind=c_char), intent(in) :: handles(*)
-      integer(c_int64_t), intent(in) :: recv_vals(*), recv_f(*), val_bounds(*), val_dst(*), f_bounds(*), f_dst(*)
+      integer(c_int64_t), intent(in) :: recv_vals(*), recv_f(*), val_bounds(*), val_dst(*), f_bounds(*), f_dst(*), recv_from(*)
+    end function
+    ! ranks that are ctxs of one process on one device: peers(q) = the q-th ctx
+    integer(c_int) function femx_peer_connect_local(ctx, nranks, rank, peers, recv_vals, recv_f, val_bounds, val_dst, &
+                                                    f_bounds, f_dst, recv_from) bind(C, name="femx_peer_connect_local")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: nranks, rank
+      type(c_ptr), intent(in) :: peers(*)
+      integer(c_int64_t), intent(in) :: recv_vals(*), recv_f(*), val_bounds(*), val_dst(*), f_bounds(*), f_dst(*), recv_from(*)
+    end function
+    ! the receiver add of MatAssemblyEnd over the interface rows (src/main.F90:167-168)
+    integer(c_int) function femx_peer_set_merge(ctx, n, own_slot, ptr, idx, nf, f_row, f_ptr, f_idx) bind(C, name="femx_peer_set_merge")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), value :: n, nf
+      integer(c_int64_t), intent(in) :: own_slot(*), ptr(*), idx(*), f_row(*), f_ptr(*), f_idx(*)
+    end function
+    integer(c_int) function femx_peer_merged(ctx, merged, n) bind(C, name="femx_peer_merged")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      type(c_ptr), intent(out) :: merged
+      integer(c_int64_t), intent(out) :: n
+    end function
+    integer(c_int) function femx_peer_complete(ctx) bind(C, name="femx_peer_complete")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
+    integer(c_int) function femx_peer_last_error(ctx) bind(C, name="femx_peer_last_error")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
+    ! GetVec_U (src/m_global.F90:549-564): owned slice of Vec_U -> ghosted local vector
+    integer(c_int) function femx_peer_set_scatter(ctx, send_ptr, send_rows, u_dst, recv_u) bind(C, name="femx_peer_set_scatter")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), intent(in) :: send_ptr(*), send_rows(*), u_dst(*), recv_u(*)
+    end function
+    integer(c_int) function femx_scatter_u(ctx, u_owned, u_local, where) bind(C, name="femx_scatter_u")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, u_owned, u_local     ! c_loc of host arrays or device pointers, by `where`
+      integer(c_int), value :: where
     end function
     integer(c_int) function femx_peer_recv(ctx, vals_recv, f_recv) bind(C, name="femx_peer_recv")
       import :: c_ptr, c_int
@@ -179,6 +220,101 @@ module femx
     integer(c_int) function femx_peer_disconnect(ctx) bind(C, name="femx_peer_disconnect")
       import :: c_ptr, c_int
       type(c_ptr), value :: ctx
+    end function
+    ! ---- memory and streams for hosts without a CUDA runtime of their own
+    integer(c_int) function femx_host_alloc(ptr, bytes) bind(C, name="femx_host_alloc")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), intent(out) :: ptr
+      integer(c_int64_t), value :: bytes
+    end function
+    integer(c_int) function femx_host_free(ptr) bind(C, name="femx_host_free")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ptr
+    end function
+    integer(c_int) function femx_device_alloc(ctx, ptr, bytes) bind(C, name="femx_device_alloc")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      type(c_ptr), intent(out) :: ptr
+      integer(c_int64_t), value :: bytes
+    end function
+    integer(c_int) function femx_device_free(ctx, ptr) bind(C, name="femx_device_free")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, ptr
+    end function
+    integer(c_int) function femx_memcpy(ctx, dst, src, bytes, dst_where, src_where) bind(C, name="femx_memcpy")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx, dst, src
+      integer(c_int64_t), value :: bytes
+      integer(c_int), value :: dst_where, src_where
+    end function
+    integer(c_int) function femx_synchronize(ctx) bind(C, name="femx_synchronize")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+    end function
+    integer(c_int) function femx_set_stream(ctx, cuda_stream) bind(C, name="femx_set_stream")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, cuda_stream          ! e.g. PetscDeviceContextGetStreamHandle
+    end function
+    integer(c_int) function femx_set_async(ctx, on) bind(C, name="femx_set_async")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: on
+    end function
+    ! ---- PETSc hand-off: MatSetPreallocationCOO arrays and the MPIAIJ split
+    integer(c_int) function femx_get_coo(ctx, coo_i, coo_j, where) bind(C, name="femx_get_coo")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, coo_i, coo_j         ! int32 [nnz]
+      integer(c_int), value :: where
+    end function
+    integer(c_int) function femx_mpiaij_sizes(ctx, row_start, row_end, nnz_diag, nnz_offdiag, n_garray) bind(C, name="femx_mpiaij_sizes")
+      import :: c_ptr, c_int, c_int64_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), value :: row_start, row_end
+      integer(c_int64_t), intent(out) :: nnz_diag, nnz_offdiag, n_garray
+    end function
+    integer(c_int) function femx_get_pattern_mpiaij(ctx, row_start, row_end, d_rowptr, d_col, o_rowptr, o_col, garray) &
+        bind(C, name="femx_get_pattern_mpiaij")
+      import :: c_ptr, c_int, c_int64_t, c_int32_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), value :: row_start, row_end
+      integer(c_int64_t), intent(out) :: d_rowptr(*), o_rowptr(*)
+      integer(c_int32_t), intent(out) :: d_col(*), o_col(*), garray(*)
+    end function
+    integer(c_int) function femx_get_slot_map(ctx, offsets, blockpos) bind(C, name="femx_get_slot_map")
+      import :: c_ptr, c_int, c_int64_t, c_int16_t
+      type(c_ptr), value :: ctx
+      integer(c_int64_t), intent(out) :: offsets(*)
+      integer(c_int16_t), intent(out) :: blockpos(*)   ! uint16 bit patterns
+    end function
+    ! ---- element-level entry points (unit parity): CalcElStress src/m_local.F90:93, applyTract_1 / applyStiff_1 src/m_global.F90:622, :762
+    integer(c_int) function femx_element_stress(ctx, etype, n, ecoords, edisp, E_nu, estress, enodal) bind(C, name="femx_element_stress")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: etype, n
+      real(c_double), intent(in) :: ecoords(*), edisp(*), E_nu(*)
+      real(c_double), intent(out) :: estress(*), enodal(*)
+    end function
+    integer(c_int) function femx_element_cohesive(ctx, n, ecoords, nodes, u_local, nu_local, props, dt, force, stiff) &
+        bind(C, name="femx_element_cohesive")
+      import :: c_ptr, c_int, c_double
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: n, nu_local
+      real(c_double), intent(in) :: ecoords(*), u_local(*), props(*)
+      integer(c_int), intent(in) :: nodes(*)
+      real(c_double), value :: dt
+      real(c_double), intent(out) :: force(*), stiff(*)
+    end function
+    ! ---- instrumentation
+    integer(c_int64_t) function femx_launch_count(ctx) bind(C, name="femx_launch_count")
+      import :: c_ptr, c_int64_t
+      type(c_ptr), value :: ctx
+    end function
+    real(c_double) function femx_last_kernel_ms(ctx) bind(C, name="femx_last_kernel_ms")
+      import :: c_ptr, c_double
+      type(c_ptr), value :: ctx
+    end function
+    integer(c_int) function femx_version() bind(C, name="femx_version")
+      import :: c_int
     end function
   end interface
 

@@ -84,6 +84,12 @@ int femx_device_alloc(femx_ctx *ctx, void **ptr, int64_t bytes);
 int femx_device_free(femx_ctx *ctx, void *ptr);
 int femx_memcpy(femx_ctx *ctx, void *dst, const void *src, int64_t bytes, int dst_where, int src_where);
 int femx_synchronize(femx_ctx *ctx);
+/* Streams (SURVEY.md 8b threading row).  Default: every call runs on the ctx's own stream and returns synchronised.
+ * femx_set_stream puts the ctx on the caller's cudaStream_t (passed as void *; NULL = its own stream again);
+ * femx_set_async(ctx, 1) makes calls return once their work is enqueued, so a host can overlap femx_jacobian with
+ * anything else; femx_synchronize (or a synchronise of that stream) before results, timings or errors are read. */
+int femx_set_stream(femx_ctx *ctx, void *cuda_stream);
+int femx_set_async(femx_ctx *ctx, int on);
 
 /* ---- state the path reads (module globals of src/m_global.F90:17-87) ------------- */
 /* local_elements(:) as eptr/eind (exactly what PartitionBroadcast builds at
@@ -105,6 +111,20 @@ int femx_pattern_size(femx_ctx *ctx, int64_t *nrows, int64_t *nnz);
 /* CSR of the assembled AIJ: columns ascending, explicit zeros kept (what MatView shows,
  * examples/tmp.txt:15-33).  Either pointer may be NULL. */
 int femx_get_pattern(femx_ctx *ctx, int64_t *rowptr, int32_t *colidx, int where);
+/* PETSc hand-off (the reference creates its Mat at src/main.F90:153-156 and fills it with MatSetValues):
+ * femx_get_coo fills the (i, j) arrays MatSetPreallocationCOO takes -- global row and column of every value, in
+ * femx_get_pattern / femx_assemble_K order, so that MatSetValuesCOO(A, vals, INSERT_VALUES) consumes the device array the
+ * assembly wrote without any copy or reordering (rows of other ranks may appear: COO assembly ships them, or the caller
+ * uses femx_peer_* and sets the interface rows' i to -1, which COO ignores).  32-bit PetscInt.
+ * femx_mpiaij_sizes / femx_get_pattern_mpiaij give rows [row_start, row_end) of the rank-local pattern the way
+ * Mat_MPIAIJ stores them: the diagonal block (columns inside the range, local numbering) and the off-diagonal block
+ * with columns compacted through garray (ascending global columns) -- for MatCreateMPIAIJWithSplitArrays or
+ * MatMPIAIJSetPreallocationCSR-style exact preallocation instead of the reference's d_nz = o_nz guess. */
+int femx_get_coo(femx_ctx *ctx, int32_t *coo_i, int32_t *coo_j, int where);
+int femx_mpiaij_sizes(femx_ctx *ctx, int64_t row_start, int64_t row_end, int64_t *nnz_diag, int64_t *nnz_offdiag,
+                      int64_t *n_garray);
+int femx_get_pattern_mpiaij(femx_ctx *ctx, int64_t row_start, int64_t row_end, int64_t *d_rowptr, int32_t *d_col,
+                            int64_t *o_rowptr, int32_t *o_col, int32_t *garray);
 /* element -> nonzero-slot map at node-block granularity: for element e, local nodes a, b
  * slot(e,a,i,b,j) = rowstart(row(a,i)) + pdim*blockpos[e][a*nen+b] + j.
  * blockpos is [sum nen^2] uint16, offsets [nels+1] (int64). */
