@@ -312,3 +312,32 @@ def petsc_ownership(n: int, nranks: int, rank: int):
     base, rem = divmod(n, nranks)
     start = rank * base + min(rank, rem)
     return start, start + base + (1 if rank < rem else 0)
+
+
+def metis_partition(g: Mesh, nparts: int):
+    """Element partition the way PartitionBroadcast gets it (src/m_io.F90:125-141): METIS_PartMeshNodal on the 0-based
+    element -> node lists, every optional argument null, epart kept.  Calls tools/libmetispart.so (tools/metis_part.c: the
+    METIS inside the CUDA toolkit, 64-bit idx_t), built on first use with `make -C tools metis`.  Returns (epart, edge cut);
+    raises RuntimeError when the wrapper cannot be built or METIS fails."""
+    import ctypes
+    import os
+    import subprocess
+    tools = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools")
+    so = os.path.join(tools, "libmetispart.so")
+    if not os.path.exists(so):
+        r = subprocess.run(["make", "-C", tools, "metis"], capture_output=True, text=True)
+        if r.returncode != 0 or not os.path.exists(so):
+            raise RuntimeError("cannot build tools/libmetispart.so: " + (r.stderr or r.stdout)[-500:])
+    lib = ctypes.CDLL(so)
+    fn = lib.femx_metis_part_mesh_nodal
+    ip = ctypes.POINTER(ctypes.c_int)
+    fn.argtypes = [ctypes.c_int, ctypes.c_int, ip, ip, ctypes.c_int, ip, ctypes.POINTER(ctypes.c_longlong)]
+    fn.restype = ctypes.c_int
+    eptr = np.ascontiguousarray(g.eptr, np.int32)
+    eind = np.ascontiguousarray(np.asarray(g.eind, np.int32) - 1)
+    epart = np.zeros(g.nels, np.int32)
+    cut = ctypes.c_longlong(0)
+    rc = fn(g.nels, g.nnds, eptr.ctypes.data_as(ip), eind.ctypes.data_as(ip), int(nparts), epart.ctypes.data_as(ip), ctypes.byref(cut))
+    if rc != 1:
+        raise RuntimeError(f"METIS_PartMeshNodal returned {rc}")
+    return epart, int(cut.value)
