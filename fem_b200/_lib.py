@@ -58,6 +58,8 @@ SIGNATURES = {
     "femx_residual": (C.c_int, [V, V, V, V, V, C.c_double, C.c_double, V, C.c_int]),
     "femx_residual_forces": (C.c_int, [V, V, V, C.c_double, C.c_double, V, C.c_int]),
     "femx_stress": (C.c_int, [V, V, V, C.c_int, C.c_int]),
+    "femx_stress_noalloc": (C.c_int, [V, V, V, C.c_int]),
+    "femx_stress_noalloc_max_doubles": (C.c_int64, []),
     "femx_set_ownership": (C.c_int, [V, C.c_int, C.c_int, C.c_int64, C.c_int64]),
     "femx_gather_sum": (C.c_int, [V, V, C.c_int64, V, V, V, C.c_int64, V]),
     "femx_stress_partial": (C.c_int, [V, V, V, V, C.c_int]),

@@ -117,6 +117,15 @@ module femx
       type(c_ptr), value :: ctx, uu_local, stress_node
       integer(c_int), value :: layout, where
     end function
+    ! no counterpart in the reference: femx_stress on a static device scratch, no allocation (include/femx.h)
+    integer(c_int) function femx_stress_noalloc(ctx, d_uu_local, d_stress_node, layout) bind(C, name="femx_stress_noalloc")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx, d_uu_local, d_stress_node
+      integer(c_int), value :: layout
+    end function
+    integer(c_int64_t) function femx_stress_noalloc_max_doubles() bind(C, name="femx_stress_noalloc_max_doubles")
+      import :: c_int64_t
+    end function
     integer(c_int) function femx_element_ke(ctx, etype, n, ecoords, E_nu, ke) bind(C, name="femx_element_ke")
       import :: c_ptr, c_int, c_double
       type(c_ptr), value :: ctx

@@ -190,6 +190,19 @@ int femx_set_loads(femx_ctx *ctx, int nfrcs, const int *fnode, const double *fva
                    const double *tval);
 int femx_form_rhs(femx_ctx *ctx, double t_init, double dt, double t_total, double *f, int where);
 int femx_stress(femx_ctx *ctx, const double *uu_local, double *stress_node, int layout, int where);
+/* No counterpart in the reference.  femx_stress for callers that may not
+ * allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): same two kernels, same bits,
+ * but the per-(element, node) stress scratch is a file-scope device array of FEMX_STRESS_NOALLOC_MAX_DOUBLES doubles
+ * (16 MiB, held by every GPU that loads the library until the process exits; csrc/stress_static.cu) instead of a context
+ * buffer grown with cudaMalloc, and the call makes no cudaMalloc / cudaFree / allocating library call.  d_uu_local
+ * [nlnds*pdim] and d_stress_node [nlnds*cp] are DEVICE buffers of the caller (pageable host memory -> FEMX_ERR_ARG).
+ * A mesh with (sum of element node counts) * cp > FEMX_STRESS_NOALLOC_MAX_DOUBLES (e.g. more than 43690 hex8) is
+ * refused with FEMX_ERR_UNSUPPORTED and a message naming both numbers.  All calls on a device share the one array, which
+ * keeps the previous call's contents (every slot read is written first within the call, so nothing needs clearing);
+ * calls that overlap on the GPU -- two contexts or streams of one device running concurrently -- race: serialise them. */
+#define FEMX_STRESS_NOALLOC_MAX_DOUBLES 2097152
+int femx_stress_noalloc(femx_ctx *ctx, const double *d_uu_local, double *d_stress_node, int layout);
+int64_t femx_stress_noalloc_max_doubles(void);
 
 /* ---- multi-GPU (one ctx per rank) ----------------------------------- */
 /* rows [row_start,row_end) of the global matrix are owned by this rank: the PETSC_DECIDE
