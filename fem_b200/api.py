@@ -92,12 +92,13 @@ class PinnedArray:
 
 class Femx:
     def __init__(self, device: int = 0, quirks: int = Q_REFERENCE, assembly_variant: int = 0, tile: int = 0, lz: int = 0, dbg: int = 0,
-                 peer_in_kernel: bool = False):
+                 peer_in_kernel: bool = False, host_plan: bool = False):
         self.L = _lib.lib()
         self.h = C.c_void_p()
         opts = _lib.FemxOpts(quirks=quirks, assembly_variant=assembly_variant)
         opts.reserved[0], opts.reserved[1], opts.reserved[2] = tile, lz, dbg     # fused-kernel tile shape / z-chunk (tuning knobs)
         opts.reserved[3] = 1 if peer_in_kernel else 0   # peer exchange: the assembly kernel stores interface rows at their owner itself
+        opts.reserved[4] = 1 if host_plan else 0        # integer pass on the host (plan.cpp: the cross-check of the device pass)
         rc = self.L.femx_create(C.byref(self.h), device, C.byref(opts))
         if rc != 0:
             raise FemxError(f"femx_create failed ({rc}): {self.L.femx_last_error(None).decode()}")

@@ -285,7 +285,30 @@ int femx_build_plan(femx_ctx *c) {
   c->dm = femx::DevMesh(); c->dhex = femx::DevHex(); c->loads = femx::DevLoads();
   c->d_bc_diag = nullptr; c->d_bc_dof = nullptr; c->d_bc_val = nullptr;
   const std::vector<void *> before = c->allocs;
-  int rc = build_plan(c->pdim, c->nels, c->etype.data(), c->eptr.data(), c->eind.data(), c->enlmat.data(),
+  int rc;
+  const bool host_plan = c->opts.reserved[4] == 1;   // plan.cpp / plan_hex.cpp on the host: the cross-check of the device pass (plan_gpu.cu)
+  if (!host_plan) {
+    if ((rc = build_plan_device(c))) return rc;
+    if (c->hex.ok) {
+      // the tile kernels scale gradients by rsqrt(detJ): a mirrored grid or an inverted element (which the reference and the
+      // general kernels assemble as is, src/m_local.F90:61-65) must not reach them
+      int *d_bad = nullptr, bad = 0;
+      if ((rc = dev_alloc(c, &d_bad, 1))) return rc;
+      CK(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+      c->launches += launch_hex_detj(c, d_bad);
+      CK(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      dev_release(c, d_bad);
+      if (bad) { c->hex.ok = false; c->hex.why = "an element with detJ <= 0 (inverted or mirrored numbering)"; }
+    }
+    const int av = c->opts.assembly_variant;
+    if (!c->hex.ok && (av == 12 || av == 13 || av == 20 || av == 21)) {
+      c->err = "fused assembly variant requested but the mesh does not qualify: " + c->hex.why;
+      return FEMX_ERR_UNSUPPORTED;
+    }
+  } else {
+  c->host_bcol = true; c->host_bpos = true;
+  rc = build_plan(c->pdim, c->nels, c->etype.data(), c->eptr.data(), c->eind.data(), c->enlmat.data(),
                       c->nlnds, c->nnds, &c->plan, &c->err);
   if (rc) return rc;
   for (int e = 0; e < c->nels; ++e)
@@ -394,6 +417,7 @@ int femx_build_plan(femx_ctx *c) {
     }
   }
 #undef UP
+  }
   if ((rc = refresh_materials(c))) return rc;
   const int av = c->opts.assembly_variant;
   if ((av == 12 || av == 13 || av == 20 || av == 21) && !c->mat_ok_hex) {
@@ -466,6 +490,7 @@ static int mpiaij_walk(femx_ctx *c, int64_t row_start, int64_t row_end, int64_t 
                        std::vector<int32_t> *garray, int64_t *nd_out, int64_t *no_out) {
   const int pd = c->pdim;
   ARG(row_start >= 0 && row_end >= row_start && row_end <= (int64_t)pd * c->nnds, "bad row range");
+  { int rcb = plan_host_blocks(c); if (rcb) return rcb; }
   const femx::Plan &P = c->plan;
   std::vector<int32_t> &ga = *garray;
   const bool fill = d_col != nullptr;
@@ -529,6 +554,7 @@ int femx_get_slot_map(femx_ctx *c, int64_t *offsets, uint16_t *blockpos) {
   if (!c) return FEMX_ERR_ARG;
   ARG(c->has_plan, "femx_build_plan first");
   if (offsets) memcpy(offsets, c->plan.eb_ptr.data(), sizeof(int64_t) * (c->nels + 1));
+  if (blockpos) { int rcb = plan_host_bpos(c); if (rcb) return rcb; }
   if (blockpos) memcpy(blockpos, c->plan.bpos.data(), sizeof(uint16_t) * c->plan.bpos.size());
   return FEMX_OK;
 }

@@ -187,6 +187,7 @@ struct femx_ctx {
   std::vector<double> coords, E_nu, cohprops, bcval;
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
+  bool host_bcol = true, host_bpos = true;   // plan.bcol / plan.bpos are present on the host (device plan: fetched on demand, plan_gpu.cu)
   bool mat_ok_simplex = false, mat_ok_hex = false;   // the CURRENT materials admit the simplex rows / hex8 tile kernels (mu > 0, one Poisson ratio)
   std::string mat_why;                                // why not
   int own_nranks = 1, own_rank = 0;            // femx_set_ownership (PETSC_DECIDE row split of this rank)

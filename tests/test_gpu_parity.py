@@ -128,6 +128,54 @@ def test_pattern_values_fint_vs_oracle(fx, orc, golden):
         assert np.array_equal(kb[pen], vb_o[pen]) and close(kb[~pen], vb_o[~pen], TOL_MAT, np.abs(va_o).max()), name
 
 
+def test_device_plan_equals_host_plan(golden):
+    """The integer pass on the device (csrc/plan_gpu.cu: radix sorts, label propagation for the hex8 logical grid) against
+    the host pass it replaces (csrc/plan.cpp, plan_hex.cpp; Femx(host_plan=True)): pattern, slot map and -- because every
+    list the kernels read is identical -- the values of every assembly variant and the nodal stress, bit for bit."""
+    cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("hex_permuted", _permuted(mg.jitter(mg.hex_cube(6, clamp=False)), 3)),
+                                     ("hex_box", mg.jitter(mg.hex_block(9, 5, 11))), ("tet_jitter", mg.jitter(mg.tet_cube(5))),
+                                     ("tri_wide", mg.jitter(mg.tri_rect(40, 3))), ("hex_two_islands", _two_islands())]
+    for name, m in cases:
+        u = mg.displacement_field(m)
+        pure = set(np.unique(m.etype))
+        variants = [0, 1, 9] + ([11] if pure <= {fm.TRI, fm.TET} else [])
+        out = {}
+        for host in (True, False):
+            for av in variants:
+                with api.Femx(assembly_variant=av, host_plan=host) as f:
+                    f.set_mesh(m).build_plan()
+                    rp, ci = f.pattern()
+                    off, bpos = f.slot_map()
+                    vals, fint = f.assemble_K_fint(u)
+                    st = f.stress(u) if av == 0 else None
+                    out[host, av] = (rp, ci, off, bpos, vals, fint, st)
+        for av in variants:
+            for x, y in zip(out[True, av], out[False, av]):
+                assert (x is None and y is None) or np.array_equal(x, y), (name, av)
+    # the hex8 tile kernels run on both plans (same logical grid, same row metadata)
+    for name, m in (("hex6_jitter", mg.jitter(mg.hex_cube(6))), ("hex_permuted", _permuted(mg.jitter(mg.hex_cube(6, clamp=False)), 3)), ("l_shaped_hex", _l_shaped(6))):
+        u = mg.displacement_field(m)
+        for av in (12, 20):
+            res = []
+            for host in (True, False):
+                with api.Femx(assembly_variant=av, host_plan=host) as f:
+                    f.set_mesh(m).build_plan()
+                    res.append(f.assemble_K_fint(u))
+            assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (name, av)
+
+
+def _two_islands():
+    """Two disconnected hex8 blocks in one mesh: the logical-grid pass has to place the second component beside the first."""
+    a, b = mg.jitter(mg.hex_block(3, 2, 2)), mg.jitter(mg.hex_block(2, 3, 2))
+    nn = a.nnds
+    eind = np.concatenate([a.eind, b.eind + nn]).astype(np.int32)
+    eptr = np.concatenate([a.eptr, b.eptr[1:] + a.eptr[-1]]).astype(np.int32)
+    coords = np.concatenate([a.coords, b.coords + np.array([10.0, 0.0, 0.0])])
+    return dataclasses.replace(a, nnds=nn + b.nnds, eptr=eptr, eind=eind, etype=np.concatenate([a.etype, b.etype]),
+                               emat=np.concatenate([a.emat, b.emat]), enlmat=np.concatenate([a.enlmat, b.enlmat]), coords=coords,
+                               nl2g=np.arange(1, nn + b.nnds + 1, dtype=np.int32), bcnode=np.zeros((0, 4), np.int32), bcval=np.zeros((0, 3)))
+
+
 def test_fused_rows_variant_vs_two_pass_and_oracle(orc, golden):
     """Variant 9 (fused rows kernel: element row blocks stay in shared memory) against variant 1 (two-pass through
     the packed Ke scratch) and the oracle, on every element mix incl. cohesive zeros and an unstructured hex mesh."""
