@@ -398,7 +398,7 @@ def main():
                            "elements_per_gpu": m.nels, "dof_per_gpu": int(m.pdim * m.nlnds), "nnz_per_gpu": int(nnz),
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
                            "parallelism": par_txt,
-                           "variant": args.variant, "lz": args.lz, "plan_build_s": round(plan_s, 3), "wall_ms_per_step": wall_ms / args.steps},
+                           "variant": args.variant, "lz": args.lz, "plan_build_s": round(plan_s, 3), "plan_pass_s": round(fx.L.femx_plan_seconds(fx.h), 4), "wall_ms_per_step": wall_ms / args.steps},
                 "gpu_launches": int(launches),
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

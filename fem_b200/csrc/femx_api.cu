@@ -1,4 +1,6 @@
 // femx_api.cu -- the C ABI of include/femx.h.  Plain pointers and sizes in, status codes out.
+#include <chrono>
+
 #include "api_util.h"
 
 static std::string g_create_err;
@@ -117,6 +119,7 @@ int femx_set_async(femx_ctx *c, int on) {
 }
 int64_t femx_launch_count(const femx_ctx *c) { return c ? c->launches : 0; }
 double femx_last_kernel_ms(const femx_ctx *c) { return c ? c->last_ms : 0.0; }
+double femx_plan_seconds(const femx_ctx *c) { return c ? c->plan_seconds : 0.0; }
 
 // --------------------------------------------------------------------------- state
 int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *eptr, const int *eind,
@@ -272,6 +275,7 @@ int femx_build_plan(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;
   ARG(c->has_mesh, "femx_set_mesh first");
   CK(cudaSetDevice(c->device));
+  const auto t_plan0 = std::chrono::steady_clock::now();
   // a second plan on the same ctx: the previous plan's device arrays go first (hundreds of MB at 1 M hex8)
   c->has_plan = false;
   CK(cudaStreamSynchronize(c->stream));
@@ -430,6 +434,7 @@ int femx_build_plan(femx_ctx *c) {
     if (std::find(before.begin(), before.end(), q) == before.end()) c->plan_allocs.push_back(q);
   if (rc) return rc;
   c->has_plan = true;
+  c->plan_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_plan0).count();
   return FEMX_OK;
 }
 
@@ -553,8 +558,8 @@ int femx_get_pattern_mpiaij(femx_ctx *c, int64_t row_start, int64_t row_end, int
 int femx_get_slot_map(femx_ctx *c, int64_t *offsets, uint16_t *blockpos) {
   if (!c) return FEMX_ERR_ARG;
   ARG(c->has_plan, "femx_build_plan first");
+  { int rcb = plan_host_bpos(c); if (rcb) return rcb; }
   if (offsets) memcpy(offsets, c->plan.eb_ptr.data(), sizeof(int64_t) * (c->nels + 1));
-  if (blockpos) { int rcb = plan_host_bpos(c); if (rcb) return rcb; }
   if (blockpos) memcpy(blockpos, c->plan.bpos.data(), sizeof(uint16_t) * c->plan.bpos.size());
   return FEMX_OK;
 }

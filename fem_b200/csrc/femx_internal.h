@@ -181,12 +181,14 @@ struct femx_ctx {
   std::string err;
   int64_t launches = 0;
   double last_ms = 0.0;
+  double plan_seconds = 0.0;          // wall time of the last femx_build_plan
   // host copies
   int pdim = 0, nels = 0, nlnds = 0, nnds = 0, nmts = 0, ncoh = 0, nbcs = 0;
   std::vector<int32_t> etype, eptr, eind, emat, enlmat, nl2g;
   std::vector<double> coords, E_nu, cohprops, bcval;
   std::vector<int32_t> bcnode;
   bool has_mesh = false, has_plan = false;
+  int64_t plan_npairs = 0;             // sum over elements of nen^2 (device plan; the host plan keeps eb_ptr)
   bool host_bcol = true, host_bpos = true;   // plan.bcol / plan.bpos are present on the host (device plan: fetched on demand, plan_gpu.cu)
   bool mat_ok_simplex = false, mat_ok_hex = false;   // the CURRENT materials admit the simplex rows / hex8 tile kernels (mu > 0, one Poisson ratio)
   std::string mat_why;                                // why not

@@ -19,8 +19,11 @@
 //     metadata.
 // CUB (radix sort, scan, select) does the heavy lifting: this pass is not the hot path.
 #include <cub/cub.cuh>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
 
 #include <chrono>
+#include <cstdlib>
 
 #include "api_util.h"
 
@@ -39,25 +42,55 @@ namespace {
     }                                                                                                          \
   } while (0)
 
-struct Scratch {   // untracked temporaries of the pass
-  std::vector<void *> p;
-  template <class T> cudaError_t get(T **q, size_t n) {
-    void *v = nullptr;
-    cudaError_t e = cudaMalloc(&v, sizeof(T) * (n ? n : 1));
-    if (e == cudaSuccess) p.push_back(v);
-    *q = (T *)v;
-    return e;
+struct Arena {   // the pass's temporaries: one allocation, bump pointer, freed when the pass returns
+  char *base = nullptr;
+  size_t cap = 0, used = 0;
+  cudaError_t reserve(size_t bytes) { cap = bytes; return cudaMalloc((void **)&base, bytes); }
+  template <class T> T *take(size_t n) {
+    const size_t b = (sizeof(T) * (n ? n : 1) + 255) & ~(size_t)255;
+    if (used + b > cap) return nullptr;
+    T *q = (T *)(base + used);
+    used += b;
+    return q;
   }
-  void drop(void *q) {
-    auto it = std::find(p.begin(), p.end(), q);
-    if (it != p.end()) { cudaFree(q); p.erase(it); }
-  }
-  ~Scratch() { for (void *q : p) cudaFree(q); }
+  ~Arena() { if (base) cudaFree(base); }
 };
+#define TAKE(ptr, T, n)                                                        \
+  do {                                                                         \
+    ptr = A.take<T>(n);                                                        \
+    if (!ptr) { c->err = "plan scratch arena exhausted"; return FEMX_ERR_ALLOC; } \
+  } while (0)
 
 constexpr int BS = 256;
 inline int grid_for(int64_t n) { return (int)((n + BS - 1) / BS); }
 inline int bits_for(int64_t n) { int b = 1; while ((1ll << b) < n) ++b; return b; }
+
+// ---------------------------------------------------------------------------------------------- element table
+struct Nen2 { __host__ __device__ int64_t operator()(int t) const { const int n = type_nen(t); return (int64_t)n * n; } };
+struct Nen2D { int d2; __host__ __device__ int64_t operator()(int t) const { const int n = type_nen(t); return (int64_t)n * n * d2; } };
+struct NenD { int d; __host__ __device__ int64_t operator()(int t) const { return (int64_t)type_nen(t) * d; } };
+struct TypeIs { const int32_t *etype; int t; __device__ bool operator()(int e) const { return etype[e] == t; } };
+struct IsNonlinear { const int32_t *enlmat; __device__ bool operator()(int e) const { return enlmat[e] != 0; } };
+// flags[0] bit 3: nlMat != 0 on a non-cohesive element, bit 4: material id out of range, bit 5: a non-simplex element;
+// flags[8 + t]: elements of type t; flags[6]: elements with nlMat != 0; flags[7]: largest element node count
+__global__ void elem_table_kernel(int nels, int nmts, const int32_t *__restrict__ etype, const int32_t *__restrict__ emat, const int32_t *__restrict__ enlmat,
+                                  int *__restrict__ flags) {
+  __shared__ int cnt[8];
+  if (threadIdx.x < 8) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nels) {
+    const int t = etype[e];
+    int bits = 0;
+    if (enlmat[e] != 0) { atomicAdd(&cnt[6], 1); if (t != FEMX_COH) bits |= 8; }
+    if (t != FEMX_COH && !(emat[e] >= 1 && emat[e] <= nmts)) bits |= 16;
+    if (t != FEMX_TRI && t != FEMX_TET) bits |= 32;
+    if (bits) atomicOr(&flags[0], bits);
+    atomicAdd(&cnt[t], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x >= 1 && threadIdx.x <= 6 && cnt[threadIdx.x]) atomicAdd(&flags[threadIdx.x == 6 ? 6 : 8 + threadIdx.x], cnt[threadIdx.x]);
+}
 
 // ---------------------------------------------------------------------------------------------- incidence
 // conn0 (0-based local nodes), sort keys (node) and payload (position in the connectivity), element of every position
@@ -235,22 +268,25 @@ __global__ void hex_sweep_kernel(int nels, const int32_t *__restrict__ conn0, in
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= nels) return;
   const int32_t *cn = conn0 + 8 * (size_t)e;
+  volatile int32_t *vn = nc;
   int x = ec[3 * (size_t)e], y = ec[3 * (size_t)e + 1], z = ec[3 * (size_t)e + 2];
-  bool fresh = false;
-  if (x == UNSET) {
+  if (x != UNSET && (y == UNSET || z == UNSET)) x = UNSET;
+  const bool was_set = x != UNSET;
+  // an unlabelled element polls its nodes a few times per launch: labels written by CTAs running at the same time travel
+  // several elements per sweep (how far is timing-dependent, the fixed point is not)
+  for (int rep = 0; rep < 8 && x == UNSET; ++rep)
     for (int a = 0; a < 8; ++a) {
       const int r = cn[a];
-      const int nx = ((volatile int32_t *)nc)[3 * (size_t)r], ny = ((volatile int32_t *)nc)[3 * (size_t)r + 1], nz = ((volatile int32_t *)nc)[3 * (size_t)r + 2];
-      if (nx != UNSET && ny != UNSET && nz != UNSET) { x = nx - kSx[a]; y = ny - kSy[a]; z = nz - kSz[a]; fresh = true; break; }
+      const int nx = vn[3 * (size_t)r], ny = vn[3 * (size_t)r + 1], nz = vn[3 * (size_t)r + 2];
+      if (nx != UNSET && ny != UNSET && nz != UNSET) { x = nx - kSx[a]; y = ny - kSy[a]; z = nz - kSz[a]; break; }
     }
-    if (!fresh) return;
-    ec[3 * (size_t)e + 1] = y; ec[3 * (size_t)e + 2] = z; ec[3 * (size_t)e] = x;
-  }
-  bool any = fresh;
+  if (x == UNSET) return;
+  bool any = !was_set;
+  if (!was_set) { ec[3 * (size_t)e + 1] = y; ec[3 * (size_t)e + 2] = z; ec[3 * (size_t)e] = x; }
   for (int b = 0; b < 8; ++b) {
     const int r = cn[b];
-    if (((volatile int32_t *)nc)[3 * (size_t)r] == UNSET || ((volatile int32_t *)nc)[3 * (size_t)r + 1] == UNSET || ((volatile int32_t *)nc)[3 * (size_t)r + 2] == UNSET) {
-      nc[3 * (size_t)r + 1] = y + kSy[b]; nc[3 * (size_t)r + 2] = z + kSz[b]; nc[3 * (size_t)r] = x + kSx[b];
+    if (vn[3 * (size_t)r] == UNSET || vn[3 * (size_t)r + 1] == UNSET || vn[3 * (size_t)r + 2] == UNSET) {
+      vn[3 * (size_t)r + 1] = y + kSy[b]; vn[3 * (size_t)r + 2] = z + kSz[b]; vn[3 * (size_t)r] = x + kSx[b];
       any = true;
     }
   }
@@ -350,18 +386,16 @@ template <class T>
 int tracked(femx_ctx *c, T **p, int64_t n) { return dev_alloc(c, p, n); }
 
 // the hex8 logical-grid plan (plan_hex.cpp on the device).  Leaves c->hex.ok / why and c->dhex.
-int hex_plan_device(femx_ctx *c, cudaStream_t st) {
+int hex_plan_device(femx_ctx *c, cudaStream_t st, Arena &A, bool all_hex) {
   HexPlan &H = c->hex;
   DevMesh &dm = c->dm;
   H = HexPlan();
   const int nels = c->nels, nn = c->nlnds;
   if (c->pdim != 3 || nels == 0) { H.why = "not a 3-D mesh"; return FEMX_OK; }
-  for (int e = 0; e < nels; ++e)
-    if (c->etype[e] != FEMX_HEX) { H.why = "mesh holds non-hex8 elements"; return FEMX_OK; }
-  Scratch S;
+  if (!all_hex) { H.why = "mesh holds non-hex8 elements"; return FEMX_OK; }
   int32_t *ec = nullptr, *nc = nullptr;
   int *d_out = nullptr;
-  PCK(S.get(&ec, 3 * (size_t)nels)); PCK(S.get(&nc, 3 * (size_t)nn)); PCK(S.get(&d_out, 16));
+  TAKE(ec, int32_t, 3 * (size_t)nels); TAKE(nc, int32_t, 3 * (size_t)nn); TAKE(d_out, int, 16);
   fill_i32_kernel<<<grid_for(3 * (int64_t)nels), BS, 0, st>>>(3 * (int64_t)nels, ec, UNSET);
   fill_i32_kernel<<<grid_for(3 * (int64_t)nn), BS, 0, st>>>(3 * (int64_t)nn, nc, UNSET);
   int h_out[16];
@@ -372,8 +406,8 @@ int hex_plan_device(femx_ctx *c, cudaStream_t st) {
     hex_seed_kernel<<<1, 1, 0, st>>>(seed, offset, dm.conn0, ec);
     for (int64_t sweeps = 0;;) {
       PCK(cudaMemsetAsync(d_out, 0, sizeof(int), st));
-      for (int s = 0; s < 16; ++s) hex_sweep_kernel<<<grid_for(nels), BS, 0, st>>>(nels, dm.conn0, ec, nc, d_out);
-      sweeps += 16;
+      for (int s = 0; s < 8; ++s) hex_sweep_kernel<<<grid_for(nels), BS, 0, st>>>(nels, dm.conn0, ec, nc, d_out);
+      sweeps += 8;
       PCK(cudaMemcpyAsync(h_out, d_out, sizeof(int), cudaMemcpyDeviceToHost, st));
       PCK(cudaStreamSynchronize(st));
       if (!h_out[0]) break;
@@ -425,115 +459,146 @@ int hex_plan_device(femx_ctx *c, cudaStream_t st) {
 }  // namespace
 
 // Everything femx_build_plan derives from the connectivity, on the device.  Fills c->dm (mesh + plan arrays), c->plan's
-// scalars and small host arrays (bptr, bdiag, offsets, cohesive overlay), c->buckets, c->hex / c->dhex.  The large host
-// arrays (bcol, bpos) are fetched on demand by plan_host_blocks / plan_host_bpos.
+// scalars and small host arrays (bptr, bdiag, cohesive overlay), c->buckets, c->hex / c->dhex.  The large host arrays
+// (bcol, bpos, eb_ptr) are fetched on demand by plan_host_blocks / plan_host_bpos.
 int build_plan_device(femx_ctx *c) {
   const auto t0 = std::chrono::steady_clock::now();
   cudaStream_t st = c->stream;
+  const bool timing = getenv("FEMX_PLAN_TIMING") != nullptr;   // stage times to stderr (synchronises between stages)
+  auto tprev = t0;
+  auto stage = [&](const char *name) {
+    if (!timing) return;
+    cudaStreamSynchronize(st);
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "femx plan: %-28s %8.3f ms\n", name, std::chrono::duration<double, std::milli>(now - tprev).count());
+    tprev = now;
+  };
   Plan &P = c->plan;
   P = Plan();
-  const int pdim = c->pdim, nels = c->nels, nlnds = c->nlnds;
+  const int pdim = c->pdim, nels = c->nels, nlnds = c->nlnds, d2 = pdim * pdim;
   P.pdim = pdim; P.nels = nels; P.nlnds = nlnds; P.nnds = c->nnds;
   const int64_t nconn = c->eptr[nels];
-  // element table checks and packed offsets (O(nels), host)
-  P.eb_ptr.assign(nels + 1, 0); P.ke_off.assign(nels + 1, 0); P.fe_off.assign(nels + 1, 0);
-  bool simplex = nels > 0;
-  int maxnen = 3;
-  for (int e = 0; e < nels; ++e) {
-    const int t = c->etype[e];
-    if (t < FEMX_TRI || t > FEMX_COH) { c->err = "unknown element type code"; return FEMX_ERR_ARG; }
-    const int nen = type_nen(t);
-    if (c->eptr[e + 1] - c->eptr[e] != nen) { c->err = "eptr does not match the element type's node count"; return FEMX_ERR_ARG; }
-    if (type_dim(t) != pdim) { c->err = "element type dimension differs from pdim"; return FEMX_ERR_ARG; }
-    P.eb_ptr[e + 1] = P.eb_ptr[e] + nen * nen;
-    P.ke_off[e + 1] = P.ke_off[e] + (int64_t)nen * nen * pdim * pdim;
-    P.fe_off[e + 1] = P.fe_off[e] + nen * pdim;
-    simplex = simplex && (t == FEMX_TRI || t == FEMX_TET);
-    maxnen = std::max(maxnen, nen);
-  }
-  P.coh_elems.clear();
-  for (int e = 0; e < nels; ++e)
-    if (c->enlmat[e] != 0) {
-      if (c->etype[e] != FEMX_COH) { c->err = "nlMat != 0 on a non-cohesive element"; return FEMX_ERR_UNSUPPORTED; }
-      P.coh_elems.push_back(e);
-    }
-  for (int e = 0; e < nels; ++e)
-    if (c->etype[e] != FEMX_COH && !(c->emat[e] >= 1 && c->emat[e] <= c->nmts)) { c->err = "element material id out of range (femx_set_materials first)"; return FEMX_ERR_ARG; }
-  const int64_t npairs = P.eb_ptr[nels];
+  // femx_set_mesh has validated type codes, node counts, dimensions and node ids; what depends on later calls (materials,
+  // nlMat) is checked below on the device
+  const int64_t npairs_max = (int64_t)kMaxNen * nconn;
   DevMesh &dm = c->dm;
   dm.pdim = pdim; dm.nels = nels; dm.nlnds = nlnds; dm.nnds = c->nnds; dm.cp = pdim == 2 ? 3 : 6;
   int rc;
+  Arena A;
+  {
+    const size_t bytes = 24 * (size_t)nconn + 16 * (size_t)npairs_max + 12 * ((size_t)nels + nlnds) + 16 * ((size_t)nlnds + 1) + 24 * ((size_t)nels + 1) +
+                         ((size_t)96 << 20);
+    cudaError_t e = A.reserve(bytes);
+    if (e != cudaSuccess) { c->err = std::string("cudaMalloc (plan scratch) failed: ") + cudaGetErrorString(e); return FEMX_ERR_ALLOC; }
+  }
 #define UP(dst, src) if ((rc = upload(c, &dst, src))) return rc
-  UP(dm.etype, c->etype); UP(dm.eptr, c->eptr); UP(dm.emat, c->emat); UP(dm.enlmat, c->enlmat);
-  UP(dm.nl2g, c->nl2g); UP(dm.coords, c->coords);
-  UP(dm.eb_ptr, P.eb_ptr); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
-  Scratch S;
+  UP(dm.eptr, c->eptr); UP(dm.emat, c->emat); UP(dm.enlmat, c->enlmat); UP(dm.nl2g, c->nl2g); UP(dm.coords, c->coords);
+  if ((rc = tracked(c, &dm.etype, (int64_t)nels + 1))) return rc;   // one readable sentinel behind the last element (scan inputs)
+  PCK(cudaMemsetAsync(dm.etype + nels, 0, sizeof(int32_t), st));
+  if (nels) PCK(cudaMemcpyAsync(dm.etype, c->etype.data(), sizeof(int32_t) * (size_t)nels, cudaMemcpyHostToDevice, st));
   int32_t *d_eind = nullptr, *posel = nullptr;
   uint32_t *key = nullptr, *pos = nullptr, *key2 = nullptr, *pos2 = nullptr;
   int *d_flags = nullptr;
-  PCK(S.get(&d_eind, (size_t)nconn)); PCK(S.get(&posel, (size_t)nconn));
-  PCK(S.get(&key, (size_t)nconn)); PCK(S.get(&pos, (size_t)nconn)); PCK(S.get(&key2, (size_t)nconn)); PCK(S.get(&pos2, (size_t)nconn));
-  PCK(S.get(&d_flags, 8));
-  PCK(cudaMemsetAsync(d_flags, 0, 8 * sizeof(int), st));
+  void *cubtmp = nullptr;
+  const size_t cubtmp_bytes = (size_t)64 << 20;   // CUB temporaries (histograms, tile states): O(tiles), far below this
+  TAKE(d_eind, int32_t, nconn); TAKE(posel, int32_t, nconn);
+  TAKE(key, uint32_t, nconn); TAKE(pos, uint32_t, nconn); TAKE(key2, uint32_t, nconn); TAKE(pos2, uint32_t, nconn);
+  TAKE(d_flags, int, 32); TAKE(cubtmp, char, cubtmp_bytes);
+  PCK(cudaMemsetAsync(d_flags, 0, 32 * sizeof(int), st));
   if (nconn) PCK(cudaMemcpyAsync(d_eind, c->eind.data(), sizeof(int32_t) * (size_t)nconn, cudaMemcpyHostToDevice, st));
+  stage("mesh uploads");
+  // ---- element table: packed offsets (scans over the type codes), type counts, checks
+  if ((rc = tracked(c, &dm.eb_ptr, (int64_t)nels + 1)) || (rc = tracked(c, &dm.ke_off, (int64_t)nels + 1)) || (rc = tracked(c, &dm.fe_off, (int64_t)nels + 1))) return rc;
+  if (nels) elem_table_kernel<<<grid_for(nels), BS, 0, st>>>(nels, c->nmts, dm.etype, dm.emat, dm.enlmat, d_flags);
+  {
+    auto scan = [&](auto op, int64_t *out) -> cudaError_t {
+      auto in = thrust::make_transform_iterator((const int32_t *)dm.etype, op);
+      size_t tb = 0;
+      cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, tb, in, out, nels + 1, st);
+      if (e != cudaSuccess) return e;
+      if (tb > cubtmp_bytes) return cudaErrorMemoryAllocation;
+      return cub::DeviceScan::ExclusiveSum(cubtmp, tb, in, out, nels + 1, st);
+    };
+    PCK(scan(Nen2{}, dm.eb_ptr)); PCK(scan(Nen2D{d2}, dm.ke_off)); PCK(scan(NenD{pdim}, dm.fe_off));
+  }
+  int h_flags[32];
+  int64_t tot[3] = {0, 0, 0};
+  PCK(cudaMemcpyAsync(h_flags, d_flags, sizeof(h_flags), cudaMemcpyDeviceToHost, st));
+  PCK(cudaMemcpyAsync(&tot[0], dm.eb_ptr + nels, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  PCK(cudaMemcpyAsync(&tot[1], dm.ke_off + nels, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  PCK(cudaMemcpyAsync(&tot[2], dm.fe_off + nels, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  PCK(cudaStreamSynchronize(st));
+  if (h_flags[0] & 8) { c->err = "nlMat != 0 on a non-cohesive element"; return FEMX_ERR_UNSUPPORTED; }
+  if (h_flags[0] & 16) { c->err = "element material id out of range (femx_set_materials first)"; return FEMX_ERR_ARG; }
+  const int64_t npairs = tot[0];
+  P.eb_ptr.clear();                       // fetched with bpos (plan_host_bpos)
+  P.ke_off.assign(nels + 1, 0); P.fe_off.assign(nels + 1, 0);   // only the totals are read on the host
+  P.ke_off[nels] = tot[1]; P.fe_off[nels] = tot[2];
+  c->plan_npairs = npairs;
+  const bool simplex = nels > 0 && !(h_flags[0] & 32);
+  const int ncoh = h_flags[6];
+  int maxnen = 3;
+  for (int t = FEMX_TRI; t <= FEMX_COH; ++t) if (h_flags[8 + t]) maxnen = std::max(maxnen, type_nen(t));
+  stage("element table");
   if ((rc = tracked(c, &dm.conn0, nconn)) || (rc = tracked(c, &dm.n2e_ptr, (int64_t)nlnds + 1)) || (rc = tracked(c, &dm.n2e_elem, nconn)) ||
       (rc = tracked(c, &dm.n2e_a, nconn)))
     return rc;
   // ---- incidence
-  if (nels) conn_kernel<<<grid_for(nels), BS, 0, st>>>(nels, dm.eptr, d_eind, nlnds, dm.conn0, key, pos, posel, d_flags);
+  if (nels) conn_kernel<<<grid_for(nels), BS, 0, st>>>(nels, dm.eptr, d_eind, nlnds, dm.conn0, key, pos, posel, d_flags + 16);
   {
+    cub::DoubleBuffer<uint32_t> dk(key, key2), dv(pos, pos2);
     size_t tb = 0;
-    PCK(cub::DeviceRadixSort::SortPairs(nullptr, tb, key, key2, pos, pos2, nconn, 0, bits_for(std::max(nlnds, 2)), st));
-    void *tmp = nullptr;
-    PCK(S.get((char **)&tmp, tb));
-    PCK(cub::DeviceRadixSort::SortPairs(tmp, tb, key, key2, pos, pos2, nconn, 0, bits_for(std::max(nlnds, 2)), st));
-    lower_bound_u32_kernel<<<grid_for((int64_t)nlnds + 1), BS, 0, st>>>(nlnds, key2, nconn, dm.n2e_ptr);
-    if (nconn) n2e_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, pos2, posel, dm.eptr, dm.n2e_elem, dm.n2e_a);
-    PCK(cudaStreamSynchronize(st));
-    S.drop(tmp); S.drop(key); S.drop(pos); S.drop(key2); S.drop(pos2); S.drop(d_eind);
+    PCK(cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, nconn, 0, bits_for(std::max(nlnds, 2)), st));
+    if (tb > cubtmp_bytes) { c->err = "CUB temporary storage exceeds the plan arena"; return FEMX_ERR_ALLOC; }
+    PCK(cub::DeviceRadixSort::SortPairs(cubtmp, tb, dk, dv, nconn, 0, bits_for(std::max(nlnds, 2)), st));
+    lower_bound_u32_kernel<<<grid_for((int64_t)nlnds + 1), BS, 0, st>>>(nlnds, dk.Current(), nconn, dm.n2e_ptr);
+    if (nconn) n2e_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, dv.Current(), posel, dm.eptr, dm.n2e_elem, dm.n2e_a);
   }
+  stage("incidence (sort by node)");
   // ---- block rows
   if ((rc = tracked(c, &dm.bptr, (int64_t)nlnds + 1))) return rc;
   int64_t nblk = 0;
   {
     uint64_t *pk = nullptr, *pk2 = nullptr;
     int64_t *d_nsel = nullptr;
-    PCK(S.get(&pk, (size_t)npairs)); PCK(S.get(&pk2, (size_t)npairs)); PCK(S.get(&d_nsel, 1));
+    TAKE(pk, uint64_t, npairs); TAKE(pk2, uint64_t, npairs); TAKE(d_nsel, int64_t, 1);
     if (nconn) pair_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, posel, dm.eptr, dm.eb_ptr, dm.conn0, pk);
     const int endbit = 32 + bits_for(std::max(nlnds, 2));
+    cub::DoubleBuffer<uint64_t> dk(pk, pk2);
     size_t tb = 0, tb2 = 0;
-    PCK(cub::DeviceRadixSort::SortKeys(nullptr, tb, pk, pk2, npairs, 0, endbit, st));
-    PCK(cub::DeviceSelect::Unique(nullptr, tb2, pk2, pk, d_nsel, npairs, st));
-    void *tmp = nullptr;
-    PCK(S.get((char **)&tmp, std::max(tb, tb2)));
-    PCK(cub::DeviceRadixSort::SortKeys(tmp, tb, pk, pk2, npairs, 0, endbit, st));
-    PCK(cub::DeviceSelect::Unique(tmp, tb2, pk2, pk, d_nsel, npairs, st));
+    PCK(cub::DeviceRadixSort::SortKeys(nullptr, tb, dk, npairs, 0, endbit, st));
+    PCK(cub::DeviceSelect::Unique(nullptr, tb2, pk, pk2, d_nsel, npairs, st));
+    if (std::max(tb, tb2) > cubtmp_bytes) { c->err = "CUB temporary storage exceeds the plan arena"; return FEMX_ERR_ALLOC; }
+    PCK(cub::DeviceRadixSort::SortKeys(cubtmp, tb, dk, npairs, 0, endbit, st));
+    uint64_t *sorted = dk.Current(), *uniq = dk.Alternate();
+    PCK(cub::DeviceSelect::Unique(cubtmp, tb2, sorted, uniq, d_nsel, npairs, st));
     PCK(cudaMemcpyAsync(&nblk, d_nsel, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     PCK(cudaStreamSynchronize(st));
     if ((rc = tracked(c, &dm.bcol, nblk))) return rc;
-    if (nblk) bcol_kernel<<<grid_for(nblk), BS, 0, st>>>(nblk, pk, dm.bcol);
-    bptr_kernel<<<grid_for((int64_t)nlnds + 1), BS, 0, st>>>(nlnds, pk, nblk, dm.bptr);
-    PCK(cudaStreamSynchronize(st));
-    S.drop(tmp); S.drop(pk); S.drop(pk2); S.drop(d_nsel);
+    if (nblk) bcol_kernel<<<grid_for(nblk), BS, 0, st>>>(nblk, uniq, dm.bcol);
+    bptr_kernel<<<grid_for((int64_t)nlnds + 1), BS, 0, st>>>(nlnds, uniq, nblk, dm.bptr);
   }
   P.nblk = nblk;
   c->nnz = (int64_t)pdim * pdim * nblk;
+  stage("block rows (sort + unique)");
   // ---- per-node statistics, bdiag, stress multiplicity, list sizes
   int64_t *rbe_cnt = nullptr;
-  PCK(S.get(&rbe_cnt, (size_t)nlnds + 1));
+  TAKE(rbe_cnt, int64_t, (size_t)nlnds + 1);
   PCK(cudaMemsetAsync(rbe_cnt, 0, sizeof(int64_t) * ((size_t)nlnds + 1), st));
   if ((rc = tracked(c, &dm.bdiag, nlnds)) || (rc = tracked(c, &dm.node_count, nlnds)) || (rc = tracked(c, &dm.rbe_ptr, (int64_t)nlnds + 1))) return rc;
   if (nlnds)
     node_stats_kernel<<<grid_for(nlnds), BS, 0, st>>>(nlnds, dm.bptr, dm.bcol, dm.n2e_ptr, dm.n2e_elem, dm.eptr, dm.etype,
-                                                      (c->opts.quirks & FEMX_Q_COH_COUNTS_NODE) ? 1 : 0, dm.bdiag, rbe_cnt, dm.node_count, d_flags + 1);
+                                                      (c->opts.quirks & FEMX_Q_COH_COUNTS_NODE) ? 1 : 0, dm.bdiag, rbe_cnt, dm.node_count, d_flags + 17);
   {
     size_t tb = 0;
     PCK(cub::DeviceScan::ExclusiveSum(nullptr, tb, rbe_cnt, dm.rbe_ptr, nlnds + 1, st));
-    void *tmp = nullptr;
-    PCK(S.get((char **)&tmp, tb));
-    PCK(cub::DeviceScan::ExclusiveSum(tmp, tb, rbe_cnt, dm.rbe_ptr, nlnds + 1, st));
+    if (tb > cubtmp_bytes) { c->err = "CUB temporary storage exceeds the plan arena"; return FEMX_ERR_ALLOC; }
+    PCK(cub::DeviceScan::ExclusiveSum(cubtmp, tb, rbe_cnt, dm.rbe_ptr, nlnds + 1, st));
   }
-  int h_flags[8];
+  // ---- element -> block position (runs while the host fetches bptr / bdiag)
+  if ((rc = tracked(c, &dm.bpos, npairs))) return rc;
+  if (nconn) bpos_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, posel, dm.eptr, dm.eb_ptr, dm.conn0, dm.bptr, dm.bcol, dm.bpos);
+  if (simplex) simplex_detj_kernel<<<grid_for(nels), BS, 0, st>>>(nels, pdim, dm.eptr, dm.conn0, dm.coords, d_flags + 20);
   int64_t nrbe = 0;
   PCK(cudaMemcpyAsync(h_flags, d_flags, sizeof(h_flags), cudaMemcpyDeviceToHost, st));
   PCK(cudaMemcpyAsync(&nrbe, dm.rbe_ptr + nlnds, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
@@ -541,25 +606,16 @@ int build_plan_device(femx_ctx *c) {
   PCK(cudaMemcpyAsync(P.bptr.data(), dm.bptr, sizeof(int64_t) * ((size_t)nlnds + 1), cudaMemcpyDeviceToHost, st));
   if (nlnds) PCK(cudaMemcpyAsync(P.bdiag.data(), dm.bdiag, sizeof(int32_t) * (size_t)nlnds, cudaMemcpyDeviceToHost, st));
   PCK(cudaStreamSynchronize(st));
-  if (h_flags[0] & 1) { c->err = "element node id out of range (expects 1-based local ids)"; return FEMX_ERR_ARG; }
-  if (h_flags[1] > 65535) { c->err = "a node couples to more than 65535 nodes"; return FEMX_ERR_UNSUPPORTED; }
-  P.max_inc = h_flags[2];
-  // ---- element -> block position
-  if ((rc = tracked(c, &dm.bpos, npairs))) return rc;
-  if (nconn) bpos_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, posel, dm.eptr, dm.eb_ptr, dm.conn0, dm.bptr, dm.bcol, dm.bpos);
+  if (h_flags[16] & 1) { c->err = "element node id out of range (expects 1-based local ids)"; return FEMX_ERR_ARG; }
+  if (h_flags[17] > 65535) { c->err = "a node couples to more than 65535 nodes"; return FEMX_ERR_UNSUPPORTED; }
+  P.max_inc = h_flags[18];
+  stage("node statistics, bpos, host bptr");
   // ---- row gather lists of the fused rows kernels
-  const int d2 = pdim * pdim;
   P.rb_foff = maxnen * d2;
   P.rb_slot = P.rb_foff + pdim;
   if (P.rb_slot % 2 == 0) ++P.rb_slot;   // odd pitch: lane-strided 8-byte stores hit distinct banks
-  P.simplex = simplex;
-  if (P.simplex) {   // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians (mu > 0: refresh_materials)
-    simplex_detj_kernel<<<grid_for(nels), BS, 0, st>>>(nels, pdim, dm.eptr, dm.conn0, dm.coords, d_flags + 4);
-    int bad = 0;
-    PCK(cudaMemcpyAsync(&bad, d_flags + 4, sizeof(int), cudaMemcpyDeviceToHost, st));
-    PCK(cudaStreamSynchronize(st));
-    if (bad) P.simplex = false;
-  }
+  // the simplex rows kernel scales gradients by sqrt(w detJ mu): admit only positive Jacobians (mu > 0: refresh_materials)
+  P.simplex = simplex && !h_flags[20];
   const bool lists = P.max_inc <= 32;
   const bool ri = pdim == 2 && P.max_inc >= 1 && P.max_inc <= 32;
   if ((rc = tracked(c, &dm.rb_off, nblk + nlnds)) || (rc = tracked(c, &dm.rb_ent, nrbe)) || (rc = tracked(c, &dm.sx_ent, P.simplex ? nrbe : 0)) ||
@@ -575,32 +631,53 @@ int build_plan_device(femx_ctx *c) {
     }
   } else if (nlnds) {
     row_lists_kernel<<<grid_for(nlnds), BS, 0, st>>>(nlnds, pdim, P.rb_slot, P.simplex ? 1 : 0, dm.bptr, dm.n2e_ptr, dm.n2e_elem, dm.n2e_a, dm.eptr, dm.eb_ptr,
-                                                      dm.bpos, dm.rbe_ptr, dm.rb_off, dm.rb_ent, dm.sx_ent);
+                                                     dm.bpos, dm.rbe_ptr, dm.rb_off, dm.rb_ent, dm.sx_ent);
   }
   if (nconn && ((P.simplex && lists) || ri))
     incidence_records_kernel<<<grid_for(nconn), BS, 0, st>>>(nconn, dm.n2e_elem, dm.n2e_a, dm.eptr, dm.conn0, dm.etype, dm.emat,
                                                              P.simplex && lists ? dm.sx_inc : nullptr, dm.sx_mat, ri ? dm.ri_nodes : nullptr, dm.ri_info);
-  // ---- type buckets (ascending element id)
+  stage("row lists");
+  // ---- type buckets (ascending element id): stream compaction of the element ids per type present
   c->buckets.clear();
-  for (int t = FEMX_TRI; t <= FEMX_COH; ++t) {
-    Bucket b;
-    b.type = t;
-    for (int e = 0; e < nels; ++e)
-      if (c->etype[e] == t) b.h_elem.push_back(e);
-    b.n = (int)b.h_elem.size();
-    if (b.n) { UP(b.d_elem, b.h_elem); c->buckets.push_back(b); }
+  {
+    int32_t *d_all = nullptr;
+    int *d_n = nullptr;
+    if ((rc = tracked(c, &d_all, nels))) return rc;
+    TAKE(d_n, int, 1);
+    int64_t at = 0;
+    for (int t = FEMX_TRI; t <= FEMX_COH; ++t) {
+      const int n = h_flags[8 + t];
+      if (!n) continue;
+      Bucket b;
+      b.type = t; b.n = n; b.d_elem = d_all + at;
+      thrust::counting_iterator<int> ids(0);
+      size_t tb = 0;
+      PCK(cub::DeviceSelect::If(nullptr, tb, ids, b.d_elem, d_n, nels, TypeIs{dm.etype, t}, st));
+      if (tb > cubtmp_bytes) { c->err = "CUB temporary storage exceeds the plan arena"; return FEMX_ERR_ALLOC; }
+      PCK(cub::DeviceSelect::If(cubtmp, tb, ids, b.d_elem, d_n, nels, TypeIs{dm.etype, t}, st));
+      at += n;
+      c->buckets.push_back(b);
+    }
   }
+  stage("type buckets");
   // ---- cohesive overlay (elements with nlMat != 0, src/m_global.F90:130-150, :188-206): O(interface), sorted on the host
   {
-    const int ncoh = (int)P.coh_elems.size();
+    P.coh_elems.assign((size_t)ncoh, 0);
     std::vector<int32_t> rows(4 * (size_t)ncoh);
     std::vector<int64_t> blks(16 * (size_t)ncoh);
-    UP(c->d_coh_elems, P.coh_elems);
+    if ((rc = tracked(c, &c->d_coh_elems, ncoh))) return rc;
     if (ncoh) {
       int32_t *d_rows = nullptr;
       int64_t *d_blk = nullptr;
-      PCK(S.get(&d_rows, rows.size())); PCK(S.get(&d_blk, blks.size()));
+      int *d_n = nullptr;
+      TAKE(d_rows, int32_t, rows.size()); TAKE(d_blk, int64_t, blks.size()); TAKE(d_n, int, 1);
+      thrust::counting_iterator<int> ids(0);
+      size_t tb = 0;
+      PCK(cub::DeviceSelect::If(nullptr, tb, ids, c->d_coh_elems, d_n, nels, IsNonlinear{dm.enlmat}, st));
+      if (tb > cubtmp_bytes) { c->err = "CUB temporary storage exceeds the plan arena"; return FEMX_ERR_ALLOC; }
+      PCK(cub::DeviceSelect::If(cubtmp, tb, ids, c->d_coh_elems, d_n, nels, IsNonlinear{dm.enlmat}, st));
       coh_blocks_kernel<<<grid_for(16 * (int64_t)ncoh), BS, 0, st>>>(ncoh, c->d_coh_elems, dm.eptr, dm.conn0, dm.eb_ptr, dm.bpos, dm.bptr, d_rows, d_blk);
+      PCK(cudaMemcpyAsync(P.coh_elems.data(), c->d_coh_elems, sizeof(int32_t) * (size_t)ncoh, cudaMemcpyDeviceToHost, st));
       PCK(cudaMemcpyAsync(rows.data(), d_rows, sizeof(int32_t) * rows.size(), cudaMemcpyDeviceToHost, st));
       PCK(cudaMemcpyAsync(blks.data(), d_blk, sizeof(int64_t) * blks.size(), cudaMemcpyDeviceToHost, st));
       PCK(cudaStreamSynchronize(st));
@@ -644,14 +721,16 @@ int build_plan_device(femx_ctx *c) {
 #undef UP
   c->nl2g_identity = c->nlnds == c->nnds;
   for (int i = 0; i < c->nlnds && c->nl2g_identity; ++i) c->nl2g_identity = c->nl2g[i] == i + 1;
-  PCK(cudaStreamSynchronize(st));
-  PCK(cudaGetLastError());
+  stage("cohesive overlay");
   // ---- hex8 logical grid
   c->hex = HexPlan();
   const int av = c->opts.assembly_variant;
   if (av != 1 && av != 9 && av != 11) {
-    if ((rc = hex_plan_device(c, st))) return rc;
+    if ((rc = hex_plan_device(c, st, A, h_flags[8 + FEMX_HEX] == nels))) return rc;
   }
+  PCK(cudaStreamSynchronize(st));
+  PCK(cudaGetLastError());
+  stage("hex8 logical grid");
   P.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   c->host_bcol = false; c->host_bpos = false;
   return FEMX_OK;
@@ -667,7 +746,9 @@ int plan_host_blocks(femx_ctx *c) {
 }
 int plan_host_bpos(femx_ctx *c) {
   if (c->host_bpos) return FEMX_OK;
-  const int64_t n = c->plan.eb_ptr[c->nels];
+  const int64_t n = c->plan_npairs;
+  c->plan.eb_ptr.resize((size_t)c->nels + 1);
+  PCK(cudaMemcpy(c->plan.eb_ptr.data(), c->dm.eb_ptr, sizeof(int64_t) * ((size_t)c->nels + 1), cudaMemcpyDeviceToHost));
   c->plan.bpos.resize((size_t)n);
   if (n) PCK(cudaMemcpy(c->plan.bpos.data(), c->dm.bpos, sizeof(uint16_t) * (size_t)n, cudaMemcpyDeviceToHost));
   c->host_bpos = true;

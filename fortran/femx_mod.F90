@@ -322,6 +322,10 @@ module femx
       import :: c_ptr, c_double
       type(c_ptr), value :: ctx
     end function
+    real(c_double) function femx_plan_seconds(ctx) bind(C, name="femx_plan_seconds")
+      import :: c_ptr, c_double
+      type(c_ptr), value :: ctx
+    end function
     integer(c_int) function femx_version() bind(C, name="femx_version")
       import :: c_int
     end function

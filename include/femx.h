@@ -272,6 +272,9 @@ int64_t femx_launch_count(const femx_ctx *ctx);
 /* device time of the last assemble / stress / jacobian call's kernels, CUDA events on the ctx
  * stream, ms (0 if none) */
 double femx_last_kernel_ms(const femx_ctx *ctx);
+/* wall time of the integer pass of the last femx_build_plan (device pass incl. its uploads; the figure the reference
+ * pays inside MatSetValues' sorted inserts, src/main.F90:157-166), seconds */
+double femx_plan_seconds(const femx_ctx *ctx);
 int femx_version(void);
 
 #ifdef __cplusplus
