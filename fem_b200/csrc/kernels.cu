@@ -223,6 +223,115 @@ __global__ void __launch_bounds__(128) mesh_stress_kernel(DevMesh dm, const int3
   }
 }
 
+// hex8 form of mesh_stress_kernel: eight lanes per element.  Lane k first acts as integration point k (CalcElStress,
+// src/m_local.F90:93-123: gradients at the point, strain from the element's displacements, sigma = D eps), then as local
+// node k of the extrapolation (RecoverNodalStress, src/m_global.F90:488-515: sn[k] = sum_j N2inv[k][j] sigma[j], j ascending).
+// The element's coordinates and displacements are gathered once (lane k fetches node k) and shared through shared memory,
+// which then carries the eight stresses; the per-(element, node) results leave as one contiguous 384-byte run per element.
+__device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__global__ void __launch_bounds__(256, 2) hex_stress_ip_kernel(DevMesh dm, const int32_t *__restrict__ elems, int n, const double *__restrict__ uu,
+                                                               double *__restrict__ sn_out) {
+  constexpr int NEN = 8, CP = 6, IP = 9;             // IP: row pitch of the inverse table (8 lanes read 8 rows: distinct banks)
+  constexpr int EP = NEN * 6 + 2;                    // + 2: the four elements of a warp start 4 banks apart (128-bit loads without conflicts)
+  __shared__ __align__(16) double sh[8][2][4][EP];   // [warp][stage][element of the warp][node][x0 x1 x2 u0 u1 u2]
+  __shared__ double inv_s[NEN * IP];
+  if (threadIdx.x < 64) inv_s[(threadIdx.x >> 3) * IP + (threadIdx.x & 7)] = c_n2inv_hex[threadIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, sub = lane >> 3, k = lane & 7;
+  // a block walks a contiguous chunk of the element list, 32 elements per iteration: consecutive iterations touch
+  // neighbouring elements, whose shared nodes are still in L1
+  const int64_t chunk = ((((int64_t)n + gridDim.x - 1) / gridDim.x) + 31) / 32 * 32, stride = 32;
+  const int64_t first = (int64_t)blockIdx.x * chunk + w * 4 + sub;
+  n = (int)min((int64_t)n, ((int64_t)blockIdx.x + 1) * chunk);
+  // the dependent chain element id -> connectivity offset -> node id -> coordinates / displacements is software-pipelined:
+  // every level is fetched one iteration before the next level needs it (the last one by cp.async straight into the other
+  // shared-memory stage), so a warp never waits for a load it just issued
+  auto elem_at = [&](int64_t i) { return i < n ? elems[i] : -1; };
+  auto fetch = [&](int stage, int nd) {   // node nd's coordinates and displacements -> this lane's slot of the stage
+    double *dst = &sh[w][stage][sub][k * 6];
+    if (nd >= 0) {
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { cp_async8(dst + d, dm.coords + (int64_t)nd * 3 + d); cp_async8(dst + 3 + d, uu + (int64_t)nd * 3 + d); }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int e3 = elem_at(first + 3 * stride), e2 = elem_at(first + 2 * stride), e1 = elem_at(first + stride), e0 = elem_at(first);
+  int o2 = e2 >= 0 ? dm.eptr[e2] : 0, o1 = e1 >= 0 ? dm.eptr[e1] : 0, o0 = e0 >= 0 ? dm.eptr[e0] : 0;   // connectivity offsets
+  int nd1 = e1 >= 0 ? dm.conn0[o1 + k] : -1;
+  fetch(0, e0 >= 0 ? dm.conn0[o0 + k] : -1);
+  int it = 0;
+  for (int64_t idx = first; idx - sub < n; idx += stride, ++it) {   // warp-uniform trip count (idx - sub = the warp's first element)
+    const bool on = idx < n;
+    const double *S = &sh[w][it & 1][sub][0];
+    double *Sw = &sh[w][it & 1][sub][0];
+    const int64_t ecur = o0;
+    const int m = on ? dm.emat[e0] - 1 : 0;
+    // next levels (each consumed one iteration from now)
+    fetch((it + 1) & 1, nd1);
+    const int e4 = elem_at(idx + 4 * stride);
+    const int o3 = e3 >= 0 ? dm.eptr[e3] : 0;
+    nd1 = e2 >= 0 ? dm.conn0[o2 + k] : -1;
+    e0 = e1; e1 = e2; e2 = e3; e3 = e4;
+    o0 = o1; o1 = o2; o2 = o3;
+    asm volatile("cp.async.wait_group 1;" ::: "memory");   // this iteration's stage has landed (the next one may be in flight)
+    __syncwarp();
+    const double lam = dm.lam_mu[2 * m], mu = dm.lam_mu[2 * m + 1];
+    double out[CP];
+    {
+      double X[NEN][3];
+#pragma unroll
+      for (int a = 0; a < NEN; ++a)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) X[a][d] = S[a * 6 + d];
+      double g[NEN][3];
+      phys_grad<FEMX_HEX>(X, k, g);
+      double U[NEN][3];
+#pragma unroll
+      for (int a = 0; a < NEN; ++a)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) U[a][d] = S[a * 6 + 3 + d];
+      double H[3][3];  // H[i][j] = du_i/dx_j
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          double t = 0.0;
+#pragma unroll
+          for (int a = 0; a < NEN; ++a) t += U[a][i] * g[a][j];
+          H[i][j] = t;
+        }
+      const double tr = H[0][0] + H[1][1] + H[2][2];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) out[i] = lam * tr + 2.0 * mu * H[i][i];
+      out[3] = mu * (H[0][1] + H[1][0]);  // xy
+      out[4] = mu * (H[1][2] + H[2][1]);  // yz
+      out[5] = mu * (H[2][0] + H[0][2]);  // zx
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < CP; ++c) Sw[k * 6 + c] = out[c];
+    __syncwarp();
+    double sn[CP];
+#pragma unroll
+    for (int c = 0; c < CP; ++c) sn[c] = 0.0;
+#pragma unroll
+    for (int j = 0; j < NEN; ++j) {
+      const double f = inv_s[k * IP + j];
+#pragma unroll
+      for (int c = 0; c < CP; ++c) sn[c] += f * S[j * 6 + c];
+    }
+    if (on) {
+      double *o = sn_out + (ecur + k) * CP;
+#pragma unroll
+      for (int c = 0; c < CP; ++c) o[c] = sn[c];
+    }
+    __syncwarp();   // the stage is rewritten by the fetch of the iteration after next
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 // nodal sum in ascending element order, then the average (src/main.F90:258-279).  One thread per (node, component);
 // the incidence loop runs in batches of four so that the dependent loads (element id -> value) of a batch are in flight
 // together while the adds keep the reference's order.  ONEIP: one stored stress per element, nen nodes per element.
@@ -587,7 +696,7 @@ int launch_mesh_stress(femx_ctx *c, const double *d_uu, double *d_sn, double *d_
         if (oneip) mesh_stress_kernel<FEMX_TET, true><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
         else mesh_stress_kernel<FEMX_TET, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn);
         break;
-      case FEMX_HEX: mesh_stress_kernel<FEMX_HEX, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
+      case FEMX_HEX: hex_stress_ip_kernel<<<std::min(nblocks(b.n, 32), 148 * 2 * 8), 256, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
       case FEMX_COH: mesh_stress_kernel<FEMX_COH, false><<<g, bs, 0, c->stream>>>(c->dm, b.d_elem, b.n, d_uu, d_sn); break;
     }
     ++launches;
