@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfemx.so")
+LIB_PATH = os.environ.get("FEMX_LIB") or os.path.join(_HERE, "libfemx.so")   # FEMX_LIB: a development build of the same library
 _lib = None
 
 c_double_p = C.POINTER(C.c_double)

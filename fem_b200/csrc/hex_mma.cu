@@ -61,7 +61,12 @@ constexpr int ZT = 12, ZC = 6 * ZT;              // z-carry entries per tile / p
 constexpr int XP = UX * 3 + 1;                   // doubles per row of the coordinate layer
 constexpr int PF_ROW = 6;                        // gather warps prefetch the next node layer when they reach this node row
 static_assert(EXC == NMW, "one MMA warp per cell column");
-static_assert(NGW == 8, "register split (setmaxnreg 160 / 96) and the prefetch protocol are validated for 8 gather warps only");
+#ifndef FEMX_MMA_REG_M
+#define FEMX_MMA_REG_M 160
+#define FEMX_MMA_REG_G 96
+#endif
+static_assert(NGW == 8 || FEMX_MMA_REG_M != 160, "register split (setmaxnreg 160 / 96) and the prefetch protocol are validated for 8 gather warps only");
+static_assert(32 * (NMW * FEMX_MMA_REG_M + NGW * FEMX_MMA_REG_G) <= 65536, "register split exceeds the register file");
 static_assert(NYT > PF_ROW + 1 && EYC > RING, "tile too short for the prefetch point / the ring");
 
 // position of entry (row m, column n) of a tile inside its 36-entry block, by the parity P of the cell row's +y nodes
@@ -115,7 +120,10 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *b, unsigned parity
   if (mbar_try(b, parity)) return;
   unsigned n = 0;
   while (!mbar_try(b, parity)) {
-    __nanosleep(40);                     // polling goes through the shared-memory pipe the working warps need
+#ifndef FEMX_MMA_NS
+#define FEMX_MMA_NS 40
+#endif
+    __nanosleep(FEMX_MMA_NS);            // polling goes through the shared-memory pipe the working warps need
     if (++n > (1u << 22)) __trap();
   }
 }
@@ -408,7 +416,7 @@ FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
 
   if (wu >= NMW) {
     // ============================================================================================ gather warps
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");      // the MMA warps take the registers (geometry + accumulators)      // the MMA warps take the registers (geometry + accumulators + pending stores)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FEMX_MMA_REG_G));      // the MMA warps take the registers (geometry + accumulators)      // the MMA warps take the registers (geometry + accumulators + pending stores)
     const int gw = wu - NMW, gt = tid - 32 * NMW;
     if (WITH_F && lane < 3)
       for (int item = gw; item < NP; item += NGW) S.fcarry[item][lane] = 0.0;   // read back by this warp only
@@ -533,7 +541,7 @@ FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
     PROF_FLUSH(8)
   } else {
     // ============================================================================================ MMA warps
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FEMX_MMA_REG_M));
     const int cx = wu;
     MmaLane L;
     L.m = lane >> 2; L.q = lane & 3;
