@@ -50,8 +50,13 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
   // auto (0): the 16-warp symmetric tile kernel with permuted gather lanes (12) for a logical hex8 grid, else the fused rows kernel, else two-pass
   const int av0 = c->opts.assembly_variant;
-  const bool fused = c->hex.ok && c->mat_ok_hex && av0 != 1 && av0 != 9 && av0 != 11;
-  if (!fused && (av0 == 12 || av0 == 13 || av0 == 20 || av0 == 21)) { c->err = "hex8 tile kernel: " + (c->hex.ok ? c->mat_why : c->hex.why); return FEMX_ERR_UNSUPPORTED; }
+  // the hex8 tile kernels address values with 32-bit slots: beyond 2^32 values (34 GB, ~17.5 M hex8 on one GPU) auto uses the general kernels
+  const bool slots32 = c->nnz <= 0xffffffffll;
+  const bool fused = c->hex.ok && c->mat_ok_hex && slots32 && av0 != 1 && av0 != 9 && av0 != 11;
+  if (!fused && (av0 == 12 || av0 == 13 || av0 == 20 || av0 == 21)) {
+    c->err = "hex8 tile kernel: " + (!c->hex.ok ? c->hex.why : !c->mat_ok_hex ? c->mat_why : std::string("more than 2^32 matrix values"));
+    return FEMX_ERR_UNSUPPORTED;
+  }
   const bool simplex = !fused && av0 != 1 && av0 != 9 && c->mat_ok_simplex && rows_simplex_ok(c);   // pure tri3 / tet4 mesh
   const bool rows = !fused && !simplex && av0 != 1 && rows_fused_ok(c);
   if (av0 == 9 && !rows) { c->err = "fused rows kernel: more than 32 elements around a node"; return FEMX_ERR_UNSUPPORTED; }
