@@ -622,7 +622,7 @@ __global__ void gather_sum_kernel(const double *__restrict__ a, int64_t na, cons
 }
 
 // ================================================================= launchers
-static inline int nblocks(int64_t n, int bs) { return (int)((n + bs - 1) / bs); }
+static inline int nblocks(int64_t n, int bs) { return n > 0 ? (int)((n + bs - 1) / bs) : 1; }   // an empty mesh launches one block that finds nothing to do
 
 void set_n2inv(const double *qua16, const double *hex64) {
   cudaMemcpyToSymbol(c_n2inv_qua, qua16, sizeof(double) * 16);

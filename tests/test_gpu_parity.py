@@ -374,6 +374,55 @@ def test_edge_cases(fx):
     assert np.all(fint == 0) and abs(vals.reshape(6, 6).sum()) < 1e-3
 
 
+def _fan(ntri):
+    """ntri triangles around one hub node (more than 32 elements around a node: the row lists do not apply, two-pass path)"""
+    ang = np.linspace(0.0, 2 * np.pi, ntri, endpoint=False)
+    xy = np.concatenate([[[0.0, 0.0]], np.stack([np.cos(ang), np.sin(ang)], 1)])
+    tris = [[1, 2 + i, 2 + (i + 1) % ntri] for i in range(ntri)]
+    return fm.from_uniform(2, fm.TRI, tris, xy)
+
+
+@pytest.mark.parametrize("host_plan", [False, True])
+def test_plan_edge_cases(orc, host_plan):
+    """Empty mesh, a local node no element touches, and a node with more than 32 elements around it, through the device
+    integer pass and the host pass: same pattern, and values against the oracle where there are any."""
+    # no elements, no nodes
+    e = fm.from_uniform(2, fm.TRI, np.zeros((0, 3), np.int32), np.zeros((0, 2)))
+    with api.Femx(host_plan=host_plan) as f:
+        f.set_mesh(e).build_plan()
+        rp, ci = f.pattern()
+        assert f.nnz == 0 and len(ci) == 0 and np.all(rp == 0)
+        assert len(f.assemble_K()) == 0
+    # node 2 of 4 belongs to no element: its rows are empty
+    m = fm.from_uniform(2, fm.TRI, [[1, 3, 4]], np.array([[0, 0], [5, 5], [1, 0], [0, 1.]]))
+    with api.Femx(host_plan=host_plan) as f:
+        f.set_mesh(m).build_plan()
+        rp, ci = f.pattern()
+        assert f.nnz == 36 and rp[2] == rp[3] == rp[4] == 12
+        vals, fint = f.assemble_K_fint(np.zeros(8))
+        om = orc.Mesh(m)
+        rp_o, ci_o, va_o = orc.assemble_K(om).export(om.ndof)
+        assert np.array_equal(rp, rp_o) and np.array_equal(ci, ci_o) and close(vals, va_o, TOL_MAT)
+        s = f.stress(np.zeros(8))
+        assert np.all(s[[0, 2, 3]] == 0) and not np.any(np.isfinite(s[1]))   # 0 / 0: the reference divides by count_node = 0 as well
+    # 40 triangles around the hub
+    fan = _fan(40)
+    u = mg.displacement_field(fan)
+    with api.Femx(host_plan=host_plan) as f:
+        f.set_mesh(fan).build_plan()
+        rp, ci = f.pattern()
+        vals, fint = f.assemble_K_fint(u)
+        om = orc.Mesh(fan)
+        rp_o, ci_o, va_o = orc.assemble_K(om, prealloc=100).export(om.ndof)
+        assert np.array_equal(rp, rp_o) and np.array_equal(ci, ci_o)
+        assert close(vals, va_o, TOL_MAT) and close(fint, orc.fint(om, u.reshape(-1)), TOL_MAT)
+        for av in (9, 11):
+            with api.Femx(assembly_variant=av, host_plan=host_plan) as g:
+                g.set_mesh(fan).build_plan()
+                with pytest.raises(api.FemxError, match="32 elements"):
+                    g.assemble_K()
+
+
 def test_large_mesh_properties(fx):
     """Size-independent properties at a size the oracle cannot finish quickly: rigid-body
     modes give zero internal force, K is symmetric, row sums vanish, stress of a linear
