@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--exchange", choices=("peer", "nccl"), default="peer")
+    ap.add_argument("--partition", choices=("slab", "metis"), default="slab",
+                    help="c3: element partition -- slabs, or METIS_PartMeshNodal called the way src/m_io.F90:137 calls it (rank 0 partitions, epart is broadcast)")
     ap.add_argument("--stress", action="store_true", help="also time the nodal-averaged stress recovery (wall clock per call)")
     args = ap.parse_args()
     rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -47,7 +49,17 @@ def main():
         n = args.edge or 94
         g = mg.jitter(mg.tet_cube(n))
         total, label = g.nels, f"C3 tet4 {n}^3x6, {world} slab(s)"
-        m = fm.localize(g, mg.slab_partition(g, world), rank) if world > 1 else g
+        if world > 1 and args.partition == "metis":
+            ep_t = torch.zeros(g.nels, dtype=torch.int32, device=dev)
+            if rank == 0:
+                tm = time.time()
+                epart, cut = fm.metis_partition(g, world)
+                label = f"C3 tet4 {n}^3x6, METIS_PartMeshNodal into {world} parts (edge cut {cut}, {time.time() - tm:.1f} s on one host core)"
+                ep_t.copy_(torch.from_numpy(epart))
+            dist.broadcast(ep_t, 0)
+            m = fm.localize(g, ep_t.cpu().numpy(), rank)
+        else:
+            m = fm.localize(g, mg.slab_partition(g, world), rank) if world > 1 else g
         del g
     u = mg.displacement_field(m)
     fx = api.Femx(device=lr)
@@ -57,7 +69,7 @@ def main():
     d_f = fx.device_buffer(8 * fx.nrows)
     da = None
     if world > 1:
-        da = par.DistributedAssembly(fx, dist, dev, with_merge=False, peer=args.exchange == "peer")
+        da = par.DistributedAssembly(fx, dist, dev, peer=args.exchange == "peer")
         vals_ptr = C.c_void_p(da.vals_local.data_ptr())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     else:
@@ -108,7 +120,7 @@ def main():
         print(json.dumps({"config": label, "n_gpus": world, "scaling": "strong", "elements": total, "ms_per_step": ms,
                           "wall_ms_per_step": float(tmax[1]) / args.steps, "elements_per_s": total / (ms * 1e-3),
                           "max_elements_per_rank": int(tmax[2]), "nnz_local_sum": int(tsum[3]),
-                          "exchange": ("peer push kernel + step barrier" if da is not None and da.peer else "nccl all_to_all") if world > 1 else "none",
+                          "exchange": ("peer push kernel + neighbours' step barrier + receiver add (inside the timed call)" if da is not None and da.peer else "nccl all_to_all") if world > 1 else "none",
                           "recv_bytes_rank0": int(da.ep.recv_counts.sum()) * 8 if da is not None else 0,
                           "stress_wall_ms_per_call": float(tmax[4]) if args.stress else None,
                           "steps": args.steps, "warmup": args.warmup, "setup_s": round(setup_s, 1)}), flush=True)
