@@ -306,6 +306,38 @@ def distribute_loads(g: Mesh, epart: np.ndarray, nprcs: int, rank: int):
     return fnode, fval, loc, tval[keep] if len(telsd) else tval
 
 
+def renumber_by_partition(g: Mesh, epart: np.ndarray, nparts: int):
+    """Global node numbering that follows an element partition (what a production host does before it creates its PETSc
+    objects; the reference keeps the mesh file's numbering, src/main.F90:57-63, so with a METIS partition most rows a
+    rank assembles belong to other ranks).  A node goes to the lowest part among the elements that touch it; nodes are
+    numbered part by part, old order inside a part.  Returns (mesh with permuted node ids, node_bounds[nparts + 1]):
+    part q holds the new nodes node_bounds[q] + 1 .. node_bounds[q + 1], i.e. the rows pdim * node_bounds[q] ..
+    pdim * node_bounds[q + 1] - 1 -- pass pdim * node_bounds as `row_bounds` to parallel.DistributedAssembly (PETSc:
+    the local sizes of MatCreateAIJ / VecCreateMPI instead of PETSC_DECIDE)."""
+    epart = np.asarray(epart, np.int64)
+    npart = np.full(g.nnds + 1, nparts, np.int64)
+    counts = (g.eptr[1:] - g.eptr[:-1]).astype(np.int64)
+    np.minimum.at(npart, np.asarray(g.eind, np.int64), np.repeat(epart, counts))
+    npart = npart[1:]
+    npart[npart == nparts] = nparts - 1                     # nodes no element touches go last
+    order = np.argsort(npart, kind="stable")                # new position -> old node (0-based)
+    new_of_old = np.empty(g.nnds, np.int64)
+    new_of_old[order] = np.arange(g.nnds)
+    bounds = np.searchsorted(npart[order], np.arange(nparts + 1)).astype(np.int64)
+    relabel = lambda ids: (new_of_old[np.asarray(ids, np.int64) - 1] + 1).astype(np.int32)   # noqa: E731
+    bcnode = np.array(g.bcnode, np.int32).copy()
+    if len(bcnode):
+        bcnode[:, 0] = relabel(bcnode[:, 0])
+        o = np.argsort(bcnode[:, 0], kind="stable")
+        bcnode, bcval = bcnode[o], np.asarray(g.bcval)[o]
+    else:
+        bcval = g.bcval
+    assert np.array_equal(g.nl2g, np.arange(1, g.nnds + 1)), "renumber the global mesh, before localize"
+    g2 = dataclasses.replace(g, eind=relabel(g.eind), coords=np.asarray(g.coords)[order], bcnode=bcnode, bcval=bcval,
+                             fnode=relabel(g.fnode) if len(g.fnode) else g.fnode).normalized()
+    return g2, bounds
+
+
 def petsc_ownership(n: int, nranks: int, rank: int):
     """PETSC_DECIDE row split used by MatCreateAIJ/VecCreateMPI (src/main.F90:137-138,154):
     rank r owns n/P + (r < n mod P) consecutive rows.  Returns [start, end)."""

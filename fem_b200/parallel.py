@@ -69,9 +69,16 @@ def _ranges(starts: np.ndarray, lens: np.ndarray) -> np.ndarray:
     return np.repeat(np.asarray(starts, np.int64) - off, lens) + np.arange(tot, dtype=np.int64)
 
 
-def plan_sends(rowptr: np.ndarray, colidx: np.ndarray, nrows: int, nranks: int, rank: int, nl2g=None, pdim: int = 0) -> ExchangePlan:
-    """Split the rank-local CSR (global row numbering, rows of absent nodes empty) by row owner."""
-    bounds = np.array([petsc_ownership(nrows, nranks, r)[0] for r in range(nranks)] + [nrows], dtype=np.int64)
+def plan_sends(rowptr: np.ndarray, colidx: np.ndarray, nrows: int, nranks: int, rank: int, nl2g=None, pdim: int = 0,
+               row_bounds=None) -> ExchangePlan:
+    """Split the rank-local CSR (global row numbering, rows of absent nodes empty) by row owner.  Owners: the PETSC_DECIDE
+    split (src/main.F90:154), or row_bounds[nranks + 1] when the host chose the local sizes itself (a numbering that
+    follows the partition, mesh.renumber_by_partition)."""
+    if row_bounds is None:
+        bounds = np.array([petsc_ownership(nrows, nranks, r)[0] for r in range(nranks)] + [nrows], dtype=np.int64)
+    else:
+        bounds = np.asarray(row_bounds, np.int64)
+        assert len(bounds) == nranks + 1 and bounds[0] == 0 and bounds[-1] == nrows and np.all(np.diff(bounds) >= 0), "row_bounds"
     lo = rowptr[bounds[:-1]].astype(np.int64)
     hi = rowptr[bounds[1:]].astype(np.int64)
     send_rows, send_cols = [], []
@@ -248,13 +255,13 @@ class DistributedAssembly:
     `vals_local` lives in a torch tensor; femx writes into it through its raw device pointer.
     """
 
-    def __init__(self, fx, dist, device, peer=False):
+    def __init__(self, fx, dist, device, peer=False, row_bounds=None):
         import torch
         self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
         self.rowptr, self.colidx = fx.pattern()
         nranks, rank = dist.get_world_size(), dist.get_rank()
         m = fx.mesh
-        ep = plan_sends(self.rowptr, self.colidx, fx.nrows, nranks, rank, m.nl2g, m.pdim)
+        ep = plan_sends(self.rowptr, self.colidx, fx.nrows, nranks, rank, m.nl2g, m.pdim, row_bounds)
         rr, rcs, rf = exchange_lists(ep, dist, device)
         self._recv_frows = rf
         self.ep = finish_plan(ep, self.rowptr, self.colidx, rr, rcs, rf)
@@ -368,12 +375,12 @@ class LocalRanks:
     kernels run one after another, so assemblies push and signal only and femx_peer_complete finishes every rank once all
     have assembled (a kernel that waited for a peer not yet launched would never finish)."""
 
-    def __init__(self, fxs: list):
+    def __init__(self, fxs: list, row_bounds=None):
         import ctypes as C
         self.fxs, P = fxs, len(fxs)
         self.P = P
         pats = [fx.pattern() for fx in fxs]
-        eps = [plan_sends(pats[r][0], pats[r][1], fxs[r].nrows, P, r, fxs[r].mesh.nl2g, fxs[r].mesh.pdim) for r in range(P)]
+        eps = [plan_sends(pats[r][0], pats[r][1], fxs[r].nrows, P, r, fxs[r].mesh.nl2g, fxs[r].mesh.pdim, row_bounds) for r in range(P)]
         self.eps = [finish_plan(eps[r], pats[r][0], pats[r][1], [eps[s].send_rows[r] for s in range(P)], [eps[s].send_cols[r] for s in range(P)],
                                 [eps[s].send_frows[r] for s in range(P)]) for r in range(P)]
         self.pats = pats

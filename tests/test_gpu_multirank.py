@@ -116,6 +116,48 @@ def test_jacobian_residual_rhs_on_rank_local_meshes(orc, world):
     assert _close(br_sum, br_g, np.abs(br_g).max())
 
 
+@pytest.mark.parametrize("renumber", [False, True])
+def test_local_ranks_on_a_metis_partition(orc, renumber):
+    """METIS_PartMeshNodal (called as src/m_io.F90:137 calls it) into 3 parts, through the device exchange: with the mesh
+    file's numbering and the PETSC_DECIDE split (what the reference does: most rows a rank assembles belong to somebody else),
+    and with the nodes renumbered part by part and the parts' own row ranges (interface rows only)."""
+    world = 3
+    g = _nobc(mg.jitter(mg.tet_cube(6)))
+    try:
+        epart, cut = fm.metis_partition(g, world)
+    except RuntimeError as e:
+        pytest.skip(str(e))
+    row_bounds = None
+    if renumber:
+        g, nb = fm.renumber_by_partition(g, epart, world)
+        row_bounds = g.pdim * nb
+    og = orc.Mesh(g)
+    rp_g, ci_g, va_g = orc.assemble_K(og).export(og.ndof)
+    f_ref = orc.fint(og, mg.displacement_field(g).reshape(-1))
+    fxs, locs = [], []
+    try:
+        for r in range(world):
+            loc = fm.localize(g, epart, r)
+            fx = api.Femx()
+            fx.set_mesh(loc).build_plan()
+            fxs.append(fx); locs.append(loc)
+        lr = par.LocalRanks(fxs, row_bounds)
+        sent = sum(int(ep.recv_counts.sum()) for ep in lr.eps)
+        for rep in range(2):
+            owned, f_tot = lr.assemble_K_fint([mg.displacement_field(loc) for loc in locs])
+            for r, (rp, ci, va) in enumerate(owned):
+                r0, r1 = lr.eps[r].row_start, lr.eps[r].row_end
+                assert np.array_equal(rp, rp_g[r0:r1 + 1] - rp_g[r0]) and np.array_equal(ci, ci_g[rp_g[r0]:rp_g[r1]]), (r, rep)
+                assert _close(va, va_g[rp_g[r0]:rp_g[r1]], np.abs(va_g).max()), (r, rep)
+            assert _close(f_tot, f_ref, np.abs(f_ref).max()), rep
+        if renumber:   # only interface rows cross: a small fraction of the matrix
+            assert all(len(ep.if_rows) < (ep.row_end - ep.row_start) for ep in lr.eps) and sent < 0.5 * len(va_g)
+        lr.close()
+    finally:
+        for fx in fxs:
+            fx.close()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_two_rank_parity_all_exchanges():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",

@@ -27,15 +27,20 @@ def _worker(rank, world, port, kind, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from oracle import pyoracle as orc
-        g = {"hex": lambda: mg.hex_cube(6, clamp=False), "quad": lambda: mg.quad_rect(9, 8), "tet-metis": lambda: mg.tet_cube(5)}[kind]()
+        g = {"hex": lambda: mg.hex_cube(6, clamp=False), "quad": lambda: mg.quad_rect(9, 8), "tet-metis": lambda: mg.tet_cube(5),
+             "tet-metis-renumbered": lambda: mg.tet_cube(5)}[kind]()
         g = mg.jitter(g)
         # "tet-metis": the partition the reference itself would use (METIS_PartMeshNodal, src/m_io.F90:137) -- parts are not
         # contiguous in the node numbering, so most of a rank's rows belong to somebody else
-        epart = fm.metis_partition(g, world)[0] if kind == "tet-metis" else mg.slab_partition(g, world)
+        epart = fm.metis_partition(g, world)[0] if kind.startswith("tet-metis") else mg.slab_partition(g, world)
+        row_bounds = None
+        if kind == "tet-metis-renumbered":   # node numbering follows the partition, local sizes chosen by the host: interface rows only
+            g, nb = fm.renumber_by_partition(g, epart, world)
+            row_bounds = g.pdim * nb
         loc = fm.localize(g, epart, rank)
         om = orc.Mesh(loc)
         rowptr, colidx, vals = orc.assemble_K(om).export(om.ndof)
-        ep = par.plan_sends(rowptr, colidx, om.ndof, world, rank, loc.nl2g, loc.pdim)
+        ep = par.plan_sends(rowptr, colidx, om.ndof, world, rank, loc.nl2g, loc.pdim, row_bounds)
         rr, rc, rf = par.exchange_lists(ep, dist)
         ep = par.finish_plan(ep, rowptr, colidx, rr, rc, rf)
         # value exchange: contiguous slices of the local value array
@@ -62,7 +67,7 @@ def _worker(rank, world, port, kind, out):
         og = orc.Mesh(g)
         rp_g, ci_g, va_g = orc.assemble_K(og).export(og.ndof)
         r0, r1 = ep.row_start, ep.row_end
-        assert (r0, r1) == fm.petsc_ownership(og.ndof, world, rank)
+        assert (r0, r1) == (fm.petsc_ownership(og.ndof, world, rank) if row_bounds is None else (row_bounds[rank], row_bounds[rank + 1]))
         assert np.array_equal(rp_o, rp_g[r0:r1 + 1] - rp_g[r0]), "owned-row pattern (rowptr)"
         assert np.array_equal(ci_o, ci_g[rp_g[r0]:rp_g[r1]]), "owned-row pattern (colidx)"
         ref = va_g[rp_g[r0]:rp_g[r1]]
@@ -145,11 +150,11 @@ def _worker(rank, world, port, kind, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,kind", [(2, "hex"), (3, "hex"), (2, "quad"), (3, "tet-metis")])
+@pytest.mark.parametrize("world,kind", [(2, "hex"), (3, "hex"), (2, "quad"), (3, "tet-metis"), (3, "tet-metis-renumbered")])
 def test_exchange_plan_reproduces_global_matrix(world, kind):
     from oracle import pyoracle as orc
     orc.build()
-    if kind == "tet-metis":
+    if kind.startswith("tet-metis"):
         try:
             epart, cut = fm.metis_partition(mg.tet_cube(5), world)
         except RuntimeError as e:

@@ -30,8 +30,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--exchange", choices=("peer", "nccl"), default="peer")
-    ap.add_argument("--partition", choices=("slab", "metis"), default="slab",
-                    help="c3: element partition -- slabs, or METIS_PartMeshNodal called the way src/m_io.F90:137 calls it (rank 0 partitions, epart is broadcast)")
+    ap.add_argument("--partition", choices=("slab", "metis", "metis-renumbered"), default="slab",
+                    help="c3: element partition -- slabs, or METIS_PartMeshNodal called the way src/m_io.F90:137 calls it (rank 0 partitions, epart is "
+                         "broadcast); metis-renumbered: the same partition with a node numbering that follows it and the parts' own row ranges "
+                         "(mesh.renumber_by_partition) instead of the reference's natural numbering + PETSC_DECIDE")
     ap.add_argument("--stress", action="store_true", help="also time the nodal-averaged stress recovery (wall clock per call)")
     args = ap.parse_args()
     rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -49,7 +51,8 @@ def main():
         n = args.edge or 94
         g = mg.jitter(mg.tet_cube(n))
         total, label = g.nels, f"C3 tet4 {n}^3x6, {world} slab(s)"
-        if world > 1 and args.partition == "metis":
+        row_bounds = None
+        if world > 1 and args.partition.startswith("metis"):
             ep_t = torch.zeros(g.nels, dtype=torch.int32, device=dev)
             if rank == 0:
                 tm = time.time()
@@ -57,7 +60,14 @@ def main():
                 label = f"C3 tet4 {n}^3x6, METIS_PartMeshNodal into {world} parts (edge cut {cut}, {time.time() - tm:.1f} s on one host core)"
                 ep_t.copy_(torch.from_numpy(epart))
             dist.broadcast(ep_t, 0)
-            m = fm.localize(g, ep_t.cpu().numpy(), rank)
+            epart = ep_t.cpu().numpy()
+            if args.partition == "metis-renumbered":
+                g, nb = fm.renumber_by_partition(g, epart, world)
+                row_bounds = g.pdim * nb
+            m = fm.localize(g, epart, rank)
+            lab = [label]
+            dist.broadcast_object_list(lab, 0)
+            label = lab[0] + (", nodes renumbered by part, rows follow the parts" if row_bounds is not None else ", natural numbering, PETSC_DECIDE rows")
         else:
             m = fm.localize(g, mg.slab_partition(g, world), rank) if world > 1 else g
         del g
@@ -69,7 +79,7 @@ def main():
     d_f = fx.device_buffer(8 * fx.nrows)
     da = None
     if world > 1:
-        da = par.DistributedAssembly(fx, dist, dev, peer=args.exchange == "peer")
+        da = par.DistributedAssembly(fx, dist, dev, peer=args.exchange == "peer", row_bounds=row_bounds if args.config == "c3" else None)
         vals_ptr = C.c_void_p(da.vals_local.data_ptr())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     else:
