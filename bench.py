@@ -260,6 +260,7 @@ def main():
         # peer mode: kernel + remote stores + neighbour barrier + receiver add (interface rows) are all inside this call
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, d_u.ptr, vals_ptr, d_f.ptr, api.DEVICE))
         ms = fx.last_kernel_ms
+        asm_ms[0] += fx.L.femx_last_assembly_kernel_ms(fx.h)
         if da is not None and not da.peer:
             ev0.record()
             da.exchange()
@@ -273,12 +274,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    asm_ms = [0.0]                       # device time of the assembly kernel alone (the rest of a step: push, neighbours' barrier, add)
     sampler = ClockSampler(local_rank)
     sampler.start()                      # samples from warm-up to the end of the e2e loop: the GPU is under load throughout
     for _ in range(args.warmup):
         step_device()
     barrier()
     l0 = fx.launches
+    asm_ms[0] = 0.0
     w0 = time.perf_counter()
     dev_ms = 0.0
     for _ in range(args.steps):
@@ -353,7 +356,18 @@ def main():
     t = torch.tensor([dev_ms, wall_ms, e2e["ms"] if e2e else 0.0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms_rank = dev_ms
     dev_ms, wall_ms, e2e_ms = (float(x) for x in t.tolist())
+    breakdown = None
+    if world > 1:   # where a multi-GPU step goes: the kernel itself (per-GPU spread) vs push + waiting for the slowest neighbour + add
+        k = asm_ms[0] / args.steps
+        x = dev_ms_rank / args.steps - k
+        tt = torch.tensor([k, -k, x, -x, k, x], device="cuda", dtype=torch.float64)
+        hi = tt[:4].clone(); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        sm = tt[4:].clone(); dist.all_reduce(sm)
+        breakdown = {"assembly_kernel_ms": {"min": -float(hi[1]), "mean": float(sm[0]) / world, "max": float(hi[0])},
+                     "push_barrier_add_ms": {"min": -float(hi[3]), "mean": float(sm[1]) / world, "max": float(hi[2])},
+                     "note": "per rank and step; the barrier waits for the slowest neighbour, so a rank with a fast kernel shows a long push_barrier_add"}
     io = torch.tensor([float(e2e["h2d"]) if e2e else 0.0, float(e2e["d2h"]) if e2e else 0.0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(io)             # bytes of all ranks per step
@@ -399,7 +413,7 @@ def main():
                            "l2": "outputs (8*nnz bytes) exceed the 126 MB L2; no flush needed",
                            "parallelism": par_txt,
                            "variant": args.variant, "lz": args.lz, "plan_build_s": round(plan_s, 3), "plan_pass_s": round(fx.L.femx_plan_seconds(fx.h), 4), "wall_ms_per_step": wall_ms / args.steps},
-                "gpu_launches": int(launches),
+                "gpu_launches": int(launches), "step_breakdown": breakdown,
                 "clocks": sampler.summary(),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",

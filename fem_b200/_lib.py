@@ -78,6 +78,7 @@ SIGNATURES = {
     "femx_peer_disconnect": (C.c_int, [V]),
     "femx_launch_count": (C.c_int64, [V]),
     "femx_plan_seconds": (C.c_double, [V]),
+    "femx_last_assembly_kernel_ms": (C.c_double, [V]),
     "femx_last_kernel_ms": (C.c_double, [V]),
     "femx_version": (C.c_int, []),
 }

@@ -57,6 +57,7 @@ int femx_destroy(femx_ctx *c) {
   for (void *p : c->allocs) cudaFree(p);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
+  if (c->ev_mid) cudaEventDestroy(c->ev_mid);
   cudaStreamDestroy(c->own_stream);
   delete c;
   return FEMX_OK;
@@ -120,6 +121,13 @@ int femx_set_async(femx_ctx *c, int on) {
 int64_t femx_launch_count(const femx_ctx *c) { return c ? c->launches : 0; }
 double femx_last_kernel_ms(const femx_ctx *c) { return c ? c->last_ms : 0.0; }
 double femx_plan_seconds(const femx_ctx *c) { return c ? c->plan_seconds : 0.0; }
+double femx_last_assembly_kernel_ms(femx_ctx *c) {
+  if (!c) return 0.0;
+  if (!c->mid_valid) return c->last_ms;     // no peer exchange behind the kernel: the whole timed region is the kernel
+  float ms = 0.f;
+  if (cudaEventSynchronize(c->ev_mid) != cudaSuccess || cudaEventElapsedTime(&ms, c->ev0, c->ev_mid) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+  return ms;
+}
 
 // --------------------------------------------------------------------------- state
 int femx_set_mesh(femx_ctx *c, int pdim, int nels, const int *etype, const int *eptr, const int *eind,

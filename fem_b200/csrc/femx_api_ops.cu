@@ -88,7 +88,13 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
     c->launches += launch_elem_rows(c, d_u, c->d_ke, fint ? c->d_fe : nullptr);
     c->launches += launch_gather_rows(c, c->d_ke, fint ? c->d_fe : nullptr, d_vals, d_fint);
   }
-  if (peer) c->launches += launch_peer_finish(c, peer_fused, d_vals, d_fint);   // step barrier: the peers' stores into this rank's arena are complete
+  c->mid_valid = false;
+  if (peer) {
+    if (!c->ev_mid) CK(cudaEventCreate(&c->ev_mid));
+    CK(cudaEventRecord(c->ev_mid, c->stream));
+    c->mid_valid = true;
+    c->launches += launch_peer_finish(c, peer_fused, d_vals, d_fint);   // push, step barrier (the peers' stores into this rank's arena are complete), receiver add
+  }
   if ((rc = end_timing(c))) return rc;
   if ((rc = copy_back(c, vals, d_vals, c->nnz, where))) return rc;
   if (fint && (rc = copy_back(c, fint, d_fint, nglob, where))) return rc;

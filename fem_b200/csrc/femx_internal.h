@@ -177,7 +177,9 @@ struct femx_ctx {
   cudaStream_t own_stream = nullptr;   // the stream femx_create made (femx_set_stream may substitute the caller's)
   bool async = false;                 // femx_set_async: calls return without synchronising the stream
   bool ms_pending = false;            // ... the last call's event pair has not been read yet
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr;   // ev_mid: behind the assembly kernel, before the peer push / barrier / add
+  bool mid_valid = false;
+  double last_asm_ms = 0.0;
   std::string err;
   int64_t launches = 0;
   double last_ms = 0.0;

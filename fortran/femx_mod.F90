@@ -322,6 +322,10 @@ module femx
       import :: c_ptr, c_double
       type(c_ptr), value :: ctx
     end function
+    real(c_double) function femx_last_assembly_kernel_ms(ctx) bind(C, name="femx_last_assembly_kernel_ms")
+      import :: c_ptr, c_double
+      type(c_ptr), value :: ctx
+    end function
     real(c_double) function femx_plan_seconds(ctx) bind(C, name="femx_plan_seconds")
       import :: c_ptr, c_double
       type(c_ptr), value :: ctx

@@ -272,6 +272,10 @@ int64_t femx_launch_count(const femx_ctx *ctx);
 /* device time of the last assemble / stress / jacobian call's kernels, CUDA events on the ctx
  * stream, ms (0 if none) */
 double femx_last_kernel_ms(const femx_ctx *ctx);
+/* ... of which the assembly kernel alone, for the last femx_assemble_* on a peer-connected ctx (the rest is the interface
+ * push, the neighbours' step barrier -- i.e. waiting for the slowest neighbour -- and the receiver add); equals
+ * femx_last_kernel_ms without peers */
+double femx_last_assembly_kernel_ms(femx_ctx *ctx);
 /* wall time of the integer pass of the last femx_build_plan (device pass incl. its uploads; the figure the reference
  * pays inside MatSetValues' sorted inserts, src/main.F90:157-166), seconds */
 double femx_plan_seconds(const femx_ctx *ctx);
