@@ -353,6 +353,25 @@ def main():
             del b, fb
         del a, fa
 
+    if world > 1 and da is not None and da.peer:
+        # in-bench check (N > 1), size-independent: a rigid translation is in the null space of the assembled matrix, so in every
+        # MERGED interface row (own part + what the peers pushed, added by femx) the entries of each column component sum to zero;
+        # a lost, duplicated or misplaced contribution of the exchange leaves a residual of the size of an entry
+        ep = da.ep
+        mer = da.merged().cpu().numpy()
+        nrow = len(ep.if_rows)
+        worst = 0.0
+        if len(mer):
+            rows = np.repeat(np.arange(nrow, dtype=np.int64), np.diff(ep.if_rowptr))
+            sums = np.bincount(rows * m.pdim + (ep.if_colidx.astype(np.int64) % m.pdim), weights=mer, minlength=nrow * m.pdim)
+            worst = float(np.abs(sums).max() / np.abs(mer).max())
+        tw = torch.tensor([worst, float(nrow)], device="cuda", dtype=torch.float64)
+        tmx = tw.clone(); dist.all_reduce(tmx, op=dist.ReduceOp.MAX)
+        tsm = tw.clone(); dist.all_reduce(tsm)
+        check = {"merged_interface_rows_rigid_translation_residual_rel": float(tmx[0]), "merged_interface_rows_all_ranks": int(tsm[1]),
+                 "note": "max over ranks and rows of |sum_j K[row, (node j, component c)]| / max|K|, rows merged by femx_assemble_K_fint"}
+        assert float(tmx[0]) < 1e-9, check
+
     t = torch.tensor([dev_ms, wall_ms, e2e["ms"] if e2e else 0.0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
