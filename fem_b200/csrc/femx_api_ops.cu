@@ -48,7 +48,8 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if (u_local && (rc = stage_in(c, u_local, nloc, where, &c->d_u, &d_u))) return rc;
   if ((rc = stage_out(c, vals, c->nnz, where, &c->d_vals, &d_vals))) return rc;
   if (fint && (rc = stage_out(c, fint, nglob, where, &c->d_vec[0], &d_fint))) return rc;
-  // auto (0): the 16-warp symmetric tile kernel with permuted gather lanes (12) for a logical hex8 grid, else the fused rows kernel, else two-pass
+  // auto (0): the warp-specialised DMMA tile kernel (20) for a logical hex8 grid (the symmetric pair-block kernel 12 when the assembly
+  // kernel itself is to store the interface rows at their owners), else the simplex / fused rows kernels, else two-pass
   const int av0 = c->opts.assembly_variant;
   // the hex8 tile kernels address values with 32-bit slots: beyond 2^32 values (34 GB, ~17.5 M hex8 on one GPU) auto uses the general kernels
   const bool slots32 = c->nnz <= 0xffffffffll;
@@ -73,7 +74,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
   if (fused) {
-    const int av = av0 == 0 ? 12 : av0;
+    const int av = av0 == 0 ? (peer_fused ? 12 : 20) : av0;
 #ifdef FEMX_DIAG
     if (av == 13) c->launches += launch_hex_sym7(c, d_u, d_vals, d_fint);
     else if (av == 21) c->launches += launch_hex_mma_prof(c, d_u, d_vals, d_fint);

@@ -53,13 +53,19 @@ constexpr int NYT = FEMX_MMA_NYT, EYC = NYT + 1; // owned node rows, cell rows
 constexpr int UX = NXT + 2, UY = NYT + 2, UL = UX * UY;   // node positions of a layer incl. halo
 constexpr int NP = NXT * NYT;
 constexpr int NMW = 8, NGW = FEMX_MMA_NGW, NT = 32 * (NMW + NGW);   // MMA and gather warps
-constexpr int RING = 4;                          // cell rows in flight between the MMA and the gather warps
+#ifndef FEMX_MMA_RING
+#define FEMX_MMA_RING 5
+#endif
+constexpr int RING = FEMX_MMA_RING;             // cell rows in flight between the MMA and the gather warps (3 / 4 / 5: 1.333 / 1.327 / 1.297 ms; 6 do not fit)
 constexpr int LR = 3, NR = 4;                    // node-layer ring, node-id ring
 constexpr int TP = 36, CP = 6 * TP, SP = 1729;   // doubles per tile / cell / ring slot (annealed against bank conflicts, tools/hex_mma_anneal.py)
 constexpr int GP = 192;                          // doubles per cell of scaled gradients [i][row][ip & 3][ip >> 2]
 constexpr int ZT = 12, ZC = 6 * ZT;              // z-carry entries per tile / per cell
 constexpr int XP = UX * 3 + 1;                   // doubles per row of the coordinate layer
-constexpr int PF_ROW = 6;                        // gather warps prefetch the next node layer when they reach this node row
+#ifndef FEMX_MMA_PF_ROW
+#define FEMX_MMA_PF_ROW 6
+#endif
+constexpr int PF_ROW = FEMX_MMA_PF_ROW;                        // gather warps prefetch the next node layer when they reach this node row
 static_assert(EXC == NMW, "one MMA warp per cell column");
 #ifndef FEMX_MMA_REG_M
 #define FEMX_MMA_REG_M 160
@@ -78,7 +84,7 @@ __constant__ unsigned char c_perm[2][TP] = {
 
 struct Smem {
   double ring[RING][SP];          // K entries of one cell row: [cell column][tile][36]
-  double zc[EXC][EYC][ZC];        // top-face pair sums of the previous cell layer (raw accumulators)
+  alignas(16) double zc[EXC][EYC][ZC];        // top-face pair sums of the previous cell layer (raw accumulators)
   double gsc[NMW][4][GP];         // per MMA warp: scaled gradients of its next four cells
   double xlay[LR][UY * XP];
   double ulay[LR][UL][3];

@@ -61,7 +61,7 @@ enum {
   FEMX_Q_UEL = 0
 };
 
-/* assembly variants: 0 = best available for the mesh (12 for a logical hex8 grid, 11 for a pure
+/* assembly variants: 0 = best available for the mesh (20 for a logical hex8 grid, 11 for a pure
  * tri3 / tet4 mesh, else 9, else 1); 1 = two-pass (element kernel -> packed Ke scratch -> ordered gather; the cross-check);
  * 9 = fused rows kernel for any element mix; 11 = simplex rows kernel (tri3 / tet4 only); 12 = symmetric pair-block hex8
  * tile kernel; 20 = warp-specialised DMMA hex8 tile kernel.  Any other value is refused by femx_create (13 / 21, the

@@ -37,7 +37,7 @@ def _nobc(m):
 
 
 @pytest.mark.parametrize("world", [2, 3])
-@pytest.mark.parametrize("kind,variant", [("hex", 0), ("hex", 20), ("tet", 0), ("quad", 0)])
+@pytest.mark.parametrize("kind,variant", [("hex", 0), ("hex", 12), ("tet", 0), ("quad", 0)])
 def test_local_ranks_exchange_on_one_gpu(orc, world, kind, variant):
     g = {"hex": lambda: mg.jitter(mg.hex_cube(9, clamp=False)), "tet": lambda: mg.jitter(mg.tet_cube(5)),
          "quad": lambda: mg.jitter(mg.quad_rect(23, 17))}[kind]()
