@@ -253,6 +253,7 @@ struct femx_ctx {
     // receiver add over the interface rows (femx_peer_set_merge)
     int64_t n_merge = 0, n_fmerge = 0;
     int64_t *d_mown = nullptr, *d_mptr = nullptr, *d_midx = nullptr, *d_frow = nullptr, *d_fptr = nullptr, *d_fidx = nullptr;
+    int32_t *d_mown32 = nullptr, *d_mptr32 = nullptr, *d_midx32 = nullptr;   // the same lists in 32 bits when everything fits
     double *d_merged = nullptr;
   } peer;
 };

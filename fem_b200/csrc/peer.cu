@@ -13,6 +13,8 @@
 // barrier kernel follows (measured slower).
 // Receive areas are double-buffered on the step parity, so a peer that is one assembly ahead never
 // overwrites values the host solver may still be reading; the step barrier keeps it from getting two ahead.
+#include <cstdlib>
+
 #include "api_util.h"
 
 namespace {
@@ -92,12 +94,14 @@ peer_push_kernel(PeerTab pt, const double *__restrict__ vals, const double *__re
 // Receiver add (the part of MatAssemblyEnd that sums the stash into the owned rows, src/main.F90:167-168), interface rows
 // only: entry s of the merged interface rows = this rank's own value (slot own[s] of the local CSR, -1 = the rank has no
 // such entry) + the received values idx[ptr[s]..ptr[s+1]) in list order = (source rank, sender position): deterministic.
-__global__ void peer_merge_kernel(const double *__restrict__ vals, const double *__restrict__ recv, const int64_t *__restrict__ own,
-                                  const int64_t *__restrict__ ptr, const int64_t *__restrict__ idx, int64_t n, double *__restrict__ out) {
+template <class I>
+__global__ void peer_merge_kernel(const double *__restrict__ vals, const double *__restrict__ recv, const I *__restrict__ own,
+                                  const I *__restrict__ ptr, const I *__restrict__ idx, int64_t n, double *__restrict__ out) {
   const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
-  double v = own[s] >= 0 ? vals[own[s]] : 0.0;
-  for (int64_t q = ptr[s]; q < ptr[s + 1]; ++q) v += recv[idx[q]];
+  const I o = own[s], q0 = ptr[s], q1 = ptr[s + 1];
+  double v = o >= 0 ? vals[o] : 0.0;
+  for (I q = q0; q < q1; ++q) v += recv[idx[q]];
   out[s] = v;
 }
 // owned internal-force entries: fint[row[s]] += received entries in (source rank, position) order
@@ -175,7 +179,9 @@ static int launch_peer_merge(femx_ctx *c, const double *d_vals, double *d_fint) 
   const int par = (int)((P.step - 1) & 1);   // the buffer the assembly that just ran filled
   const double *buf = reinterpret_cast<const double *>(P.arena + kFlagBytes) + par * buffer_doubles(P.nv, P.nf);
   if (P.n_merge > 0) {
-    peer_merge_kernel<<<(unsigned)((P.n_merge + 255) / 256), 256, 0, c->stream>>>(d_vals, buf, P.d_mown, P.d_mptr, P.d_midx, P.n_merge, P.d_merged);
+    // 32-bit lists when every index fits (femx_peer_set_merge): the add moves 32 instead of 48 bytes per merged value
+    if (P.d_mown32) peer_merge_kernel<int32_t><<<(unsigned)((P.n_merge + 255) / 256), 256, 0, c->stream>>>(d_vals, buf, P.d_mown32, P.d_mptr32, P.d_midx32, P.n_merge, P.d_merged);
+    else peer_merge_kernel<int64_t><<<(unsigned)((P.n_merge + 255) / 256), 256, 0, c->stream>>>(d_vals, buf, P.d_mown, P.d_mptr, P.d_midx, P.n_merge, P.d_merged);
     ++n;
   }
   if (P.n_fmerge > 0 && d_fint) {
@@ -194,6 +200,15 @@ int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_
   const long long limit = 20000000000ll;   // ~10 s
   const bool wait = !P.deferred;
   int n = 1;
+  // FEMX_PEER_TIMING=1: device time of the push (+ barrier) and of the receiver add, averaged, to stderr every 20 assemblies
+  static const bool timing = getenv("FEMX_PEER_TIMING") != nullptr;
+  static cudaEvent_t te[3] = {nullptr, nullptr, nullptr};
+  static double tacc[2] = {0.0, 0.0};
+  static int tn = 0;
+  if (timing) {
+    if (!te[0]) for (auto &e : te) cudaEventCreate(&e);
+    cudaEventRecord(te[0], c->stream);
+  }
   if (fused) {
     ++P.step;
     peer_signal_wait_kernel<<<1, 32, 0, c->stream>>>(fp, mine, P.nranks, P.rank, P.nbr_mask, P.step, limit, P.d_err, true, wait);
@@ -206,8 +221,20 @@ int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_
     peer_push_kernel<<<grid, 256, 0, c->stream>>>(pt, d_vals, d_fint, c->dm.nl2g, c->pdim, fp, mine, P.nbr_mask, P.step, limit, P.d_err,
                                                   reinterpret_cast<unsigned int *>(P.d_err + 1), wait);
   }
+  if (timing) cudaEventRecord(te[1], c->stream);
   if (wait) n += launch_peer_merge(c, d_vals, d_fint);
   else { P.pending = true; P.pend_vals = const_cast<double *>(d_vals); P.pend_fint = d_fint; }
+  if (timing) {
+    cudaEventRecord(te[2], c->stream);
+    cudaEventSynchronize(te[2]);
+    float a = 0.f, b = 0.f;
+    cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]);
+    tacc[0] += a; tacc[1] += b;
+    if (++tn % 20 == 0) {
+      fprintf(stderr, "femx peer timing (rank %d, %d assemblies): push + barrier %.4f ms, receiver add %.4f ms\n", P.rank, tn, tacc[0] / 20, tacc[1] / 20);
+      tacc[0] = tacc[1] = 0.0;
+    }
+  }
   return n;
 }
 
@@ -328,14 +355,21 @@ int femx_peer_set_merge(femx_ctx *c, int64_t n, const int64_t *own_slot, const i
   for (int64_t q = 0; q < (n ? ptr[n] : 0); ++q) ARG(idx[q] >= 0 && idx[q] < P.nv, "merge list: received index outside the arena");
   for (int64_t s = 0; s < nf; ++s) ARG(f_row[s] >= 0 && f_row[s] < (int64_t)c->pdim * c->nnds && f_ptr[s] <= f_ptr[s + 1], "force merge list: bad row / ptr");
   for (int64_t q = 0; q < (nf ? f_ptr[nf] : 0); ++q) ARG(f_idx[q] >= 0 && f_idx[q] < P.nf, "force merge list: received index outside the arena");
-  for (void *q : {(void *)P.d_mown, (void *)P.d_mptr, (void *)P.d_midx, (void *)P.d_frow, (void *)P.d_fptr, (void *)P.d_fidx, (void *)P.d_merged}) dev_release(c, q);
+  for (void *q : {(void *)P.d_mown, (void *)P.d_mptr, (void *)P.d_midx, (void *)P.d_frow, (void *)P.d_fptr, (void *)P.d_fidx, (void *)P.d_merged,
+                  (void *)P.d_mown32, (void *)P.d_mptr32, (void *)P.d_midx32}) dev_release(c, q);
   P.d_mown = P.d_mptr = P.d_midx = P.d_frow = P.d_fptr = P.d_fidx = nullptr; P.d_merged = nullptr;
+  P.d_mown32 = P.d_mptr32 = P.d_midx32 = nullptr;
   P.n_merge = n; P.n_fmerge = nf;
   int rc;
   if (n > 0) {
-    if ((rc = upload(c, &P.d_mown, std::vector<int64_t>(own_slot, own_slot + n))) || (rc = upload(c, &P.d_mptr, std::vector<int64_t>(ptr, ptr + n + 1))) ||
-        (rc = upload(c, &P.d_midx, std::vector<int64_t>(idx, idx + ptr[n]))) || (rc = dev_alloc(c, &P.d_merged, n)))
+    if (c->nnz < 2147483647ll && P.nv < 2147483647ll && ptr[n] < 2147483647ll) {   // every slot, arena position and list offset fits 32 bits
+      if ((rc = upload(c, &P.d_mown32, std::vector<int32_t>(own_slot, own_slot + n))) || (rc = upload(c, &P.d_mptr32, std::vector<int32_t>(ptr, ptr + n + 1))) ||
+          (rc = upload(c, &P.d_midx32, std::vector<int32_t>(idx, idx + ptr[n]))))
+        return rc;
+    } else if ((rc = upload(c, &P.d_mown, std::vector<int64_t>(own_slot, own_slot + n))) || (rc = upload(c, &P.d_mptr, std::vector<int64_t>(ptr, ptr + n + 1))) ||
+               (rc = upload(c, &P.d_midx, std::vector<int64_t>(idx, idx + ptr[n]))))
       return rc;
+    if ((rc = dev_alloc(c, &P.d_merged, n))) return rc;
   }
   if (nf > 0) {
     if ((rc = upload(c, &P.d_frow, std::vector<int64_t>(f_row, f_row + nf))) || (rc = upload(c, &P.d_fptr, std::vector<int64_t>(f_ptr, f_ptr + nf + 1))) ||
