@@ -71,7 +71,11 @@ static_assert(EXC == NMW, "one MMA warp per cell column");
 #define FEMX_MMA_REG_M 160
 #define FEMX_MMA_REG_G 96
 #endif
-static_assert(NGW == 8 || FEMX_MMA_REG_M != 160, "register split (setmaxnreg 160 / 96) and the prefetch protocol are validated for 8 gather warps only");
+// setmaxnreg moves registers inside the CTA's pool only: what the gather warps release (launch allocation - REG_G each) must cover
+// what the MMA warps take (REG_M - launch allocation each), or setmaxnreg.inc never returns; and setmaxnreg is a warpgroup
+// instruction: the gather warps must come in groups of four (7 gather warps, one per node column, trap in the protocol's bounded
+// waits).  Validated splits: 8 gather warps 160 / 96 (launch 128), 12 gather warps 128 / 72 or 136 / 64 (launch 96).
+static_assert(NGW % 4 == 0 && NMW % 4 == 0, "setmaxnreg works on warpgroups of four warps");
 static_assert(32 * (NMW * FEMX_MMA_REG_M + NGW * FEMX_MMA_REG_G) <= 65536, "register split exceeds the register file");
 static_assert(NYT > PF_ROW + 1 && EYC > RING, "tile too short for the prefetch point / the ring");
 
