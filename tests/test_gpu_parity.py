@@ -134,7 +134,8 @@ def test_device_plan_equals_host_plan(golden):
     list the kernels read is identical -- the values of every assembly variant and the nodal stress, bit for bit."""
     cases = list(_meshes(golden)) + [("l_shaped_hex", _l_shaped(6)), ("hex_permuted", _permuted(mg.jitter(mg.hex_cube(6, clamp=False)), 3)),
                                      ("hex_box", mg.jitter(mg.hex_block(9, 5, 11))), ("tet_jitter", mg.jitter(mg.tet_cube(5))),
-                                     ("tri_wide", mg.jitter(mg.tri_rect(40, 3))), ("hex_two_islands", _two_islands())]
+                                     ("tri_wide", mg.jitter(mg.tri_rect(40, 3))), ("hex_two_islands", _two_islands()),
+                                     ("tet_shuffled", _shuffled(mg.jitter(mg.tet_cube(5)), 11)), ("quad_shuffled", _shuffled(mg.jitter(mg.quad_rect(12, 9)), 12))]
     for name, m in cases:
         u = mg.displacement_field(m)
         pure = set(np.unique(m.etype))
@@ -162,6 +163,17 @@ def test_device_plan_equals_host_plan(golden):
                     f.set_mesh(m).build_plan()
                     res.append(f.assemble_K_fint(u))
             assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (name, av)
+
+
+def _shuffled(m, seed):
+    """Same mesh with random node numbering AND random element order (an unstructured mesh as far as the integer pass can tell)."""
+    rng = np.random.default_rng(seed)
+    perm = rng.permutation(m.nlnds)            # new id of old node i = perm[i]
+    eo = rng.permutation(m.nels)
+    nen = int(m.eptr[1] - m.eptr[0])
+    conn = (perm[m.eind - 1] + 1).reshape(-1, nen)[eo]
+    return dataclasses.replace(m, eind=conn.reshape(-1).astype(np.int32), coords=m.coords[np.argsort(perm)], emat=m.emat[eo], enlmat=m.enlmat[eo],
+                               etype=m.etype[eo], bcnode=np.zeros((0, 1 + m.pdim), np.int32), bcval=np.zeros((0, m.pdim)))
 
 
 def _two_islands():
