@@ -4,10 +4,14 @@ does not cover.  Run under torchrun, one rank per GPU:
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         tools/scale_bench.py --config c5|c3 [--steps K --warmup W --exchange peer|nccl]
   c5  hex8 200^3 (8,000,000 elements, 24.4 M dof, 1.95 G nonzeros) cut into N z-slabs, built rank-locally
-  c3  tet4 94^3 x 6 (4,983,504 elements) cut into N slabs of the global mesh (mesh.localize), K + f_int
-Elements follow the slab partition, rows the PETSC_DECIDE split; interface rows travel through the peer-memory push
-kernel + device-side step barrier (csrc/peer.cu) or NCCL.  Time = device time of femx_assemble_K_fint per step (CUDA
-events on the library's stream, barrier inside for peer mode), max over ranks.  One JSON line from rank 0."""
+  c3  tet4 94^3 x 6 (4,983,504 elements), K + f_int (+ --stress: nodal-averaged stress), --partition
+        slab              N slabs of the global mesh in element order (mesh.localize)
+        metis             METIS_PartMeshNodal as src/m_io.F90:137 calls it, the mesh file's node numbering, PETSC_DECIDE rows
+                          (the reference's situation: most rows a rank assembles belong to other ranks)
+        metis-renumbered  the same partition, node ids following the parts (mesh.renumber_by_partition), rows = the parts' ranges
+c5 rows follow the PETSC_DECIDE split; interface rows travel through the peer-memory push kernel, the neighbours' step barrier and
+the receiver add inside the timed call (csrc/peer.cu), or NCCL after it.  Time = device time of femx_assemble_K_fint per step
+(CUDA events on the library's stream), max over ranks.  One JSON line from rank 0."""
 import argparse
 import ctypes as C
 import json
