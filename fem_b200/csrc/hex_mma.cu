@@ -67,6 +67,7 @@ constexpr int XP = UX * 3 + 1;                   // doubles per row of the coord
 #endif
 constexpr int PF_ROW = FEMX_MMA_PF_ROW;                        // gather warps prefetch the next node layer when they reach this node row
 static_assert(EXC == NMW, "one MMA warp per cell column");
+static_assert(sizeof(HexRowMeta) % 16 == 0, "bulk copies move multiples of 16 bytes");
 #ifndef FEMX_MMA_REG_M
 #define FEMX_MMA_REG_M 160
 #define FEMX_MMA_REG_G 96
@@ -93,7 +94,7 @@ struct Smem {
   double xlay[LR][UY * XP];
   double ulay[LR][UL][3];
   double esc[LR][EYC * EXC];
-  HexRowMeta meta[LR][NP];
+  alignas(16) HexRowMeta meta[LR][NP];   // rows arrive by bulk copy: 16-byte aligned
   int nid[NR][UL];
   double fcarry[NP][3];
   unsigned long long bar_full[RING], bar_empty[RING], bar_lay[LR];
@@ -116,6 +117,14 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long *b) {
 }
 __device__ __forceinline__ void mbar_arrive_cp_async(unsigned long long *b) {   // arrives when this thread's cp.async are done
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(saddr(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *b, unsigned bytes) {   // bytes a bulk copy will deliver in this phase
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(saddr(b)), "r"(bytes) : "memory");
+}
+// TMA engine, 1-D: size and both addresses multiples of 16 bytes; completion is counted in bytes on the mbarrier
+__device__ __forceinline__ void bulk_g2s(void *smem, const void *gmem, unsigned bytes, unsigned long long *b) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(saddr(smem)), "l"(gmem), "r"(bytes), "r"(saddr(b)) : "memory");
 }
 __device__ __forceinline__ bool mbar_try(unsigned long long *b, unsigned parity) {
   unsigned ok;
@@ -233,12 +242,22 @@ __device__ __forceinline__ void fetch_layer(Smem &S, const DevHex &hx, const Til
 #pragma unroll
       for (int d = 0; d < 3; ++d) cp_async8z(&S.ulay[sl][t][d], src + d, r >= 0);
     }
-    const int ux = t % UX, uy = t / UX;
-    if (ux >= 1 && ux <= NXT && uy >= 1 && uy <= NYT) {
-      double *rm = reinterpret_cast<double *>(&S.meta[sl][(uy - 1) * NXT + (ux - 1)]);
-      const double *src = reinterpret_cast<const double *>(hx.pos_meta + c);
+  }
+  // row metadata (48 bytes per node, the tile's 7 nodes of a row are contiguous in pos_meta): one bulk copy by the TMA engine per
+  // node row, issued by one thread per row and counted in bytes on the layer barrier; positions outside the grid are zero-filled
+  // (nb = 0: no node here) with cp.async as before
+  for (int row = gt; row < NYT; row += 32 * NGW) {
+    const int nj = T.j0 + row;
+    const int nvalid = (lay >= 0 && lay < hx.NK && nj < hx.NJ) ? max(0, min(NXT, hx.NI - T.i0)) : 0;
+    HexRowMeta *dst = &S.meta[sl][row * NXT];
+    if (nvalid > 0) {
+      mbar_expect_tx(&S.bar_lay[sl], (unsigned)(nvalid * sizeof(HexRowMeta)));
+      bulk_g2s(dst, hx.pos_meta + ((long long)lay * hx.NJ + nj) * hx.NI + T.i0, (unsigned)(nvalid * sizeof(HexRowMeta)), &S.bar_lay[sl]);
+    }
+    for (int q = nvalid; q < NXT; ++q) {
+      double *rm = reinterpret_cast<double *>(dst + q);
 #pragma unroll
-      for (int d = 0; d < 6; ++d) cp_async8z(rm + d, src + d, ok);   // zero-filled: nb = 0, no node here
+      for (int d = 0; d < 6; ++d) cp_async8z(rm + d, hx.pos_meta, false);
     }
   }
   for (int t = gt; t < EYC * EXC; t += 32 * NGW) {
