@@ -71,6 +71,7 @@ SIGNATURES = {
     "femx_peer_set_merge": (C.c_int, [V, C.c_int64, V, V, V, C.c_int64, V, V, V]),
     "femx_peer_merged": (C.c_int, [V, V, V]),
     "femx_peer_complete": (C.c_int, [V]),
+    "femx_peer_set_deferred": (C.c_int, [V, C.c_int]),
     "femx_peer_last_error": (C.c_int, [V]),
     "femx_peer_set_scatter": (C.c_int, [V, V, V, V, V]),
     "femx_scatter_u": (C.c_int, [V, V, V, C.c_int]),

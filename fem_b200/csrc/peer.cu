@@ -398,10 +398,23 @@ static int peer_check_error(femx_ctx *c) {
   return FEMX_OK;
 }
 
+// Several PROCESSES that share one GPU (a host that runs more MPI ranks than it has GPUs) are in the position of local
+// ranks: their kernels are time-sliced, so a step barrier spun on the device waits for a context switch.  Deferred mode
+// on an IPC connection: the assembly pushes and signals, the host synchronises its stream and meets the other ranks
+// (MPI_Barrier), femx_peer_complete checks the flags and runs the receiver add.
+int femx_peer_set_deferred(femx_ctx *c, int on) {
+  if (!c) return FEMX_ERR_ARG;
+  auto &P = c->peer;
+  ARG(P.connected && !P.local, "femx_peer_set_deferred belongs to femx_peer_connect connections (local peers are always deferred)");
+  ARG(!P.pending && !P.upending, "an assembly / scatter is outstanding (femx_peer_complete)");
+  P.deferred = on != 0;
+  return FEMX_OK;
+}
+
 int femx_peer_complete(femx_ctx *c) {
   if (!c) return FEMX_ERR_ARG;
   auto &P = c->peer;
-  ARG(P.connected && P.deferred, "femx_peer_complete belongs to deferred (local) peer connections");
+  ARG(P.connected && P.deferred, "femx_peer_complete belongs to deferred peer connections");
   ARG(P.pending || P.upending, "no assembly / scatter is outstanding");
   CK(cudaSetDevice(c->device));
   FlagPtrs fp{};

@@ -253,16 +253,21 @@ class DistributedAssembly:
     among neighbours and the receiver add run inside femx_assemble_* (csrc/peer.cu).  peer = False: the value slices go
     through torch.distributed all_to_all (NCCL; gloo in the CPU tests) after the call and merged_host() adds on the host.
     `vals_local` lives in a torch tensor; femx writes into it through its raw device pointer.
+    deferred = True (with peer): ranks that SHARE a GPU (more ranks than GPUs) -- assemblies and scatter_u push and signal,
+    complete() synchronises, meets the other ranks and runs the receiver add (femx_peer_set_deferred).  comm_device = where
+    the setup collectives' tensors live ("cpu" for a gloo group; default: device, for NCCL).
     """
 
-    def __init__(self, fx, dist, device, peer=False, row_bounds=None):
+    def __init__(self, fx, dist, device, peer=False, row_bounds=None, deferred=False, comm_device=None):
         import torch
         self.fx, self.dist, self.device, self.torch = fx, dist, device, torch
+        self.comm = comm = device if comm_device is None else comm_device
+        self.deferred = False
         self.rowptr, self.colidx = fx.pattern()
         nranks, rank = dist.get_world_size(), dist.get_rank()
         m = fx.mesh
         ep = plan_sends(self.rowptr, self.colidx, fx.nrows, nranks, rank, m.nl2g, m.pdim, row_bounds)
-        rr, rcs, rf = exchange_lists(ep, dist, device)
+        rr, rcs, rf = exchange_lists(ep, dist, comm)
         self._recv_frows = rf
         self.ep = finish_plan(ep, self.rowptr, self.colidx, rr, rcs, rf)
         fx._ck(fx.L.femx_set_ownership(fx.h, nranks, rank, ep.row_start, ep.row_end))
@@ -280,21 +285,24 @@ class DistributedAssembly:
                 import sys
                 print(f"femx: peer-memory exchange unavailable on rank {rank} ({e}); using NCCL", file=sys.stderr, flush=True)
                 good = 0
-            t = torch.tensor([good], device=device)
+            t = torch.tensor([good], device=comm)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
             if not int(t.item()) and good:
                 self.fx._ck(self.fx.L.femx_peer_disconnect(self.fx.h))
             self.peer = bool(int(t.item()))
+            if self.peer and deferred:
+                fx._ck(fx.L.femx_peer_set_deferred(fx.h, 1))
+                self.deferred = True
 
     def _connect_peers(self):
         import ctypes as C
         torch, fx, dist, ep = self.torch, self.fx, self.dist, self.ep
         P = ep.nranks
         self.lay = lay = peer_layout(ep, fx.nnz)
-        val_dst, f_dst, caps = exchange_offsets(lay, dist, P, self.device)
+        val_dst, f_dst, caps = exchange_offsets(lay, dist, P, self.comm)
         handle = (C.c_char * 64)()
         fx._ck(fx.L.femx_peer_arena_create(fx.h, int(caps[ep.rank, 0]), int(caps[ep.rank, 1]), C.addressof(handle)))
-        mine = torch.frombuffer(bytearray(handle.raw), dtype=torch.uint8).to(self.device)
+        mine = torch.frombuffer(bytearray(handle.raw), dtype=torch.uint8).to(self.comm)
         alls = [torch.empty_like(mine) for _ in range(P)]
         dist.all_gather(alls, mine)
         handles = b"".join(bytes(t.cpu().numpy().tobytes()) for t in alls)
@@ -303,7 +311,7 @@ class DistributedAssembly:
         _set_merge(fx, ep)
         self.n_recv_f = int(caps[ep.rank, 1])
         # GetVec_U: every rank tells its peers where (in its local dof numbering) the block they own starts, and its pdim * nlnds
-        mine = torch.tensor(np.stack([lay["f_bounds"][:-1], np.full(P, fx.mesh.pdim * fx.mesh.nlnds)], 1).reshape(-1), dtype=torch.int64, device=self.device)
+        mine = torch.tensor(np.stack([lay["f_bounds"][:-1], np.full(P, fx.mesh.pdim * fx.mesh.nlnds)], 1).reshape(-1), dtype=torch.int64, device=self.comm)
         theirs = torch.empty_like(mine)
         dist.all_to_all_single(theirs, mine)
         theirs = theirs.cpu().numpy().reshape(P, 2)
@@ -315,6 +323,13 @@ class DistributedAssembly:
         import ctypes as C
         self.fx._ck(self.fx.L.femx_scatter_u(self.fx.h, C.c_void_p(u_owned.data_ptr()), C.c_void_p(u_local.data_ptr()), 1))
         return u_local
+
+    def complete(self):
+        """deferred peers: finish the outstanding assembly / scatter_u once every rank has issued its own"""
+        self.torch.cuda.synchronize(self.device)
+        self.dist.barrier()
+        self.fx._ck(self.fx.L.femx_peer_complete(self.fx.h))
+        self.dist.barrier()      # nobody starts the next step's pushes into a buffer a peer is still adding from
 
     def peer_received(self):
         """(values, force entries) the last assembly received, as torch views of the arena."""

@@ -206,6 +206,11 @@ module femx
       import :: c_ptr, c_int
       type(c_ptr), value :: ctx
     end function
+    integer(c_int) function femx_peer_set_deferred(ctx, on) bind(C, name="femx_peer_set_deferred")
+      import :: c_ptr, c_int
+      type(c_ptr), value :: ctx
+      integer(c_int), value :: on
+    end function
     integer(c_int) function femx_peer_last_error(ctx) bind(C, name="femx_peer_last_error")
       import :: c_ptr, c_int
       type(c_ptr), value :: ctx

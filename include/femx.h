@@ -252,6 +252,10 @@ int femx_peer_set_merge(femx_ctx *ctx, int64_t n, const int64_t *own_slot, const
                         int64_t nf, const int64_t *f_row, const int64_t *f_ptr, const int64_t *f_idx);
 int femx_peer_merged(femx_ctx *ctx, const double **merged, int64_t *n);
 int femx_peer_complete(femx_ctx *ctx);
+/* femx_peer_connect connections whose ranks SHARE a GPU (more MPI ranks than GPUs: their kernels are time-sliced, a
+ * device-side step barrier would wait for context switches): on = 1 makes assemblies / femx_scatter_u push and signal
+ * only; the host synchronises, meets the other ranks (MPI_Barrier) and calls femx_peer_complete. */
+int femx_peer_set_deferred(femx_ctx *ctx, int on);
 int femx_peer_last_error(femx_ctx *ctx);   /* reports (and clears) a step-barrier timeout */
 /* GetVec_U across ranks (src/m_global.F90:549-564; scatter of src/main.F90:183-190), the reverse of the force exchange:
  * femx_peer_set_scatter names, per peer q, the owned global rows send_rows[send_ptr[q] .. send_ptr[q+1]) whose

@@ -4,7 +4,10 @@
 Every rank assembles its slab with the CUDA path; interface rows travel either inside the assembly kernel
 (peer-memory stores over NVLink, csrc/peer.cu) or over NCCL after it, and the merged owned rows are compared
 with the CPU oracle's 1-rank global matrix (pattern bit-exact, values 1e-12), twice per mode so that both
-receive buffers of the peer arena are exercised."""
+receive buffers of the peer arena are exercised.
+FEMX_SAME_DEVICE=1: the ranks are PROCESSES that share GPU 0 (more ranks than GPUs): gloo for the setup exchange, the same
+IPC-mapped arenas, deferred completion (femx_peer_set_deferred + femx_peer_complete after a host barrier) because kernels
+of different processes are time-sliced; the NCCL mode is left out (NCCL refuses two ranks on one device)."""
 import os
 import sys
 
@@ -19,14 +22,21 @@ from oracle import pyoracle as orc  # noqa: E402
 
 def main():
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    same = os.environ.get("FEMX_SAME_DEVICE") == "1"
+    if same:
+        lr = 0
     torch.cuda.set_device(lr)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     dev = torch.device("cuda", lr)
+    if same:
+        dist.init_process_group("gloo")
+    else:
+        dist.init_process_group("nccl", device_id=dev)
+    comm = "cpu" if same else dev
     ok = True
     import ctypes as C
     cases = [(name, g, peer, rep) for name, g in (("hex", mg.jitter(mg.hex_cube(12, clamp=False))), ("tet", mg.jitter(mg.tet_cube(6))),
                                                   ("quad", mg.jitter(mg.quad_rect(40, 31))))
-             for peer in (0, 1, 2) for rep in ((0, 1, 2) if peer else (0,))]   # 0 NCCL, 1 push kernel, 2 stores fused into the assembly kernel
+             for peer in ((1, 2) if same else (0, 1, 2)) for rep in ((0, 1, 2) if peer else (0,))]   # 0 NCCL, 1 push kernel, 2 stores fused into the assembly kernel
     fx = da = None
     for name, g, peer, rep in cases:
         if rep == 0:
@@ -35,7 +45,8 @@ def main():
             loc = fm.localize(g, mg.slab_partition(g, world), rank)
             fx = api.Femx(device=lr, peer_in_kernel=peer == 2)
             fx.set_mesh(loc).build_plan()
-            da = par.DistributedAssembly(fx, dist, dev, peer=peer > 0)
+            da = par.DistributedAssembly(fx, dist, dev, peer=peer > 0, deferred=same, comm_device=comm)
+            assert not same or (da.peer and da.deferred), "same-device ranks need the IPC arenas"
         u = mg.displacement_field(loc)
         d_u = torch.from_numpy(u.reshape(-1)).to(dev)
         d_f = torch.zeros(fx.nrows, dtype=torch.float64, device=dev)
@@ -43,6 +54,8 @@ def main():
         torch.cuda.synchronize()
         fx._ck(fx.L.femx_assemble_K_fint(fx.h, C.c_void_p(d_u.data_ptr()), C.c_void_p(da.vals_local.data_ptr()),
                                          C.c_void_p(d_f.data_ptr()), api.DEVICE))
+        if same:
+            da.complete()
         recv = da.exchange()
         vl = da.vals_local.cpu().numpy()
         if peer:                                   # the receiver add ran inside the assemble call (interface rows only)
@@ -53,6 +66,8 @@ def main():
         else:
             merged = da.merged_host(vl, recv.cpu().numpy())
         rp_o, ci_o, va_o = da.owned_csr(vl, merged)
+        if same:
+            d_f = d_f.cpu()
         dist.all_reduce(d_f)                       # residual: the ranks' owned entries (peer) / partial vectors (NCCL) sum to the global vector
         og = orc.Mesh(g)
         rp, ci, va = orc.assemble_K(og).export(og.ndof)
@@ -67,6 +82,8 @@ def main():
         if peer == 1:                              # GetVec_U through the arenas: owned slice of the global vector -> ghosted local vector
             ug_all = torch.from_numpy(mg.displacement_field(g).reshape(-1) + rep).to(dev)
             ul = da.scatter_u(ug_all[da.ep.row_start:da.ep.row_end].contiguous(), torch.empty(loc.pdim * loc.nlnds, dtype=torch.float64, device=dev))
+            if same:
+                da.complete()
             want_u = ug_all.cpu().numpy().reshape(-1, g.pdim)[loc.nl2g - 1].reshape(-1)
             good = good and np.array_equal(ul.cpu().numpy(), want_u)
         if rep == 0 and peer == 0:                 # nodal stress across ranks (femx_stress_partial + DistributedStress)
@@ -82,7 +99,7 @@ def main():
               f"{'OK' if good else 'MISMATCH'}", flush=True)
         ok = ok and bool(good)
     da.close(); fx.close()
-    t = torch.tensor([1 if ok else 0], device=dev)
+    t = torch.tensor([1 if ok else 0], device=comm)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
         print("MGPU PARITY", "OK" if int(t.item()) else "FAILED", flush=True)
