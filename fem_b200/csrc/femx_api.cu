@@ -301,6 +301,7 @@ int femx_build_plan(femx_ctx *c) {
   const bool host_plan = c->opts.reserved[4] == 1;   // plan.cpp / plan_hex.cpp on the host: the cross-check of the device pass (plan_gpu.cu)
   if (!host_plan) {
     if ((rc = build_plan_device(c))) return rc;
+    if ((rc = plan_simplex_localize(c))) return rc;
     if (c->hex.ok) {
       // the tile kernels scale gradients by rsqrt(detJ): a mirrored grid or an inverted element (which the reference and the
       // general kernels assemble as is, src/m_local.F90:61-65) must not reach them
@@ -363,6 +364,7 @@ int femx_build_plan(femx_ctx *c) {
   UP(dm.bptr, P.bptr); UP(dm.bcol, P.bcol); UP(dm.bdiag, P.bdiag); UP(dm.n2e_ptr, P.n2e_ptr); UP(dm.n2e_elem, P.n2e_elem);
   UP(dm.rbe_ptr, P.rbe_ptr); UP(dm.rb_off, P.rb_off); UP(dm.rb_ent, P.rb_ent); UP(dm.sx_ent, P.sx_ent); UP(dm.sx_inc, P.sx_inc); UP(dm.sx_mat, P.sx_mat); UP(dm.ri_nodes, P.ri_nodes); UP(dm.ri_info, P.ri_info);
   UP(dm.n2e_a, P.n2e_a); UP(dm.eb_ptr, P.eb_ptr); UP(dm.bpos, P.bpos); UP(dm.ke_off, P.ke_off); UP(dm.fe_off, P.fe_off);
+  if ((rc = plan_simplex_localize(c))) return rc;
   // stress multiplicity (count_node, src/main.F90:263); mesh constant, computed once
   std::vector<int32_t> cnt(c->nlnds, 0);
   for (int r = 0; r < c->nlnds; ++r)

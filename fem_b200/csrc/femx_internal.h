@@ -53,6 +53,7 @@ struct Plan {
   bool simplex = false;            // every element is a tri3 / tet4 (one integration point)
   int rb_slot = 0, rb_foff = 0;    // slot pitch per incident element (odd) and offset of its f share inside the slot
   int max_inc = 0;                 // largest number of elements around a node
+  int max_nb = 0;                  // widest block row among the rows of the simplex rows kernel (plan_simplex_localize)
   // cohesive overlay: blocks / nodes touched by nonlinear elements, contributions ascending
   std::vector<int32_t> coh_elems;        // local element ids with enlmat != 0
   std::vector<int64_t> cblk_id;          // touched block ids (r-major order)
@@ -152,7 +153,8 @@ struct DevMesh {
   uint16_t *rb_off = nullptr;
   uint16_t *rb_ent = nullptr;
   uint16_t *sx_ent = nullptr;
-  int32_t *sx_inc = nullptr, *sx_mat = nullptr;
+  int32_t *sx_inc = nullptr, *sx_mat = nullptr;   // sx_inc: plan intermediate, released once sx_loc exists
+  uint32_t *sx_loc = nullptr;      // simplex rows kernel: per (node, incident element) the element's nodes as positions in the node's block row, one byte each
   int32_t *ri_nodes = nullptr, *ri_info = nullptr;
   int32_t *node_count = nullptr;  // stress-average multiplicity per local node
 };

@@ -16,6 +16,7 @@ int launch_colidx(femx_ctx *c, int32_t *d_colidx);
 int launch_coo(femx_ctx *c, int32_t *d_i, int32_t *d_j);
 int build_plan_device(femx_ctx *c);          // plan_gpu.cu: the integer pass on the device (default)
 int plan_host_blocks(femx_ctx *c);           // ... host copy of bcol, fetched when an exporter first needs it
+int plan_simplex_localize(femx_ctx *c);     // plan_gpu.cu: sx_inc (node ids) -> sx_loc (positions in the row), after either plan pass
 int plan_host_bpos(femx_ctx *c);             // ... of bpos
 int launch_hex_detj(femx_ctx *c, int *d_bad);   // hex8 meshes: counts (element, integration point) pairs with detJ <= 0
 int launch_apply_kbc(femx_ctx *c, double *d_vals);

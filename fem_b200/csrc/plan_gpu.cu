@@ -166,6 +166,21 @@ __global__ void node_stats_kernel(int nlnds, const int64_t *__restrict__ bptr, c
   atomicMax(&stats[0], nb);
   atomicMax(&stats[1], (int)(n2e_ptr[r + 1] - n2e_ptr[r]));
 }
+// simplex rows kernel: the nodes of every element around node r are columns of r's block row -- name them by their position
+// there (one byte each), so that the kernel fetches the coordinates of a row's column nodes once instead of once per incidence
+__global__ void sx_loc_kernel(int nlnds, int nen, const int64_t *__restrict__ n2e_ptr, const int64_t *__restrict__ bptr, const int32_t *__restrict__ bcol,
+                              const int32_t *__restrict__ sx_inc, uint32_t *__restrict__ sx_loc, int *__restrict__ max_nb) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nlnds) return;
+  const int32_t *b0 = bcol + bptr[r];
+  const int nb = (int)(bptr[r + 1] - bptr[r]);
+  for (int64_t p = n2e_ptr[r]; p < n2e_ptr[r + 1]; ++p) {
+    uint32_t w = 0;
+    for (int b = 0; b < nen; ++b) w |= (uint32_t)row_find(b0, nb, sx_inc[4 * p + b]) << (8 * b);
+    sx_loc[p] = w;
+  }
+  atomicMax(max_nb, nb);
+}
 __global__ void bpos_kernel(int64_t nconn, const int32_t *__restrict__ posel, const int32_t *__restrict__ eptr, const int64_t *__restrict__ eb_ptr,
                             const int32_t *__restrict__ conn0, const int64_t *__restrict__ bptr, const int32_t *__restrict__ bcol, uint16_t *__restrict__ bpos) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -737,6 +752,26 @@ int build_plan_device(femx_ctx *c) {
 }
 
 // host copies of the large plan arrays, fetched when a host-side exporter first needs them
+int plan_simplex_localize(femx_ctx *c) {
+  femx::Plan &P = c->plan;
+  femx::DevMesh &dm = c->dm;
+  if (!P.simplex || P.max_inc < 1 || P.max_inc > 32 || !dm.sx_inc || c->nlnds == 0) return FEMX_OK;   // rows_simplex_ok
+  const int64_t nconn = c->eptr[c->nels];
+  int rc, *d_max = nullptr, h_max = 0;
+  if ((rc = dev_alloc(c, &dm.sx_loc, nconn)) || (rc = dev_alloc(c, &d_max, 1))) return rc;
+  PCK(cudaMemsetAsync(d_max, 0, sizeof(int), c->stream));
+  sx_loc_kernel<<<grid_for(c->nlnds), BS, 0, c->stream>>>(c->nlnds, c->pdim + 1, dm.n2e_ptr, dm.bptr, dm.bcol, dm.sx_inc, dm.sx_loc, d_max);
+  c->launches += 1;
+  PCK(cudaMemcpyAsync(&h_max, d_max, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  PCK(cudaStreamSynchronize(c->stream));
+  PCK(cudaGetLastError());
+  P.max_nb = h_max;
+  dev_release(c, d_max);
+  dev_release(c, dm.sx_inc);
+  dm.sx_inc = nullptr;
+  return FEMX_OK;
+}
+
 int plan_host_blocks(femx_ctx *c) {
   if (c->host_bcol) return FEMX_OK;
   c->plan.bcol.resize((size_t)c->plan.nblk);
