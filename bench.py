@@ -386,7 +386,9 @@ def main():
         sm = tt[4:].clone(); dist.all_reduce(sm)
         breakdown = {"assembly_kernel_ms": {"min": -float(hi[1]), "mean": float(sm[0]) / world, "max": float(hi[0])},
                      "push_barrier_add_ms": {"min": -float(hi[3]), "mean": float(sm[1]) / world, "max": float(hi[2])},
-                     "note": "per rank and step; the barrier waits for the slowest neighbour, so a rank with a fast kernel shows a long push_barrier_add"}
+                     "note": "per rank and step; assembly_kernel_ms = device time until the last tile kernel ends, push_barrier_add_ms = what is left of the "
+                             "exchange after it (the exchange runs on a high-priority stream behind the interface tiles, overlapped with the interior "
+                             "tiles; FEMX_PEER_OVERLAP=0: serial behind the kernel); the barrier waits for the slowest neighbour"}
     io = torch.tensor([float(e2e["h2d"]) if e2e else 0.0, float(e2e["d2h"]) if e2e else 0.0], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(io)             # bytes of all ranks per step
@@ -419,7 +421,8 @@ def main():
                        "PETSC_DECIDE row split, interface rows "
                        + ((("stored by the assembly kernel" if args.exchange == "peer-fused" else "pushed by femx's peer kernel")
                            + " into the owner's arena over NVLink + device-side step barrier among neighbours + receiver add over the "
-                             "interface rows, all inside the timed step")
+                             "interface rows, all inside the timed step"
+                           + ("" if args.exchange == "peer-fused" else "; tiles owning interface rows first, exchange overlapped with the interior tiles"))
                           if da.peer else "sent with NCCL all_to_all after the kernel (receiver add on the host, not timed)")
                        + f" ({int(da.ep.recv_counts.sum()) * 8} B received, {len(da.ep.m_own)} merged values on rank 0 per step)")
         else:
@@ -437,7 +440,7 @@ def main():
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                              "frac_of_8TBs_nominal": achieved / 8000.0, "bytes_per_element": alg / m.nels, "algorithmic_bytes_per_launch": alg,
-                             "kernel": KERNEL_NAME.get(args.variant, "?") + " (one launch per step)", "traffic": traffic,
+                             "kernel": KERNEL_NAME.get(args.variant, "?") + (" (one launch per step)" if world == 1 else " (two launches per step: the CTAs owning interface rows on a high-priority stream with the exchange behind them, the interior CTAs on the ctx stream)"), "traffic": traffic,
                              "ncu_pipe_utilisation": pipes}}
         if check:
             line["check"] = check

@@ -58,6 +58,7 @@ int femx_destroy(femx_ctx *c) {
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   if (c->ev_mid) cudaEventDestroy(c->ev_mid);
+  if (c->peer.hi) { cudaStreamDestroy(c->peer.hi); cudaEventDestroy(c->peer.ev_fork); cudaEventDestroy(c->peer.ev_join); }
   cudaStreamDestroy(c->own_stream);
   delete c;
   return FEMX_OK;
@@ -298,6 +299,7 @@ int femx_build_plan(femx_ctx *c) {
   c->d_bc_diag = nullptr; c->d_bc_dof = nullptr; c->d_bc_val = nullptr;
   const std::vector<void *> before = c->allocs;
   int rc;
+  c->peer.split_valid = false;
   const bool host_plan = c->opts.reserved[4] == 1;   // plan.cpp / plan_hex.cpp on the host: the cross-check of the device pass (plan_gpu.cu)
   if (!host_plan) {
     if ((rc = build_plan_device(c))) return rc;

@@ -73,6 +73,7 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
   }
   if ((rc = begin_timing(c))) return rc;
   if (fint && c->nlnds != c->nnds) CK(cudaMemsetAsync(d_fint, 0, sizeof(double) * (size_t)nglob, c->stream));
+  bool split = false;
   if (fused) {
     const int av = av0 == 0 ? (peer_fused ? 12 : 20) : av0;
 #ifdef FEMX_DIAG
@@ -80,6 +81,20 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
     else if (av == 21) c->launches += launch_hex_mma_prof(c, d_u, d_vals, d_fint);
     else
 #endif
+    // peer exchange behind variant 20: interface CTAs first on a high-priority stream, the exchange behind them, interior CTAs
+    // meanwhile on the ctx stream (FEMX_PEER_OVERLAP=0 keeps one launch and the exchange behind it)
+    static const bool overlap_on = !(getenv("FEMX_PEER_OVERLAP") && atoi(getenv("FEMX_PEER_OVERLAP")) == 0);
+    if (av == 20 && peer && !peer_fused && overlap_on) {
+      if ((rc = peer_hex_split(c))) return rc;
+      split = c->peer.n_cta_if > 0 && c->peer.n_cta_if < c->peer.n_cta;
+    }
+    if (split) {
+      auto &P = c->peer;
+      CK(cudaEventRecord(P.ev_fork, c->stream));
+      CK(cudaStreamWaitEvent(P.hi, P.ev_fork, 0));
+      c->launches += launch_hex_mma_part(c, d_u, d_vals, d_fint, P.d_cta_list, P.n_cta_if, P.hi);
+      c->launches += launch_hex_mma_part(c, d_u, d_vals, d_fint, P.d_cta_list + P.n_cta_if, P.n_cta - P.n_cta_if, c->stream);
+    } else
     c->launches += av == 20 ? launch_hex_mma(c, d_u, d_vals, d_fint) : launch_hex_sym6(c, d_u, d_vals, d_fint);
   } else if (simplex) {
     c->launches += launch_rows_simplex(c, d_u, d_vals, d_fint);
@@ -94,6 +109,16 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
     if (!c->ev_mid) CK(cudaEventCreate(&c->ev_mid));
     CK(cudaEventRecord(c->ev_mid, c->stream));
     c->mid_valid = true;
+    if (split) {   // the exchange follows the interface CTAs on their stream; the ctx stream joins when both are done
+      auto &P = c->peer;
+      cudaStream_t main = c->stream;
+      c->stream = P.hi;
+      const int nl = launch_peer_finish(c, peer_fused, d_vals, d_fint);
+      c->stream = main;
+      c->launches += nl;
+      CK(cudaEventRecord(P.ev_join, P.hi));
+      CK(cudaStreamWaitEvent(c->stream, P.ev_join, 0));
+    } else
     c->launches += launch_peer_finish(c, peer_fused, d_vals, d_fint);   // push, step barrier (the peers' stores into this rank's arena are complete), receiver add
   }
   if ((rc = end_timing(c))) return rc;

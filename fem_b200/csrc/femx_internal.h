@@ -257,5 +257,12 @@ struct femx_ctx {
     int64_t *d_mown = nullptr, *d_mptr = nullptr, *d_midx = nullptr, *d_frow = nullptr, *d_fptr = nullptr, *d_fidx = nullptr;
     int32_t *d_mown32 = nullptr, *d_mptr32 = nullptr, *d_midx32 = nullptr;   // the same lists in 32 bits when everything fits
     double *d_merged = nullptr;
+    // exchange overlapped with the assembly (hex8 tile kernel): the CTAs that own interface rows run first on a high-priority
+    // stream, followed there by push, step barrier and receiver add, while the interior CTAs run on the ctx stream
+    int *d_cta_list = nullptr;             // linear CTA ids: [0, n_cta_if) own an interface row, [n_cta_if, n_cta) do not
+    int n_cta_if = 0, n_cta = 0;
+    bool split_valid = false;
+    cudaStream_t hi = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   } peer;
 };

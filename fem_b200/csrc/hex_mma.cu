@@ -421,7 +421,8 @@ __device__ __forceinline__ void mma_cell(Smem &S, double (&acc)[6][2], const Mma
 
 template <bool WITH_F>
 __global__ void __launch_bounds__(NT, 1)
-FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg_in) {
+FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ vals, double *__restrict__ fint, int LZ, int dbg_in,
+                const int *__restrict__ cta_list) {
 #if FEMX_MMA_PROF
   const int dbg = dbg_in;   // diagnostic: bit 0 skip geometry, 1 DMMA, 2 z-carry, 3 ring stores, 4 gather loads, 5 value stores, 6 f
 #else
@@ -432,8 +433,13 @@ FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   const int tid = threadIdx.x, lane = tid & 31;
   const int wu = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp index in a uniform register
   Tile T;
-  T.i0 = blockIdx.x * NXT; T.j0 = blockIdx.y * NYT;
-  T.l0 = blockIdx.z * LZ; T.l1 = min(T.l0 + LZ, hx.NK) - 1;
+  int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z;
+  if (cta_list) {   // a subset of the grid (peer exchange: interface tiles first, on their own stream): linear ids, x fastest
+    const int gx = (hx.NI + NXT - 1) / NXT, gy = (hx.NJ + NYT - 1) / NYT, id = cta_list[blockIdx.x];
+    bx = id % gx; by = (id / gx) % gy; bz = id / (gx * gy);
+  }
+  T.i0 = bx * NXT; T.j0 = by * NYT;
+  T.l0 = bz * LZ; T.l1 = min(T.l0 + LZ, hx.NK) - 1;
   const int nsteps = T.l1 - T.l0 + 2;   // cell layers l0-1 .. l1; node layers rl = 0 .. nsteps (layer l0 - 1 + rl)
   const double rho = hx.rho;
 
@@ -612,12 +618,10 @@ FEMX_MMA_KERNEL(DevHex hx, const double *__restrict__ u, double *__restrict__ va
   }
 }
 
-int FEMX_MMA_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+// z-chunk length: fewest (waves x steps per chunk); every chunk pays one extra cell layer
+static int mma_lz(const femx_ctx *c, int nsm) {
   const DevHex &hx = c->dhex;
   const int tiles = ((hx.NI + NXT - 1) / NXT) * ((hx.NJ + NYT - 1) / NYT);
-  int nsm = 148;
-  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
-  // z-chunk length: fewest (waves x steps per chunk); every chunk pays one extra cell layer
   int LZ = c->opts.reserved[1] > 0 ? c->opts.reserved[1] : 0;
   if (LZ <= 0) {
     double best = 1e300;
@@ -629,14 +633,47 @@ int FEMX_MMA_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fi
       if (cost < best) { best = cost; LZ = lz; }
     }
   }
-  if (LZ > hx.NK) LZ = hx.NK;
+  return LZ > hx.NK ? hx.NK : LZ;
+}
+
+#if !FEMX_MMA_PROF
+// grid of the tile kernel: tiles in x, tiles in y, z-chunks, node columns / rows per tile, layers per chunk
+void hex_mma_grid(const femx_ctx *c, int *gx, int *gy, int *gz, int *nxt, int *nyt, int *lz) {
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+  const DevHex &hx = c->dhex;
+  *lz = mma_lz(c, nsm);
+  *gx = (hx.NI + NXT - 1) / NXT; *gy = (hx.NJ + NYT - 1) / NYT; *gz = (hx.NK + *lz - 1) / *lz;
+  *nxt = NXT; *nyt = NYT;
+}
+// n CTAs of the grid, named by d_list (linear ids), on stream st
+int launch_hex_mma_part(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, const int *d_list, int n, cudaStream_t st) {
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+  const int LZ = mma_lz(c, nsm);
+  const size_t smem = sizeof(Smem);
+  auto go = [&](auto kern) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<n, NT, smem, st>>>(c->dhex, d_u, d_vals, d_fint, LZ, c->opts.reserved[2], d_list);
+  };
+  if (d_u) go(FEMX_MMA_KERNEL<true>); else go(FEMX_MMA_KERNEL<false>);
+  return 1;
+}
+#endif
+
+int FEMX_MMA_LAUNCH(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint) {
+  const DevHex &hx = c->dhex;
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device);
+  const int LZ = mma_lz(c, nsm);
   dim3 grid((hx.NI + NXT - 1) / NXT, (hx.NJ + NYT - 1) / NYT, (hx.NK + LZ - 1) / LZ);
   const size_t smem = sizeof(Smem);
   static_assert(sizeof(Smem) <= 232448, "shared memory exceeds what a CTA may opt into");
   auto go = [&](auto kern) {
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2]);
+    kern<<<grid, NT, smem, c->stream>>>(hx, d_u, d_vals, d_fint, LZ, c->opts.reserved[2], nullptr);
   };
   if (d_u) go(FEMX_MMA_KERNEL<true>); else go(FEMX_MMA_KERNEL<false>);
 #if FEMX_MMA_PROF

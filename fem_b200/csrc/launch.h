@@ -33,6 +33,9 @@ int launch_gather_sum(femx_ctx *c, const double *a, int64_t na, const double *b,
 int launch_hex_sym6(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_sym7(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 int launch_hex_mma(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
+void hex_mma_grid(const femx_ctx *c, int *gx, int *gy, int *gz, int *nxt, int *nyt, int *lz);
+int launch_hex_mma_part(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint, const int *d_list, int n, cudaStream_t st);
+int peer_hex_split(femx_ctx *c);            // peer.cu: interface / interior CTA lists of the tile kernel (cached)
 int launch_hex_mma_prof(femx_ctx *c, const double *d_u, double *d_vals, double *d_fint);
 PeerTab peer_tab(const femx_ctx *c);          // peer.cu
 int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_fint);   // push + step barrier + receiver add

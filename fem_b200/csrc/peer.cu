@@ -71,7 +71,12 @@ peer_push_kernel(PeerTab pt, const double *__restrict__ vals, const double *__re
       const double *src = vals + pt.vb[q];
       double *dst = pt.vdst[q];
       const long long len = pt.vb[q + 1] - pt.vb[q];
-      for (long long i = tid; i < len; i += nth) dst[i] = src[i];
+      long long i = tid;
+      for (; i + 3 * nth < len; i += 4 * nth) {   // four independent loads in flight per thread: the copy runs on few CTAs when it overlaps the tile kernel
+        const double a0 = src[i], a1 = src[i + nth], a2 = src[i + 2 * nth], a3 = src[i + 3 * nth];
+        dst[i] = a0; dst[i + nth] = a1; dst[i + 2 * nth] = a2; dst[i + 3 * nth] = a3;
+      }
+      for (; i < len; i += nth) dst[i] = src[i];
     }
     if (fint && pt.fdst[q]) {
       double *dst = pt.fdst[q];
@@ -191,6 +196,72 @@ static int launch_peer_merge(femx_ctx *c, const double *d_vals, double *d_fint) 
   return n;
 }
 
+// ---- interface-first order of the hex8 tile kernel --------------------------------------------------------------
+// An interface node is one that another rank also holds: its row is sent (the local dof lies in a peer's f_bounds range)
+// or receives (it is named by the force merge list).  A CTA of the tile kernel that owns such a row runs in the first,
+// high-priority launch; push, step barrier and receiver add follow on that stream while the other CTAs still assemble.
+__global__ void mark_recv_nodes_kernel(int64_t nf, int pdim, const int64_t *__restrict__ f_row, unsigned char *__restrict__ markg) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nf) markg[f_row[s] / pdim] = 1;
+}
+__global__ void mark_cta_kernel(int NI, int NJ, int NK, int nxt, int nyt, int lz, int gx, int gy, const int32_t *__restrict__ node_at,
+                                const int32_t *__restrict__ nl2g, int pdim, long long own_lo, long long own_hi,
+                                const unsigned char *__restrict__ markg, int *__restrict__ flag) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= (int64_t)NI * NJ * NK) return;
+  const int r = node_at[q];
+  if (r < 0) return;
+  const long long dof = (long long)pdim * r;
+  if (dof >= own_lo && dof < own_hi && !markg[nl2g[r] - 1]) return;   // owned here and nobody adds to it
+  const int i = (int)(q % NI), j = (int)((q / NI) % NJ), k = (int)(q / ((int64_t)NI * NJ));
+  flag[((k / lz) * gy + j / nyt) * gx + i / nxt] = 1;
+}
+
+int peer_hex_split(femx_ctx *c) {
+  auto &P = c->peer;
+  if (P.split_valid) return FEMX_OK;
+  CK(cudaSetDevice(c->device));
+  int gx, gy, gz, nxt, nyt, lz;
+  hex_mma_grid(c, &gx, &gy, &gz, &nxt, &nyt, &lz);
+  const int n = gx * gy * gz;
+  const DevHex &hx = c->dhex;
+  unsigned char *d_mark = nullptr;
+  int *d_flag = nullptr, rc;
+  if ((rc = dev_alloc(c, &d_mark, (int64_t)c->nnds)) || (rc = dev_alloc(c, &d_flag, n))) return rc;
+  CK(cudaMemsetAsync(d_mark, 0, (size_t)c->nnds, c->stream));
+  CK(cudaMemsetAsync(d_flag, 0, sizeof(int) * (size_t)n, c->stream));
+  if (P.n_fmerge > 0)
+    mark_recv_nodes_kernel<<<(unsigned)((P.n_fmerge + 255) / 256), 256, 0, c->stream>>>(P.n_fmerge, c->pdim, P.d_frow, d_mark);
+  const int64_t npos = (int64_t)hx.NI * hx.NJ * hx.NK;
+  mark_cta_kernel<<<(unsigned)((npos + 255) / 256), 256, 0, c->stream>>>(hx.NI, hx.NJ, hx.NK, nxt, nyt, lz, gx, gy, hx.node_at, c->dm.nl2g, c->pdim,
+                                                                       (long long)P.fb[P.rank], (long long)P.fb[P.rank + 1], d_mark, d_flag);
+  c->launches += 2;
+  std::vector<int> flag((size_t)n), list;
+  CK(cudaMemcpyAsync(flag.data(), d_flag, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  dev_release(c, d_mark); dev_release(c, d_flag);
+  list.reserve((size_t)n);
+  for (int id = 0; id < n; ++id) if (flag[(size_t)id]) list.push_back(id);
+  P.n_cta_if = (int)list.size();
+  for (int id = 0; id < n; ++id) if (!flag[(size_t)id]) list.push_back(id);
+  P.n_cta = n;
+  if (P.d_cta_list) { dev_release(c, P.d_cta_list); P.d_cta_list = nullptr; }
+  if ((rc = upload(c, &P.d_cta_list, list))) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  if (!P.hi) {
+    int least = 0, greatest = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    CK(cudaStreamCreateWithPriority(&P.hi, cudaStreamNonBlocking, greatest));
+    CK(cudaEventCreateWithFlags(&P.ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&P.ev_join, cudaEventDisableTiming));
+  }
+  P.split_valid = true;
+  if (getenv("FEMX_PEER_TIMING"))
+    fprintf(stderr, "femx peer (rank %d): %d of the tile kernel's %d CTAs own interface rows and run first\n", P.rank, P.n_cta_if, P.n_cta);
+  return FEMX_OK;
+}
+
 // fused = the assembly kernel already stored the interface rows at their owners (PEER instantiations)
 int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_fint) {
   auto &P = c->peer;
@@ -217,7 +288,12 @@ int launch_peer_finish(femx_ctx *c, bool fused, const double *d_vals, double *d_
     ++P.step;
     int64_t nv = 0;
     for (int q = 0; q < P.nranks; ++q) if (q != P.rank) nv += P.vb[q + 1] - P.vb[q];
-    int grid = (int)std::min<int64_t>(296, std::max<int64_t>(1, (nv + 255) / 256 / 8));
+    // behind the assembly: two CTAs per SM.  Overlapped with the interior tiles (the stream is the high-priority one): the
+    // copy is off the critical path, and every SM it touches is one the tile kernel (one CTA = a whole SM) cannot use meanwhile,
+    // so it is confined to a few SMs' worth of CTAs (FEMX_PEER_PUSH_CTAS, default 64 = 8 SMs)
+    static const int ov_ctas = getenv("FEMX_PEER_PUSH_CTAS") ? std::max(1, atoi(getenv("FEMX_PEER_PUSH_CTAS"))) : 64;
+    const int64_t cap = (P.hi && c->stream == P.hi) ? ov_ctas : 296;
+    int grid = (int)std::min<int64_t>(cap, std::max<int64_t>(1, (nv + 255) / 256 / 8));
     peer_push_kernel<<<grid, 256, 0, c->stream>>>(pt, d_vals, d_fint, c->dm.nl2g, c->pdim, fp, mine, P.nbr_mask, P.step, limit, P.d_err,
                                                   reinterpret_cast<unsigned int *>(P.d_err + 1), wait);
   }
@@ -282,6 +358,7 @@ static int peer_connect_common(femx_ctx *c, int nranks, int rank, const int64_t 
   auto &P = c->peer;
   P.nranks = nranks; P.rank = rank;
   P.nbr_mask = 0;
+  P.split_valid = false;
   for (int q = 0; q <= nranks; ++q) { P.vb[q] = val_bounds[q]; P.fb[q] = f_bounds[q]; }
   for (int q = 0; q < nranks; ++q) {
     ARG(val_bounds[q] <= val_bounds[q + 1] && f_bounds[q] <= f_bounds[q + 1], "bounds must ascend");
@@ -360,6 +437,7 @@ int femx_peer_set_merge(femx_ctx *c, int64_t n, const int64_t *own_slot, const i
   P.d_mown = P.d_mptr = P.d_midx = P.d_frow = P.d_fptr = P.d_fidx = nullptr; P.d_merged = nullptr;
   P.d_mown32 = P.d_mptr32 = P.d_midx32 = nullptr;
   P.n_merge = n; P.n_fmerge = nf;
+  P.split_valid = false;
   int rc;
   if (n > 0) {
     if (c->nnz < 2147483647ll && P.nv < 2147483647ll && ptr[n] < 2147483647ll) {   // every slot, arena position and list offset fits 32 bits
@@ -552,6 +630,7 @@ int femx_peer_disconnect(femx_ctx *c) {
     if (P.remote[q]) { if (!P.local) cudaIpcCloseMemHandle(P.remote[q]); P.remote[q] = nullptr; }
   P.connected = false;   // the arena stays until femx_destroy: peers may still have it mapped
   P.deferred = false; P.pending = false;
+  P.split_valid = false;
   return FEMX_OK;
 }
 

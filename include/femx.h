@@ -240,7 +240,12 @@ int femx_gather_sum(femx_ctx *ctx, const double *a, int64_t na, const double *b,
  *   femx_peer_merged        device pointer / length of the merged interface-row values of the last assembly;
  *   femx_peer_recv          device pointers to what the LAST assembly received (source-rank order, as laid out by
  *                           the caller's val_dst / f_dst);
- *   femx_peer_disconnect    unmaps the peers' arenas (call on every rank before any rank destroys its ctx). */
+ *   femx_peer_disconnect    unmaps the peers' arenas (call on every rank before any rank destroys its ctx).
+ * Behind the hex8 tile kernel (assembly variant 20, auto) the exchange overlaps the assembly: the CTAs that own interface
+ * rows run first on a high-priority stream, push, barrier and add follow them there, the interior CTAs run meanwhile on the
+ * ctx stream, which joins before the call returns (in stream / async mode: before later work on that stream).
+ * Environment (read once per process): FEMX_PEER_OVERLAP=0 keeps the exchange serial behind one launch;
+ * FEMX_PEER_PUSH_CTAS=n bounds the overlapped copy kernel's grid (default 64); FEMX_PEER_TIMING=1 prints push / add times. */
 int femx_peer_arena_create(femx_ctx *ctx, int64_t n_recv_vals, int64_t n_recv_f, char handle[64]);
 int femx_peer_connect(femx_ctx *ctx, int nranks, int rank, const char *handles, const int64_t *recv_vals,
                       const int64_t *recv_f, const int64_t *val_bounds, const int64_t *val_dst,
