@@ -84,7 +84,9 @@ int assemble(femx_ctx *c, const double *u_local, double *vals, double *fint, int
     // peer exchange behind variant 20: interface CTAs first on a high-priority stream, the exchange behind them, interior CTAs
     // meanwhile on the ctx stream (FEMX_PEER_OVERLAP=0 keeps one launch and the exchange behind it)
     static const bool overlap_on = !(getenv("FEMX_PEER_OVERLAP") && atoi(getenv("FEMX_PEER_OVERLAP")) == 0);
-    if (av == 20 && peer && !peer_fused && overlap_on) {
+    // (the interface rows are found through the force lists -- every node another rank holds sends or receives a force entry; a host
+    // that set a matrix merge list without a force merge list gets the serial order)
+    if (av == 20 && peer && !peer_fused && overlap_on && (c->peer.n_fmerge > 0 || c->peer.n_merge == 0)) {
       if ((rc = peer_hex_split(c))) return rc;
       split = c->peer.n_cta_if > 0 && c->peer.n_cta_if < c->peer.n_cta;
     }
